@@ -1,0 +1,527 @@
+// K-GEMM / K-CONV-FPROP / K-CONV-DGRAD / K-CONV-WGRAD for sm_100a.
+//
+// One warp-specialised kernel family: D[M,N] (+)= A[M,K] * B[K,N], bf16 inputs, fp32 accumulation in TMEM.
+//   * B is always an "MN-major" operand: a row-major [K, N] matrix in global memory (TF's HWIO filters and
+//     [in,out] FC weights are exactly that), streamed by TMA into 128B-swizzled tiles.
+//   * A is one of
+//       A_TMA_K     dense row-major [M, K]              (FC forward, FC dX)           -> TMA, K-major tiles
+//       A_TMA_MN    dense row-major [K, M] (i.e. A^T)   (FC dW: X^T dY)               -> TMA, MN-major tiles
+//       A_GATHER_K  implicit im2col of an NHWC tensor   (conv fprop, conv dgrad/deconv) -> cp.async gather
+//       A_GATHER_MN implicit im2col^T of an NHWC tensor (conv wgrad)                  -> cp.async gather
+//   * tcgen05.mma (cta_group::1, M=128, N=BLOCK_N, K=16) issued by one thread; accumulator lives in TMEM and is
+//     read back with tcgen05.ld for the fused epilogue (bias, ReLU, bf16/fp32 store, or split-K fp32 red.add).
+//
+// Reference behaviour being replaced: tf.nn.conv2d / conv2d_transpose / matmul calls of
+// /root/reference/distribute_tools.py:69-143,190-208 (library cuDNN/cuBLAS kernels in TF1).
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "ptx.cuh"
+#include "dtf_internal.h"
+
+namespace dtf {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;  // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;  // warps 0-3: gather producers + epilogue; warp 4: MMA issuer; warp 5: TMA
+constexpr int GATHER_LAG = 2;     // cp.async groups kept in flight per producer thread
+
+enum AMode { A_TMA_K = 0, A_TMA_MN = 1, A_GATHER_K = 2, A_GATHER_MN = 3 };
+enum Geo { GEO_FPROP = 0, GEO_DGRAD = 1 };
+
+struct IgemmParams {
+  int M, N, K;
+  // gather source (NHWC bf16) and geometry
+  const __nv_bfloat16* src;
+  int H, W, C;      // source tensor spatial dims / channels
+  int PH, PW;       // pixel grid indexed by the GEMM row (K-mode) or by the reduction index (MN-mode)
+  int KH, KW;
+  int stride, pad_h, pad_w;
+  int geo;
+  // epilogue
+  void* out;
+  int ldc;
+  const float* bias;
+  int relu;
+  int out_fp32;
+  int atomic;
+  int kb_per_split;
+};
+
+template <int BN, int STAGES>
+struct SmemLayout {
+  static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
+  static constexpr int B_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // barriers + slack for 1024 B alignment
+};
+
+// Decompose k (im2col column) -> tap, channel offset. C is a multiple of 8 so a 16 B chunk never straddles taps.
+struct PixelCoord {
+  int n, y, x;
+};
+
+template <int BN, int STAGES, int AMODE>
+__global__ void __launch_bounds__(NUM_THREADS)
+igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+             const IgemmParams p) {
+  using L = SmemLayout<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFFSET);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tile_n = blockIdx.x;
+  const int tile_m = blockIdx.y;
+  const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int kb0 = blockIdx.z * p.kb_per_split;
+  const int kb1 = min(total_kb, kb0 + p.kb_per_split);
+  constexpr bool kGather = (AMODE == A_GATHER_K || AMODE == A_GATHER_MN);
+  constexpr bool kAMn = (AMODE == A_TMA_MN || AMODE == A_GATHER_MN);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], kGather ? 129 : 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    mbar_fence_init();
+  }
+  if (warp == 4) {
+    tmem_alloc<BN>(tmem_slot);
+  }
+  if (warp == 5 && lane == 0) {
+    tma_prefetch_desc(&tma_b);
+    if (!kGather) tma_prefetch_desc(&tma_a);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const uint32_t smem_base = smem_u32(smem);
+  auto a_stage = [&](int s) { return smem_base + s * L::STAGE_BYTES; };
+  auto b_stage = [&](int s) { return smem_base + s * L::STAGE_BYTES + L::A_BYTES; };
+
+  if (warp < 4) {
+    // ===================================================== A producer (gather modes), then epilogue
+    if constexpr (AMODE == A_GATHER_K) {
+      const int r = threadIdx.x;  // tile row owned by this thread
+      const int m = tile_m * BLOCK_M + r;
+      const bool row_ok = m < p.M;
+      int n_img = 0, py = 0, px = 0;
+      if (row_ok) {
+        n_img = m / (p.PH * p.PW);
+        int rem = m - n_img * (p.PH * p.PW);
+        py = rem / p.PW;
+        px = rem - py * p.PW;
+      }
+      const __nv_bfloat16* img = p.src + (size_t)n_img * p.H * p.W * p.C;
+      const uint32_t row_off = r * 128;
+      const uint32_t sw = r & 7;
+      int it = 0;
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        const uint32_t dst_row = a_stage(s) + row_off;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const int k = kb * BLOCK_K + c * 8;
+          const void* srcp = p.src;
+          uint32_t nbytes = 0;
+          if (row_ok && k < p.K) {
+            const int tap = k / p.C;
+            const int ci = k - tap * p.C;
+            const int kh = tap / p.KW;
+            const int kw = tap - kh * p.KW;
+            int iy, ix;
+            bool ok;
+            if (p.geo == GEO_FPROP) {
+              iy = py * p.stride - p.pad_h + kh;
+              ix = px * p.stride - p.pad_w + kw;
+              ok = (iy >= 0) && (iy < p.H) && (ix >= 0) && (ix < p.W);
+            } else {
+              const int ty = py + p.pad_h - kh;
+              const int tx = px + p.pad_w - kw;
+              iy = ty / p.stride;
+              ix = tx / p.stride;
+              ok = (ty >= 0) && (tx >= 0) && (iy * p.stride == ty) && (ix * p.stride == tx) && (iy < p.H) &&
+                   (ix < p.W);
+            }
+            if (ok) {
+              srcp = img + ((size_t)iy * p.W + ix) * p.C + ci;
+              nbytes = 16;
+            }
+          }
+          cp_async16(dst_row + ((c ^ sw) << 4), srcp, nbytes);
+        }
+        cp_async_commit();
+        if (it >= GATHER_LAG) {
+          cp_async_wait<GATHER_LAG>();
+          fence_proxy_async_smem();
+          mbar_arrive(&full_bar[(it - GATHER_LAG) % STAGES]);
+        }
+      }
+      cp_async_wait<0>();
+      fence_proxy_async_smem();
+      for (int j = max(0, it - GATHER_LAG); j < it; ++j) mbar_arrive(&full_bar[j % STAGES]);
+    } else if constexpr (AMODE == A_GATHER_MN) {
+      // A^T tile: [2 atoms][64 reduction rows (pixels)][64 M' elements = 128 B]
+      const int krow = threadIdx.x & 63;
+      const int atom = threadIdx.x >> 6;
+      const uint32_t sw = krow & 7;
+      const uint32_t dst_off = atom * 8192 + krow * 128;
+      // M' chunks owned by this thread are fixed for the whole tile: decode (tap, ci) once.
+      int tap_kh[8], tap_kw[8], tap_ci[8];
+      bool tap_ok[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const int mp = tile_m * BLOCK_M + atom * 64 + c * 8;
+        tap_ok[c] = mp < p.M;
+        const int tap = mp / p.C;
+        tap_ci[c] = mp - tap * p.C;
+        tap_kh[c] = tap / p.KW;
+        tap_kw[c] = tap - tap_kh[c] * p.KW;
+      }
+      int it = 0;
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        const int pix = kb * BLOCK_K + krow;
+        const bool pix_ok = pix < p.K;
+        int n_img = 0, py = 0, px = 0;
+        if (pix_ok) {
+          n_img = pix / (p.PH * p.PW);
+          int rem = pix - n_img * (p.PH * p.PW);
+          py = rem / p.PW;
+          px = rem - py * p.PW;
+        }
+        const __nv_bfloat16* img = p.src + (size_t)n_img * p.H * p.W * p.C;
+        const int by = py * p.stride - p.pad_h;
+        const int bx = px * p.stride - p.pad_w;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        const uint32_t dst_row = a_stage(s) + dst_off;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const int iy = by + tap_kh[c];
+          const int ix = bx + tap_kw[c];
+          const bool ok = pix_ok && tap_ok[c] && (iy >= 0) && (iy < p.H) && (ix >= 0) && (ix < p.W);
+          const void* srcp = ok ? (const void*)(img + ((size_t)iy * p.W + ix) * p.C + tap_ci[c]) : (const void*)p.src;
+          cp_async16(dst_row + ((c ^ sw) << 4), srcp, ok ? 16u : 0u);
+        }
+        cp_async_commit();
+        if (it >= GATHER_LAG) {
+          cp_async_wait<GATHER_LAG>();
+          fence_proxy_async_smem();
+          mbar_arrive(&full_bar[(it - GATHER_LAG) % STAGES]);
+        }
+      }
+      cp_async_wait<0>();
+      fence_proxy_async_smem();
+      for (int j = max(0, it - GATHER_LAG); j < it; ++j) mbar_arrive(&full_bar[j % STAGES]);
+    }
+
+    // ----------------------------------------------------- epilogue: TMEM -> registers -> global
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int r = threadIdx.x;  // accumulator row == TMEM lane
+    const int m = tile_m * BLOCK_M + r;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 32; ++cc) {
+      uint32_t v[32];
+      tmem_ld32(lane_addr + cc * 32, v);
+      tmem_ld_wait();
+      const int n0 = tile_n * BN + cc * 32;
+      if (m < p.M && n0 < p.N) {
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.N) f[j] += __ldg(p.bias + n0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        const bool full = (n0 + 32 <= p.N);
+        if (p.atomic) {
+          float* o = reinterpret_cast<float*>(p.out) + (size_t)m * p.ldc + n0;
+          if (full && ((p.ldc & 3) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(o + j), "f"(f[j]), "f"(f[j + 1]),
+                           "f"(f[j + 2]), "f"(f[j + 3])
+                           : "memory");
+          } else {
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.N) red_add_f32(o + j, f[j]);
+          }
+        } else if (p.out_fp32) {
+          float* o = reinterpret_cast<float*>(p.out) + (size_t)m * p.ldc + n0;
+          if (full && ((p.ldc & 3) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+          } else {
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.N) o[j] = f[j];
+          }
+        } else {
+          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.ldc + n0;
+          if (full && ((p.ldc & 7) == 0)) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 q;
+              q.x = pack_bf16x2(f[j], f[j + 1]);
+              q.y = pack_bf16x2(f[j + 2], f[j + 3]);
+              q.z = pack_bf16x2(f[j + 4], f[j + 5]);
+              q.w = pack_bf16x2(f[j + 6], f[j + 7]);
+              *reinterpret_cast<uint4*>(o + j) = q;
+            }
+          } else {
+            for (int j = 0; j < 32; ++j)
+              if (n0 + j < p.N) o[j] = __float2bfloat16(f[j]);
+          }
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // ===================================================== MMA issuer
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, /*b_mn=*/true);
+    int it = 0;
+    for (int kb = kb0; kb < kb1; ++kb, ++it) {
+      const int s = it % STAGES;
+      const uint32_t ph = (it / STAGES) & 1;
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+          uint64_t adesc, bdesc;
+          if constexpr (kAMn) {
+            adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 128), /*lbo=*/8192, /*sbo=*/1024);
+          } else {
+            adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 2), /*lbo=*/16, /*sbo=*/1024);
+          }
+          bdesc = make_smem_desc(b_stage(s) + k * (UMMA_K * 128), /*lbo=*/8192, /*sbo=*/1024);
+          umma_bf16(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);
+      }
+      __syncwarp();
+    }
+    if (lane == 0) umma_commit(tmem_full_bar);
+    __syncwarp();
+  } else {
+    // ===================================================== TMA producer (B always; A in dense modes)
+    if (lane == 0) {
+      int it = 0;
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        mbar_arrive_expect_tx(&full_bar[s], kGather ? L::B_BYTES : L::STAGE_BYTES);
+        if constexpr (AMODE == A_TMA_K) {
+          tma_load_2d(a_stage(s), &tma_a, &full_bar[s], kb * BLOCK_K, tile_m * BLOCK_M);
+        } else if constexpr (AMODE == A_TMA_MN) {
+          tma_load_2d(a_stage(s), &tma_a, &full_bar[s], tile_m * BLOCK_M, kb * BLOCK_K);
+          tma_load_2d(a_stage(s) + 8192, &tma_a, &full_bar[s], tile_m * BLOCK_M + 64, kb * BLOCK_K);
+        }
+#pragma unroll
+        for (int j = 0; j < BN / 64; ++j)
+          tma_load_2d(b_stage(s) + j * 8192, &tma_b, &full_bar[s], tile_n * BN + j * 64, kb * BLOCK_K);
+      }
+    }
+    __syncwarp();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<BN>(tmem_base);
+  }
+}
+
+// --------------------------------------------------------------------------- SIMT fallback (tiny / unaligned)
+// C[M,N] = act(A*B + bias); a_t: A stored [K,M]; b_t: B stored [N,K]. One thread per output element.
+__global__ void gemm_simt_kernel(const __nv_bfloat16* A, const __nv_bfloat16* B, void* C, const float* bias, int M,
+                                 int N, int K, int lda, int ldb, int ldc, int a_t, int b_t, int relu, int out_fp32,
+                                 int accumulate) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = blockIdx.y * blockDim.y + threadIdx.y;
+  if (m >= M || n >= N) return;
+  float acc = 0.f;
+  for (int k = 0; k < K; ++k) {
+    const float a = __bfloat162float(a_t ? A[(size_t)k * lda + m] : A[(size_t)m * lda + k]);
+    const float b = __bfloat162float(b_t ? B[(size_t)n * ldb + k] : B[(size_t)k * ldb + n]);
+    acc = fmaf(a, b, acc);
+  }
+  if (bias) acc += bias[n];
+  if (relu) acc = fmaxf(acc, 0.f);
+  if (out_fp32) {
+    float* o = reinterpret_cast<float*>(C) + (size_t)m * ldc + n;
+    *o = accumulate ? (*o + acc) : acc;
+  } else {
+    reinterpret_cast<__nv_bfloat16*>(C)[(size_t)m * ldc + n] = __float2bfloat16(acc);
+  }
+}
+
+// --------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || sym == nullptr) return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(sym);
+  return fn;
+}
+
+// 2D bf16 row-major [rows, cols] with leading dimension ld (elements); box = [box_rows, 64 cols], 128B swizzle.
+static int make_map_2d(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                       uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return DTF_ERR_DRIVER;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? DTF_OK : DTF_ERR_TENSORMAP;
+}
+
+template <int BN, int STAGES, int AMODE>
+static int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
+                        cudaStream_t stream) {
+  using L = SmemLayout<BN, STAGES>;
+  static bool attr_set[64] = {};  // per (template instance, device)
+  auto kern = igemm_kernel<BN, STAGES, AMODE>;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL);
+    if (e != cudaSuccess) return DTF_ERR_CUDA;
+    attr_set[dev & 63] = true;
+  }
+  dim3 grid((p.N + BN - 1) / BN, (p.M + BLOCK_M - 1) / BLOCK_M, splits);
+  kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(ta, tb, p);
+  return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+}
+
+template <int AMODE>
+static int dispatch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
+                       cudaStream_t stream) {
+  if (p.N <= 64) return launch_igemm<64, 4, AMODE>(ta, tb, p, splits, stream);
+  return launch_igemm<128, 3, AMODE>(ta, tb, p, splits, stream);
+}
+
+static int pick_splits(int M, int N, int total_kb, int want_split) {
+  if (!want_split) return 1;
+  const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + 127) / 128);
+  int s = (2 * 148 + tiles - 1) / tiles;  // aim for ~2 CTAs per SM
+  s = max(1, min(s, total_kb));
+  return s;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+}  // namespace dtf
+
+using namespace dtf;
+
+// flags
+//   bit0 relu, bit1 out_fp32, bit2 atomic accumulate into fp32 out (split-K allowed), bit3 A is stored [K,M]
+extern "C" int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda,
+                             int ldb, int ldc, int flags, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  const int relu = flags & 1, out_fp32 = (flags >> 1) & 1, atomic = (flags >> 2) & 1, a_t = (flags >> 3) & 1;
+  if (M <= 0 || N <= 0 || K <= 0) return DTF_ERR_ARG;
+  const bool tc_ok = aligned16(A) && aligned16(B) && (lda % 8 == 0) && (ldb % 8 == 0) && (M * (long long)N >= 4096);
+  if (!tc_ok) {
+    dim3 block(32, 8), grid((N + 31) / 32, (M + 7) / 8);
+    gemm_simt_kernel<<<grid, block, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(A),
+                                                 reinterpret_cast<const __nv_bfloat16*>(B), C, bias, M, N, K, lda, ldb,
+                                                 ldc, a_t, 0, relu, out_fp32 | atomic, atomic);
+    return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+  }
+  CUtensorMap ta, tb;
+  int rc;
+  if (a_t) rc = make_map_2d(&ta, A, K, M, lda, 64);
+  else rc = make_map_2d(&ta, A, M, K, lda, 128);
+  if (rc) return rc;
+  rc = make_map_2d(&tb, B, K, N, ldb, 64);
+  if (rc) return rc;
+  IgemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.out = C; p.ldc = ldc; p.bias = bias; p.relu = relu; p.out_fp32 = out_fp32; p.atomic = atomic;
+  const int total_kb = (K + BLOCK_K - 1) / BLOCK_K;
+  const int splits = pick_splits(M, N, total_kb, atomic);
+  p.kb_per_split = (total_kb + splits - 1) / splits;
+  const int eff_splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+  if (a_t) return dispatch_bn<A_TMA_MN>(ta, tb, p, eff_splits, stream);
+  return dispatch_bn<A_TMA_K>(ta, tb, p, eff_splits, stream);
+}
+
+// Implicit-GEMM convolution family on NHWC bf16 tensors. `geo`: 0 = fprop (gather from x), 1 = dgrad / transposed
+// conv (gather from dy). W2d is the row-major [KH*KW*Csrc, Nout] bf16 filter matrix (HWIO for fprop; per-tap
+// transposed HWOI for dgrad). Output [Nimg*PH*PW, Nout] row-major (= NHWC).
+extern "C" int dtf_conv_igemm_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H,
+                                   int W, int C, int PH, int PW, int KH, int KW, int n_out, int stride, int pad_h,
+                                   int pad_w, int geo, int flags, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if ((C % 8) != 0 || (n_out % 8) != 0 || !aligned16(src) || !aligned16(W2d)) return DTF_ERR_ALIGN;
+  CUtensorMap ta{}, tb;
+  IgemmParams p{};
+  p.M = n_img * PH * PW; p.N = n_out; p.K = KH * KW * C;
+  int rc = make_map_2d(&tb, W2d, p.K, n_out, n_out, 64);
+  if (rc) return rc;
+  p.src = reinterpret_cast<const __nv_bfloat16*>(src);
+  p.H = H; p.W = W; p.C = C; p.PH = PH; p.PW = PW; p.KH = KH; p.KW = KW;
+  p.stride = stride; p.pad_h = pad_h; p.pad_w = pad_w; p.geo = geo;
+  p.out = out; p.ldc = n_out; p.bias = bias; p.relu = flags & 1; p.out_fp32 = (flags >> 1) & 1; p.atomic = 0;
+  p.kb_per_split = (p.K + BLOCK_K - 1) / BLOCK_K;
+  return dispatch_bn<A_GATHER_K>(ta, tb, p, 1, stream);
+}
+
+// Filter gradient: dW[KH*KW*C, n_out] (fp32, accumulated with red.add, split over pixels) =
+//   im2col(x)^T [KH*KW*C, P] * dy [P, n_out],  P = n_img*PH*PW output pixels (fprop geometry).
+extern "C" int dtf_conv_wgrad_bf16(const void* x, const void* dy, float* dw, int n_img, int H, int W, int C, int PH,
+                                   int PW, int KH, int KW, int n_out, int stride, int pad_h, int pad_w,
+                                   void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if ((C % 8) != 0 || (n_out % 8) != 0 || !aligned16(x) || !aligned16(dy)) return DTF_ERR_ALIGN;
+  CUtensorMap ta{}, tb;
+  IgemmParams p{};
+  p.M = KH * KW * C; p.N = n_out; p.K = n_img * PH * PW;
+  int rc = make_map_2d(&tb, dy, p.K, n_out, n_out, 64);
+  if (rc) return rc;
+  p.src = reinterpret_cast<const __nv_bfloat16*>(x);
+  p.H = H; p.W = W; p.C = C; p.PH = PH; p.PW = PW; p.KH = KH; p.KW = KW;
+  p.stride = stride; p.pad_h = pad_h; p.pad_w = pad_w; p.geo = GEO_FPROP;
+  p.out = dw; p.ldc = n_out; p.bias = nullptr; p.relu = 0; p.out_fp32 = 1; p.atomic = 1;
+  const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int splits = pick_splits(p.M, p.N, total_kb, 1);
+  p.kb_per_split = (total_kb + splits - 1) / splits;
+  const int eff_splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
+  return dispatch_bn<A_GATHER_MN>(ta, tb, p, eff_splits, stream);
+}

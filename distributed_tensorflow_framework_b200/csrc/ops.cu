@@ -1,0 +1,947 @@
+// Memory-bound ops for sm_100a: input conversion, ReLU/bias-grad, pooling, LRN, batch-norm, fused losses,
+// L2, optimizers (flat arena, fp32 master + bf16 shadow), Philox initialisers, tap transposes.
+// All activations are NHWC bf16 with C % 8 == 0 (16-byte vectors); reductions accumulate in fp32.
+//
+// Reference behaviour being replaced (all TF library calls): /root/reference/distribute_tools.py:123-128 (relu),
+// :160-165 (pool), :168-180 (batch_norm), :183-187 (lrn), :41-66 (init + l2 weight decay);
+// losses of /root/reference/distribute_tower.py:60-76; optimizer apply of /root/reference/distribute_train.py:151-158.
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <math.h>
+#include "dtf_internal.h"
+#include "optim.cuh"
+
+namespace dtf {
+
+struct alignas(16) BF8 {
+  __nv_bfloat162 v[4];
+};
+__device__ __forceinline__ void unpack8(const BF8& b, float (&f)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 t = __bfloat1622float2(b.v[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ BF8 pack8(const float (&f)[8]) {
+  BF8 b;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) b.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return b;
+}
+__device__ __forceinline__ BF8 ld8(const __nv_bfloat16* p) { return *reinterpret_cast<const BF8*>(p); }
+__device__ __forceinline__ void st8(__nv_bfloat16* p, const BF8& b) { *reinterpret_cast<BF8*>(p) = b; }
+
+static inline int grid_for(long long n, int block, int cap = 148 * 16) {
+  long long g = (n + block - 1) / block;
+  if (g < 1) g = 1;
+  if (g > cap) g = cap;
+  return (int)g;
+}
+
+// ------------------------------------------------------------------------------------------- input conversion
+// src: [pixels, C] (fp32 or uint8) -> dst: [pixels, Cpad] bf16, y = x*scale + shift, pad channels zero.
+template <typename T>
+__global__ void convert_input_kernel(const T* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long pixels,
+                                     int C, int Cpad, float scale, float shift) {
+  const int chunks = Cpad / 8;
+  const long long total = pixels * chunks;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / chunks;
+    const int c0 = (int)(i - pix * chunks) * 8;
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      f[j] = (c < C) ? (float)src[pix * C + c] * scale + shift : 0.f;
+    }
+    st8(dst + pix * Cpad + c0, pack8(f));
+  }
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = __float2bfloat16(src[i]);
+}
+__global__ void cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, long long n) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dst[i] = __bfloat162float(src[i]);
+}
+
+// ------------------------------------------------------------------------------------------- elementwise
+__global__ void relu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n8) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(ld8(x + i * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+    st8(y + i * 8, pack8(f));
+  }
+}
+__global__ void relu_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                                __nv_bfloat16* __restrict__ dx, long long n8) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float g[8], a[8];
+    unpack8(ld8(dy + i * 8), g);
+    unpack8(ld8(y + i * 8), a);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = a[j] > 0.f ? g[j] : 0.f;
+    st8(dx + i * 8, pack8(g));
+  }
+}
+// z = a + b (optionally relu)
+__global__ void add_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloat16* __restrict__ b,
+                           __nv_bfloat16* __restrict__ z, long long n8, int relu) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float fa[8], fb[8];
+    unpack8(ld8(a + i * 8), fa);
+    unpack8(ld8(b + i * 8), fb);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      fa[j] += fb[j];
+      if (relu) fa[j] = fmaxf(fa[j], 0.f);
+    }
+    st8(z + i * 8, pack8(fa));
+  }
+}
+
+// ------------------------------------------------------------------------------------------- column reductions
+// Matrix [R, N] bf16 (N % 8 == 0). Each thread owns one 8-column chunk and walks rows; per-block partials are
+// combined with fp32 atomics into acc[NACC][N] (caller zeroes acc).
+//   MODE 0: acc0 += dy                                   (bias grad)
+//   MODE 1: dz = dy*(y>0) -> store; acc0 += dz           (fused ReLU backward + bias grad)
+//   MODE 2: acc0 += x ; acc1 += x*x                      (BN statistics)
+//   MODE 3: dz = relu? dy*(y>0) : dy -> store (if dz);   (BN backward reduce)
+//           acc0 += dz ; acc1 += dz * (x-mean)*rstd
+template <int MODE>
+__global__ void __launch_bounds__(256)
+colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __restrict__ in1,
+                 const __nv_bfloat16* __restrict__ in2, __nv_bfloat16* __restrict__ out, float* __restrict__ acc,
+                 const float* __restrict__ mean, const float* __restrict__ rstd, long long R, int N, int relu,
+                 int rows_per_block) {
+  constexpr int NACC = (MODE >= 2) ? 2 : 1;
+  const int cpr = N / 8;
+  const int cg0 = blockIdx.x * 256;
+  const int cprg = min(256, cpr - cg0);
+  const int rpp = 256 / cprg;  // rows per pass
+  const int tid = threadIdx.x;
+  const bool active = tid < rpp * cprg;
+  const int col_chunk = cg0 + (tid % cprg);
+  const int row_lane = tid / cprg;
+  float a0[8], a1[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) a0[j] = a1[j] = 0.f;
+  float mu[8], rs[8];
+  if (MODE == 3 && active) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      mu[j] = mean[col_chunk * 8 + j];
+      rs[j] = rstd[col_chunk * 8 + j];
+    }
+  }
+  const long long r0 = (long long)blockIdx.y * rows_per_block;
+  const long long r1 = min(R, r0 + rows_per_block);
+  if (active) {
+    for (long long r = r0 + row_lane; r < r1; r += rpp) {
+      const long long off = r * N + (long long)col_chunk * 8;
+      float g[8];
+      unpack8(ld8(in0 + off), g);
+      if (MODE == 1 || (MODE == 3 && relu)) {
+        float y[8];
+        unpack8(ld8(in1 + off), y);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = y[j] > 0.f ? g[j] : 0.f;
+      }
+      if ((MODE == 1 || MODE == 3) && out != nullptr) st8(out + off, pack8(g));
+      if (MODE == 2) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          a0[j] += g[j];
+          a1[j] = fmaf(g[j], g[j], a1[j]);
+        }
+      } else if (MODE == 3) {
+        float x[8];
+        unpack8(ld8(in2 + off), x);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          a0[j] += g[j];
+          a1[j] = fmaf(g[j], (x[j] - mu[j]) * rs[j], a1[j]);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a0[j] += g[j];
+      }
+    }
+  }
+  __shared__ float red[NACC][256][9];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    red[0][tid][j] = a0[j];
+    if (NACC == 2) red[NACC - 1][tid][j] = a1[j];
+  }
+  __syncthreads();
+  if (tid < cprg) {
+#pragma unroll
+    for (int q = 0; q < NACC; ++q) {
+      float s[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] = 0.f;
+      for (int l = 0; l < rpp; ++l)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] += red[q][tid + l * cprg][j];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) atomicAdd(acc + (size_t)q * N + (size_t)(cg0 + tid) * 8 + j, s[j]);
+    }
+  }
+}
+
+template <int MODE>
+static int launch_colreduce(const void* in0, const void* in1, const void* in2, void* out, float* acc,
+                            const float* mean, const float* rstd, long long R, int N, int relu, cudaStream_t st) {
+  if (N % 8) return DTF_ERR_ALIGN;
+  const int cpr = N / 8;
+  const int gx = (cpr + 255) / 256;
+  const int cprg = cpr < 256 ? cpr : 256;
+  const int rpp = 256 / cprg;
+  long long want_blocks = 148 * 8 / gx;
+  long long rows_per_block = (R + want_blocks - 1) / want_blocks;
+  const long long min_rows = (long long)rpp * 8;
+  if (rows_per_block < min_rows) rows_per_block = min_rows;
+  const int gy = (int)((R + rows_per_block - 1) / rows_per_block);
+  colreduce_kernel<MODE><<<dim3(gx, gy), 256, 0, st>>>(
+      (const __nv_bfloat16*)in0, (const __nv_bfloat16*)in1, (const __nv_bfloat16*)in2, (__nv_bfloat16*)out, acc, mean,
+      rstd, R, N, relu, (int)rows_per_block);
+  return DTF_CHECK_LAUNCH();
+}
+
+// ------------------------------------------------------------------------------------------- batch norm
+// stats: [2][N] = {sum, sumsq}. Produces mean, rstd and folded scale/shift; updates running stats (momentum m).
+__global__ void bn_finalize_kernel(const float* __restrict__ stats, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* __restrict__ mean, float* __restrict__ rstd,
+                                   float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ run_mean,
+                                   float* __restrict__ run_var, int N, float inv_R, float eps, float momentum,
+                                   float unbias) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  const float mu = stats[c] * inv_R;
+  float var = stats[N + c] * inv_R - mu * mu;
+  var = fmaxf(var, 0.f);
+  const float rs = rsqrtf(var + eps);
+  mean[c] = mu;
+  rstd[c] = rs;
+  const float g = gamma ? gamma[c] : 1.f;
+  const float b = beta ? beta[c] : 0.f;
+  scale[c] = g * rs;
+  shift[c] = b - mu * g * rs;
+  if (run_mean) run_mean[c] = (1.f - momentum) * run_mean[c] + momentum * mu;
+  if (run_var) run_var[c] = (1.f - momentum) * run_var[c] + momentum * var * unbias;
+}
+// inference: fold running stats
+__global__ void bn_fold_kernel(const float* __restrict__ run_mean, const float* __restrict__ run_var,
+                               const float* __restrict__ gamma, const float* __restrict__ beta,
+                               float* __restrict__ scale, float* __restrict__ shift, int N, float eps) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  const float rs = rsqrtf(run_var[c] + eps);
+  const float g = gamma ? gamma[c] : 1.f;
+  const float b = beta ? beta[c] : 0.f;
+  scale[c] = g * rs;
+  shift[c] = b - run_mean[c] * g * rs;
+}
+// y = x*scale[c] + shift[c] (+res) (relu)
+__global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                                __nv_bfloat16* __restrict__ y, const float* __restrict__ scale,
+                                const float* __restrict__ shift, long long total8, int N, int relu) {
+  const int cpr = N / 8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cpr) * 8;
+    float f[8];
+    unpack8(ld8(x + i * 8), f);
+    const float4 s0 = *reinterpret_cast<const float4*>(scale + c0), s1 = *reinterpret_cast<const float4*>(scale + c0 + 4);
+    const float4 h0 = *reinterpret_cast<const float4*>(shift + c0), h1 = *reinterpret_cast<const float4*>(shift + c0 + 4);
+    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+    if (res) {
+      float r[8];
+      unpack8(ld8(res + i * 8), r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+    }
+    st8(y + i * 8, pack8(f));
+  }
+}
+// dx = gamma*rstd * (dz - sum_dz/R - xhat * sum_dz_xhat/R);  sums: [2][N]
+__global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x,
+                                    __nv_bfloat16* __restrict__ dx, const float* __restrict__ sums,
+                                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                                    const float* __restrict__ gamma, long long total8, int N, float inv_R) {
+  const int cpr = N / 8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cpr) * 8;
+    float g[8], xv[8];
+    unpack8(ld8(dz + i * 8), g);
+    unpack8(ld8(x + i * 8), xv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = c0 + j;
+      const float rs = rstd[c];
+      const float xhat = (xv[j] - mean[c]) * rs;
+      const float ga = gamma ? gamma[c] : 1.f;
+      g[j] = ga * rs * (g[j] - sums[c] * inv_R - xhat * sums[N + c] * inv_R);
+    }
+    st8(dx + i * 8, pack8(g));
+  }
+}
+
+// ------------------------------------------------------------------------------------------- pooling (NHWC)
+__global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int n_img, int H,
+                                int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt, int pl,
+                                int is_max) {
+  const int cpr = C / 8;
+  const long long total = (long long)n_img * OH * OW * cpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cpr) * 8;
+    long long t = i / cpr;
+    const int ow = (int)(t % OW);
+    t /= OW;
+    const int oh = (int)(t % OH);
+    const int n = (int)(t / OH);
+    float a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = is_max ? -INFINITY : 0.f;
+    int cnt = 0;
+    for (int dy = 0; dy < kh; ++dy) {
+      const int ih = oh * sh - pt + dy;
+      if (ih < 0 || ih >= H) continue;
+      for (int dx = 0; dx < kw; ++dx) {
+        const int iw = ow * sw - pl + dx;
+        if (iw < 0 || iw >= W) continue;
+        float f[8];
+        unpack8(ld8(x + (((long long)n * H + ih) * W + iw) * C + c0), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) a[j] = is_max ? fmaxf(a[j], f[j]) : a[j] + f[j];
+        ++cnt;
+      }
+    }
+    if (!is_max) {
+      const float inv = cnt > 0 ? 1.f / cnt : 0.f;  // TF SAME avg-pool excludes padding from the divisor
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] *= inv;
+    }
+    st8(y + i * 8, pack8(a));
+  }
+}
+// Gather-style backward (deterministic, no atomics): each input element visits the windows that cover it.
+// Max: gradient goes to the first maximum of the window in row-major scan order (matches ATen / cuDNN).
+__global__ void pool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                __nv_bfloat16* __restrict__ dx, int n_img, int H, int W, int C, int OH, int OW, int kh,
+                                int kw, int sh, int sw, int pt, int pl, int is_max) {
+  const int cpr = C / 8;
+  const long long total = (long long)n_img * H * W * cpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cpr) * 8;
+    long long t = i / cpr;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    float g[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = 0.f;
+    float xs[8];
+    if (is_max) unpack8(ld8(x + i * 8), xs);
+    const int oh_lo = max(0, (h + pt - kh + sh) / sh), oh_hi = min(OH - 1, (h + pt) / sh);
+    const int ow_lo = max(0, (w + pl - kw + sw) / sw), ow_hi = min(OW - 1, (w + pl) / sw);
+    for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        float d[8];
+        unpack8(ld8(dy + (((long long)n * OH + oh) * OW + ow) * C + c0), d);
+        const int ih0 = oh * sh - pt, iw0 = ow * sw - pl;
+        if (is_max) {
+          // is (h,w) the first max of this window?
+          bool win[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) win[j] = true;
+          for (int ddy = 0; ddy < kh; ++ddy) {
+            const int ih = ih0 + ddy;
+            if (ih < 0 || ih >= H) continue;
+            for (int ddx = 0; ddx < kw; ++ddx) {
+              const int iw = iw0 + ddx;
+              if (iw < 0 || iw >= W) continue;
+              if (ih == h && iw == w) continue;
+              float f[8];
+              unpack8(ld8(x + (((long long)n * H + ih) * W + iw) * C + c0), f);
+              const bool before = (ih < h) || (ih == h && iw < w);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                if (before ? (f[j] >= xs[j]) : (f[j] > xs[j])) win[j] = false;
+              }
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] += win[j] ? d[j] : 0.f;
+        } else {
+          const int h0 = max(ih0, 0), h1 = min(ih0 + kh, H), w0 = max(iw0, 0), w1 = min(iw0 + kw, W);
+          const float inv = 1.f / ((h1 - h0) * (w1 - w0));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] += d[j] * inv;
+        }
+      }
+    }
+    st8(dx + i * 8, pack8(g));
+  }
+}
+
+// ------------------------------------------------------------------------------------------- LRN (across channels)
+// s_c = bias + alpha * sum_{|j-c|<=r} x_j^2 ; y_c = x_c * s_c^-beta   (TF semantics: alpha is NOT divided by n)
+__device__ __forceinline__ void lrn_load24(const __nv_bfloat16* row, int c0, int C, float (&v)[24]) {
+  // channels c0-8 .. c0+15 (zero outside [0,C))
+#pragma unroll
+  for (int q = 0; q < 3; ++q) {
+    const int cb = c0 - 8 + q * 8;
+    if (cb >= 0 && cb < C) {
+      float f[8];
+      unpack8(ld8(row + cb), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[q * 8 + j] = f[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[q * 8 + j] = 0.f;
+    }
+  }
+}
+__global__ void lrn_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long pixels,
+                               int C, int radius, float bias, float alpha, float beta) {
+  const int cpr = C / 8;
+  const long long total = pixels * cpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / cpr;
+    const int c0 = (int)(i - pix * cpr) * 8;
+    float v[24];
+    lrn_load24(x + pix * C, c0, C, v);
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float s = 0.f;
+      for (int d = -radius; d <= radius; ++d) {
+        const float t = v[8 + j + d];
+        s = fmaf(t, t, s);
+      }
+      s = bias + alpha * s;
+      o[j] = v[8 + j] * __powf(s, -beta);
+    }
+    st8(y + pix * C + c0, pack8(o));
+  }
+}
+// dx_i = dy_i s_i^-b - 2ab x_i sum_{|j-i|<=r} dy_j x_j s_j^(-b-1)
+__global__ void lrn_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                               __nv_bfloat16* __restrict__ dx, long long pixels, int C, int radius, float bias,
+                               float alpha, float beta) {
+  const int cpr = C / 8;
+  const long long total = pixels * cpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / cpr;
+    const int c0 = (int)(i - pix * cpr) * 8;
+    // need x on [c0-2r, c0+7+2r] and dy on [c0-r, c0+7+r]; radius <= 4 keeps both within +-8
+    float xv[24], gv[24];
+    lrn_load24(x + pix * C, c0, C, xv);
+    lrn_load24(dy + pix * C, c0, C, gv);
+    float sc[16 + 8];  // s for channels c0-4 .. c0+11 stored at index (j+4)
+    float tt[16 + 8];
+#pragma unroll
+    for (int j = -4; j < 12; ++j) {
+      float s = 0.f;
+      for (int d = -radius; d <= radius; ++d) {
+        const int idx = 8 + j + d;
+        const float t = (idx >= 0 && idx < 24) ? xv[idx] : 0.f;
+        s = fmaf(t, t, s);
+      }
+      s = bias + alpha * s;
+      sc[j + 4] = s;
+      tt[j + 4] = gv[8 + j] * xv[8 + j] * __powf(s, -beta - 1.f);
+    }
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float acc = 0.f;
+      for (int d = -radius; d <= radius; ++d) acc += tt[j + d + 4];
+      o[j] = gv[8 + j] * __powf(sc[j + 4], -beta) - 2.f * alpha * beta * xv[8 + j] * acc;
+    }
+    st8(dx + pix * C + c0, pack8(o));
+  }
+}
+
+// ------------------------------------------------------------------------------------------- fused losses
+// Scratch protocol shared by the loss kernels: scratch[0] is an arrival counter (as uint32, must be 0 on entry; the
+// last block resets it to 0), scratch[1 + i] holds per-row / per-block partials. The last block to arrive performs
+// the final reduction in a fixed order, so the loss value is deterministic.
+template <typename T>
+__device__ __forceinline__ float ldf(const T* p, long long i);
+template <>
+__device__ __forceinline__ float ldf<float>(const float* p, long long i) { return p[i]; }
+template <>
+__device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p, long long i) {
+  return __bfloat162float(p[i]);
+}
+template <typename T>
+__device__ __forceinline__ void stf(T* p, long long i, float v);
+template <>
+__device__ __forceinline__ void stf<float>(float* p, long long i, float v) { p[i] = v; }
+template <>
+__device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, long long i, float v) {
+  p[i] = __float2bfloat16(v);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// Final, ordered reduction of `n` partials by the last-arriving block. Returns true in thread 0 of that block.
+__device__ bool last_block_reduce(float* scratch, int n, float* result_out, float scale) {
+  __shared__ bool is_last;
+  __shared__ float wsum[32];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int* counter = reinterpret_cast<unsigned int*>(scratch);
+    const unsigned int prev = atomicAdd(counter, 1u);
+    is_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return false;
+  __threadfence();
+  float s = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s += __ldcg(scratch + 1 + i);
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < (blockDim.x + 31) / 32; ++w) t += wsum[w];
+    *result_out = t * scale;
+    *reinterpret_cast<unsigned int*>(scratch) = 0u;  // ready for the next call
+    return true;
+  }
+  return false;
+}
+
+// One warp per row. loss = mean_i(logsumexp(x_i) - x_i[label_i]); dlogits = (softmax - onehot) * gscale / B.
+template <typename T>
+__global__ void __launch_bounds__(256)
+softmax_xent_kernel(const T* __restrict__ logits, const long long* __restrict__ labels, T* __restrict__ dlogits,
+                    float* __restrict__ loss_out, float* __restrict__ scratch, int B, int C, float gscale) {
+  const int warps_per_block = blockDim.x >> 5;
+  const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row < B) {
+    const T* x = logits + (long long)row * C;
+    float mx = -INFINITY;
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, ldf(x, c));
+    mx = warp_max(mx);
+    float se = 0.f;
+    for (int c = lane; c < C; c += 32) se += __expf(ldf(x, c) - mx);
+    se = warp_sum(se);
+    const int lab = (int)labels[row];
+    const float lse = mx + __logf(se);
+    if (lane == 0) scratch[1 + row] = lse - ldf(x, lab);
+    if (dlogits != nullptr) {
+      const float inv = 1.f / se;
+      const float gs = gscale / (float)B;
+      T* d = dlogits + (long long)row * C;
+      for (int c = lane; c < C; c += 32) {
+        float pr = __expf(ldf(x, c) - mx) * inv;
+        if (c == lab) pr -= 1.f;
+        stf(d, c, pr * gs);
+      }
+    }
+  }
+  last_block_reduce(scratch, B, loss_out, 1.f / (float)B);
+}
+
+// loss = mean((p-t)^2); dp = 2 (p-t) gscale / n. Per-block partial sums in scratch[1 + blockIdx.x].
+template <typename T>
+__global__ void __launch_bounds__(256)
+mse_kernel(const T* __restrict__ pred, const T* __restrict__ target, T* __restrict__ dpred,
+           float* __restrict__ loss_out, float* __restrict__ scratch, long long n, float gscale) {
+  float s = 0.f;
+  const float gs = 2.f * gscale / (float)n;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float d = ldf(pred, i) - ldf(target, i);
+    s = fmaf(d, d, s);
+    if (dpred != nullptr) stf(dpred, i, d * gs);
+  }
+  __shared__ float wsum[8];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += wsum[w];
+    scratch[1 + blockIdx.x] = t;
+  }
+  last_block_reduce(scratch, gridDim.x, loss_out, 1.f / (float)n);
+}
+
+// out = 0.5 * sum(w^2) * scale, same scratch protocol.
+__global__ void __launch_bounds__(256)
+l2_kernel(const float* __restrict__ w, float* __restrict__ out, float* __restrict__ scratch, long long n, float scale) {
+  float s = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    s = fmaf(w[i], w[i], s);
+  __shared__ float wsum[8];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w2 = 0; w2 < 8; ++w2) t += wsum[w2];
+    scratch[1 + blockIdx.x] = t;
+  }
+  last_block_reduce(scratch, gridDim.x, out, 0.5f * scale);
+}
+
+// ------------------------------------------------------------------------------------------- optimizers
+// kind: 0 = SGD, 1 = momentum (v = mu*v + g; p -= lr*v, TF MomentumOptimizer), 2 = Adam (TF AdamOptimizer form).
+// g is pre-scaled by gscale (1/num_replicas); wd adds wd*p to the gradient. Writes the bf16 shadow copy.
+__global__ void optim_kernel(int kind, float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                             float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n, float lr,
+                             float b1, float b2, float eps, float wd, float gscale, float lr_t) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float np = optim_update(kind, p[i], g[i] * gscale, m, v, i, lr, b1, b2, eps, wd, lr_t);
+    p[i] = np;
+    if (shadow) shadow[i] = __float2bfloat16(np);
+  }
+}
+
+// Batched per-tap transpose of bf16 filters: src [T, Ci, Co] -> dst [T, Co, Ci] for many variables in one launch.
+struct TapDesc {
+  long long src_off, dst_off;  // element offsets into the bf16 arenas
+  int T, Ci, Co;
+  int tile_start;  // prefix sum of 32x32 tiles
+};
+__global__ void tap_transpose_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                     const TapDesc* __restrict__ descs, int ndesc) {
+  __shared__ __nv_bfloat16 tile[32][33];
+  const int tileid = blockIdx.x;
+  int lo = 0, hi = ndesc - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (descs[mid].tile_start <= tileid) lo = mid;
+    else hi = mid - 1;
+  }
+  const TapDesc d = descs[lo];
+  const int local = tileid - d.tile_start;
+  const int tci = (d.Ci + 31) / 32, tco = (d.Co + 31) / 32;
+  const int t = local / (tci * tco);
+  const int rem = local - t * (tci * tco);
+  const int bi = rem / tco, bo = rem - bi * tco;
+  const __nv_bfloat16* s = src + d.src_off + (long long)t * d.Ci * d.Co;
+  __nv_bfloat16* o = dst + d.dst_off + (long long)t * d.Ci * d.Co;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int ci = bi * 32 + r, co = bo * 32 + threadIdx.x;
+    if (ci < d.Ci && co < d.Co) tile[r][threadIdx.x] = s[(long long)ci * d.Co + co];
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    const int co = bo * 32 + r, ci = bi * 32 + threadIdx.x;
+    if (ci < d.Ci && co < d.Co) o[(long long)co * d.Ci + ci] = tile[threadIdx.x][r];
+  }
+}
+
+// ------------------------------------------------------------------------------------------- Philox init
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+    const uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += W0;
+    key.y += W1;
+  }
+  return ctr;
+}
+__device__ __forceinline__ float u01(uint32_t x) { return ((x >> 8) + 0.5f) * (1.f / 16777216.f); }
+// kind 0: constant a; 1: uniform [a, b); 2: normal(mean a, std b); 3: truncated normal (|z| <= 2), mean a, std b
+__global__ void init_kernel(float* __restrict__ out, long long n, int kind, float a, float b, unsigned long long seed,
+                            unsigned long long stream_id) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    if (kind == 0) {
+      out[i] = a;
+      continue;
+    }
+    const uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+    float val = a;
+    for (uint32_t attempt = 0; attempt < 8; ++attempt) {
+      const uint4 r = philox4x32_10(
+          make_uint4((uint32_t)i, (uint32_t)((unsigned long long)i >> 32), (uint32_t)stream_id, attempt), key);
+      if (kind == 1) {
+        val = a + (b - a) * u01(r.x);
+        break;
+      }
+      const float rad = sqrtf(-2.f * __logf(u01(r.x)));
+      const float z0 = rad * __cosf(6.283185307f * u01(r.y));
+      const float z1 = rad * __sinf(6.283185307f * u01(r.y));
+      if (kind == 2) {
+        val = a + b * z0;
+        break;
+      }
+      if (fabsf(z0) <= 2.f) {
+        val = a + b * z0;
+        break;
+      }
+      if (fabsf(z1) <= 2.f) {
+        val = a + b * z1;
+        break;
+      }
+      val = a;  // astronomically unlikely after 16 draws
+    }
+    out[i] = val;
+  }
+}
+
+__global__ void fill_u32_kernel(uint32_t* p, long long n, uint32_t v) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    p[i] = v;
+}
+
+// top-1 hits: count rows whose argmax equals the label (first max wins, like torch.argmax)
+template <typename T>
+__global__ void top1_kernel(const T* __restrict__ logits, const long long* __restrict__ labels,
+                            unsigned int* __restrict__ hits, int B, int C) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= B) return;
+  float best = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int c = lane; c < C; c += 32) {
+    const float v = ldf(logits + (long long)row * C, c);
+    if (v > best) {
+      best = v;
+      bi = c;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ob > best || (ob == best && oi < bi)) {
+      best = ob;
+      bi = oi;
+    }
+  }
+  if (lane == 0 && bi == (int)labels[row]) atomicAdd(hits, 1u);
+}
+
+}  // namespace dtf
+
+using namespace dtf;
+#define ST(s) dtf_stream(s)
+
+extern "C" int dtf_convert_input(const void* src, void* dst, long long pixels, int C, int Cpad, float scale,
+                                 float shift, int src_is_u8, void* stream) {
+  if (Cpad % 8 || Cpad < C) return DTF_ERR_ALIGN;
+  const int g = grid_for(pixels * (Cpad / 8), 256);
+  if (src_is_u8)
+    convert_input_kernel<uint8_t><<<g, 256, 0, ST(stream)>>>((const uint8_t*)src, (__nv_bfloat16*)dst, pixels, C, Cpad,
+                                                             scale, shift);
+  else
+    convert_input_kernel<float><<<g, 256, 0, ST(stream)>>>((const float*)src, (__nv_bfloat16*)dst, pixels, C, Cpad,
+                                                           scale, shift);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
+  cast_f32_bf16_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(src, (__nv_bfloat16*)dst, n);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_cast_bf16_to_f32(const void* src, float* dst, long long n, void* stream) {
+  cast_bf16_f32_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)src, dst, n);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_relu_fwd(const void* x, void* y, long long n, void* stream) {
+  if (n % 8) return DTF_ERR_ALIGN;
+  relu_fwd_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_relu_bwd(const void* dy, const void* y, void* dx, long long n, void* stream) {
+  if (n % 8) return DTF_ERR_ALIGN;
+  relu_bwd_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,
+                                                                (__nv_bfloat16*)dx, n / 8);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_add(const void* a, const void* b, void* z, long long n, int relu, void* stream) {
+  if (n % 8) return DTF_ERR_ALIGN;
+  add_kernel<<<grid_for(n / 8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)a, (const __nv_bfloat16*)b,
+                                                           (__nv_bfloat16*)z, n / 8, relu);
+  return DTF_CHECK_LAUNCH();
+}
+// db[N] += colsum(dy[R,N])   (db must be zeroed by the caller when starting a new accumulation)
+extern "C" int dtf_bias_grad(const void* dy, float* db, long long R, int N, void* stream) {
+  return launch_colreduce<0>(dy, nullptr, nullptr, nullptr, db, nullptr, nullptr, R, N, 0, ST(stream));
+}
+// dz = dy * (y > 0); db[N] += colsum(dz)
+extern "C" int dtf_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db, long long R, int N,
+                                      void* stream) {
+  return launch_colreduce<1>(dy, y, nullptr, dz, db, nullptr, nullptr, R, N, 1, ST(stream));
+}
+// stats[2][N] += {sum x, sum x^2}
+extern "C" int dtf_bn_stats(const void* x, float* stats, long long R, int N, void* stream) {
+  return launch_colreduce<2>(x, nullptr, nullptr, nullptr, stats, nullptr, nullptr, R, N, 0, ST(stream));
+}
+extern "C" int dtf_bn_finalize(const float* stats, const float* gamma, const float* beta, float* mean, float* rstd,
+                               float* scale, float* shift, float* run_mean, float* run_var, int N, long long R,
+                               float eps, float momentum, void* stream) {
+  const float unbias = R > 1 ? (float)R / (float)(R - 1) : 1.f;
+  bn_finalize_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(stats, gamma, beta, mean, rstd, scale, shift, run_mean,
+                                                              run_var, N, 1.f / (float)R, eps, momentum, unbias);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma, const float* beta,
+                           float* scale, float* shift, int N, float eps, void* stream) {
+  bn_fold_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(run_mean, run_var, gamma, beta, scale, shift, N, eps);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift,
+                            long long R, int N, int relu, void* stream) {
+  if (N % 8) return DTF_ERR_ALIGN;
+  const long long total8 = R * (N / 8);
+  bn_apply_kernel<<<grid_for(total8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)res,
+                                                                 (__nv_bfloat16*)y, scale, shift, total8, N, relu);
+  return DTF_CHECK_LAUNCH();
+}
+// sums[2][N] += {sum dz, sum dz*xhat}; dz (optional output) = relu ? dy*(y>0) : dy
+extern "C" int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* sums,
+                                 const float* mean, const float* rstd, long long R, int N, int relu, void* stream) {
+  return launch_colreduce<3>(dy, y, x, dz, sums, mean, rstd, R, N, relu, ST(stream));
+}
+extern "C" int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* sums, const float* mean,
+                                const float* rstd, const float* gamma, long long R, int N, void* stream) {
+  if (N % 8) return DTF_ERR_ALIGN;
+  const long long total8 = R * (N / 8);
+  bn_bwd_apply_kernel<<<grid_for(total8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)x,
+                                                                     (__nv_bfloat16*)dx, sums, mean, rstd, gamma,
+                                                                     total8, N, 1.f / (float)R);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_pool_fwd(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int kh, int kw,
+                            int sh, int sw, int pt, int pl, int is_max, void* stream) {
+  if (C % 8) return DTF_ERR_ALIGN;
+  const long long total = (long long)n_img * OH * OW * (C / 8);
+  pool_fwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n_img, H,
+                                                                W, C, OH, OW, kh, kw, sh, sw, pt, pl, is_max);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_pool_bwd(const void* x, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW,
+                            int kh, int kw, int sh, int sw, int pt, int pl, int is_max, void* stream) {
+  if (C % 8) return DTF_ERR_ALIGN;
+  const long long total = (long long)n_img * H * W * (C / 8);
+  pool_bwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
+                                                                (__nv_bfloat16*)dx, n_img, H, W, C, OH, OW, kh, kw,
+                                                                sh, sw, pt, pl, is_max);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_lrn_fwd(const void* x, void* y, long long pixels, int C, int radius, float bias, float alpha,
+                           float beta, void* stream) {
+  if (C % 8 || radius > 4 || radius < 0) return DTF_ERR_UNSUPPORTED;
+  lrn_fwd_kernel<<<grid_for(pixels * (C / 8), 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y,
+                                                                          pixels, C, radius, bias, alpha, beta);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_lrn_bwd(const void* x, const void* dy, void* dx, long long pixels, int C, int radius, float bias,
+                           float alpha, float beta, void* stream) {
+  if (C % 8 || radius > 4 || radius < 0) return DTF_ERR_UNSUPPORTED;
+  lrn_bwd_kernel<<<grid_for(pixels * (C / 8), 128), 128, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, pixels, C, radius, bias, alpha, beta);
+  return DTF_CHECK_LAUNCH();
+}
+
+// Loss kernels. `scratch` is caller-provided global memory: 1 + B floats (xent) or 1 + dtf_loss_scratch_blocks()
+// floats (mse / l2); word 0 must be zero before the first call and is left zero by every call.
+extern "C" int dtf_loss_scratch_blocks(void) { return 148 * 8; }
+extern "C" int dtf_softmax_xent(const void* logits, const long long* labels, void* dlogits, float* loss,
+                                float* scratch, int B, int C, float gscale, int is_bf16, void* stream) {
+  if (B <= 0 || C <= 0) return DTF_ERR_ARG;
+  const int blocks = (B + 7) / 8;
+  if (is_bf16)
+    softmax_xent_kernel<__nv_bfloat16><<<blocks, 256, 0, ST(stream)>>>(
+        (const __nv_bfloat16*)logits, labels, (__nv_bfloat16*)dlogits, loss, scratch, B, C, gscale);
+  else
+    softmax_xent_kernel<float><<<blocks, 256, 0, ST(stream)>>>((const float*)logits, labels, (float*)dlogits, loss,
+                                                               scratch, B, C, gscale);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_mse(const void* pred, const void* target, void* dpred, float* loss, float* scratch, long long n,
+                       float gscale, int is_bf16, void* stream) {
+  if (n <= 0) return DTF_ERR_ARG;
+  const int blocks = grid_for(n, 256 * 8, dtf_loss_scratch_blocks());
+  if (is_bf16)
+    mse_kernel<__nv_bfloat16><<<blocks, 256, 0, ST(stream)>>>((const __nv_bfloat16*)pred, (const __nv_bfloat16*)target,
+                                                              (__nv_bfloat16*)dpred, loss, scratch, n, gscale);
+  else
+    mse_kernel<float><<<blocks, 256, 0, ST(stream)>>>((const float*)pred, (const float*)target, (float*)dpred, loss,
+                                                      scratch, n, gscale);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_l2_loss(const float* w, float* out, float* scratch, long long n, float scale, void* stream) {
+  if (n <= 0) return DTF_ERR_ARG;
+  const int blocks = grid_for(n, 256 * 8, dtf_loss_scratch_blocks());
+  l2_kernel<<<blocks, 256, 0, ST(stream)>>>(w, out, scratch, n, scale);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_top1_hits(const void* logits, const long long* labels, unsigned int* hits, int B, int C,
+                             int is_bf16, void* stream) {
+  const int blocks = (B + 7) / 8;
+  if (is_bf16)
+    top1_kernel<__nv_bfloat16><<<blocks, 256, 0, ST(stream)>>>((const __nv_bfloat16*)logits, labels, hits, B, C);
+  else
+    top1_kernel<float><<<blocks, 256, 0, ST(stream)>>>((const float*)logits, labels, hits, B, C);
+  return DTF_CHECK_LAUNCH();
+}
+
+extern "C" int dtf_optim_step(int kind, float* p, const float* g, float* m, float* v, void* shadow, long long n,
+                              float lr, float b1, float b2, float eps, float wd, float gscale, long long step,
+                              void* stream) {
+  if (kind < 0 || kind > 2) return DTF_ERR_ARG;
+  float lr_t = lr;
+  if (kind == 2) lr_t = lr * sqrtf(1.f - powf(b2, (float)step)) / (1.f - powf(b1, (float)step));
+  optim_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(kind, p, g, m, v, (__nv_bfloat16*)shadow, n, lr, b1, b2, eps,
+                                                         wd, gscale, lr_t);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_tap_transpose(const void* src, void* dst, const void* descs_dev, int ndesc, int total_tiles,
+                                 void* stream) {
+  if (total_tiles <= 0) return DTF_OK;
+  tap_transpose_kernel<<<total_tiles, dim3(32, 8), 0, ST(stream)>>>((const __nv_bfloat16*)src, (__nv_bfloat16*)dst,
+                                                                    (const TapDesc*)descs_dev, ndesc);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_init(float* out, long long n, int kind, float a, float b, unsigned long long seed,
+                        unsigned long long stream_id, void* stream) {
+  init_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(out, n, kind, a, b, seed, stream_id);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_fill_u32(void* p, long long n, unsigned int v, void* stream) {
+  fill_u32_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>((uint32_t*)p, n, v);
+  return DTF_CHECK_LAUNCH();
+}

@@ -1,0 +1,159 @@
+/* dtf_b200 -- C ABI of the B200-native kernel library (libdtf_b200_cuda.so).
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on (a cudaStream_t passed as void*),
+ * returns 0 on success or a DTF_ERR_* code, and never synchronises the device. Activations are NHWC bf16 with the
+ * channel count a multiple of 8; parameters are fp32 masters with bf16 "shadow" copies for the tensor cores.
+ * The Python bindings (distributed_tensorflow_framework_b200/ops/_lib.py) parse THIS file to build their ctypes
+ * signatures, so a declaration here is the single source of truth: one function per declaration, scalar types
+ * limited to int / long long / unsigned int / unsigned long long / size_t / float, everything else is a pointer.
+ *
+ * Reference parity citations are relative to /root/reference/.
+ */
+#ifndef DTF_B200_H_
+#define DTF_B200_H_
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DTF_OK 0
+#define DTF_ERR_ARG 1
+#define DTF_ERR_ALIGN 2
+#define DTF_ERR_CUDA 3
+#define DTF_ERR_DRIVER 4
+#define DTF_ERR_TENSORMAP 5
+#define DTF_ERR_TOO_LARGE 6
+#define DTF_ERR_UNSUPPORTED 7
+
+/* ---- tcgen05 / TMEM / TMA GEMM family (csrc/igemm.cu) --------------------------------------------------------- */
+
+/* C[M,N] = act(A[M,K] * B[K,N] + bias). B row-major [K,N] (ldb). A row-major [M,K] (lda), or [K,M] when flag bit3.
+ * flags: bit0 relu, bit1 fp32 output, bit2 accumulate into fp32 C with red.add (split-K), bit3 A stored [K,M].
+ * Replaces tf.matmul + bias_add + relu of FC_layer (distribute_tools.py:190-208) and its gradients. */
+int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
+                  int ldc, int flags, void* stream);
+
+/* Implicit-GEMM convolution on NHWC bf16. geo 0: forward conv (gather from x[n_img,H,W,C], output pixel grid PHxPW);
+ * geo 1: data gradient / transposed conv (gather from dy[n_img,H,W,C], output grid PHxPW is the input image grid).
+ * W2d is the row-major [KH*KW*C, n_out] filter matrix. flags: bit0 relu, bit1 fp32 output.
+ * Replaces tf.nn.conv2d+bias_add+relu (distribute_tools.py:69-121) and tf.nn.conv2d_transpose (:131-157). */
+int dtf_conv_igemm_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H, int W,
+                        int C, int PH, int PW, int KH, int KW, int n_out, int stride, int pad_h, int pad_w, int geo,
+                        int flags, void* stream);
+
+/* Filter gradient dW[KH*KW*C, n_out] (fp32, red.add accumulated; zero it first) from x[n_img,H,W,C] and
+ * dy[n_img,PH,PW,n_out]. Backward of the conv layers above (TF autodiff, distribute_tower.py:26-27). */
+int dtf_conv_wgrad_bf16(const void* x, const void* dy, float* dw, int n_img, int H, int W, int C, int PH, int PW,
+                        int KH, int KW, int n_out, int stride, int pad_h, int pad_w, void* stream);
+
+/* ---- memory-bound ops (csrc/ops.cu) --------------------------------------------------------------------------- */
+
+/* [pixels,C] fp32 or uint8 -> [pixels,Cpad] bf16, y = x*scale + shift, pad channels zero (input pipeline tail,
+ * distribute_input.py:54-106). */
+int dtf_convert_input(const void* src, void* dst, long long pixels, int C, int Cpad, float scale, float shift,
+                      int src_is_u8, void* stream);
+int dtf_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
+int dtf_cast_bf16_to_f32(const void* src, float* dst, long long n, void* stream);
+
+/* acti_layer (distribute_tools.py:123-128) and its gradient; z = a + b (+relu) for residual joins. */
+int dtf_relu_fwd(const void* x, void* y, long long n, void* stream);
+int dtf_relu_bwd(const void* dy, const void* y, void* dx, long long n, void* stream);
+int dtf_add(const void* a, const void* b, void* z, long long n, int relu, void* stream);
+
+/* db[N] += column sums of dy[R,N]; fused variant also writes dz = dy*(y>0). (bias_add gradient) */
+int dtf_bias_grad(const void* dy, float* db, long long R, int N, void* stream);
+int dtf_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db, long long R, int N, void* stream);
+
+/* Batch norm over the rows of x[R,N]: per-channel BN uses R = batch*H*W, N = C; the reference's literal
+ * batch_norm (moments over axis 0, no affine, eps 1e-3; distribute_tools.py:168-180) uses R = batch, N = H*W*C. */
+int dtf_bn_stats(const void* x, float* stats, long long R, int N, void* stream);
+int dtf_bn_finalize(const float* stats, const float* gamma, const float* beta, float* mean, float* rstd, float* scale,
+                    float* shift, float* run_mean, float* run_var, int N, long long R, float eps, float momentum,
+                    void* stream);
+int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma, const float* beta, float* scale,
+                float* shift, int N, float eps, void* stream);
+int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift, long long R, int N,
+                 int relu, void* stream);
+int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* sums, const float* mean,
+                      const float* rstd, long long R, int N, int relu, void* stream);
+int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* sums, const float* mean, const float* rstd,
+                     const float* gamma, long long R, int N, void* stream);
+
+/* pool (distribute_tools.py:160-165): max / avg, TF SAME semantics via explicit top/left padding. */
+int dtf_pool_fwd(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
+                 int pt, int pl, int is_max, void* stream);
+int dtf_pool_bwd(const void* x, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW, int kh,
+                 int kw, int sh, int sw, int pt, int pl, int is_max, void* stream);
+
+/* norm / tf.nn.lrn (distribute_tools.py:183-187): y = x / (bias + alpha * sum_{|j-c|<=radius} x_j^2)^beta. */
+int dtf_lrn_fwd(const void* x, void* y, long long pixels, int C, int radius, float bias, float alpha, float beta,
+                void* stream);
+int dtf_lrn_bwd(const void* x, const void* dy, void* dx, long long pixels, int C, int radius, float bias, float alpha,
+                float beta, void* stream);
+
+/* Fused loss forward+backward (Loss.loss implementations for distribute_tower.py:60-76). `scratch` is global
+ * memory provided by the caller: 1 + B floats (softmax_xent) or 1 + dtf_loss_scratch_blocks() floats (mse, l2).
+ * Word 0 must be zero before the first call; every call leaves it zero. dlogits / dpred may be NULL. */
+int dtf_loss_scratch_blocks(void);
+int dtf_softmax_xent(const void* logits, const long long* labels, void* dlogits, float* loss, float* scratch, int B,
+                     int C, float gscale, int is_bf16, void* stream);
+int dtf_mse(const void* pred, const void* target, void* dpred, float* loss, float* scratch, long long n, float gscale,
+            int is_bf16, void* stream);
+/* out = 0.5 * scale * sum(w^2): tf.nn.l2_loss weight-decay term (distribute_tools.py:63-65). */
+int dtf_l2_loss(const float* w, float* out, float* scratch, long long n, float scale, void* stream);
+int dtf_top1_hits(const void* logits, const long long* labels, unsigned int* hits, int B, int C, int is_bf16,
+                  void* stream);
+
+/* Optimizer apply on a flat arena (distribute.py:26,112; distribute_train.py:151-158). kind 0 SGD, 1 momentum,
+ * 2 Adam. g is multiplied by gscale; wd*p is added to it; the bf16 shadow (may be NULL) receives the new weights. */
+int dtf_optim_step(int kind, float* p, const float* g, float* m, float* v, void* shadow, long long n, float lr,
+                   float b1, float b2, float eps, float wd, float gscale, long long step, void* stream);
+/* Batched per-tap transpose [T,Ci,Co] -> [T,Co,Ci] of bf16 filters (second shadow used by dgrad / deconv). */
+int dtf_tap_transpose(const void* src, void* dst, const void* descs_dev, int ndesc, int total_tiles, void* stream);
+/* Philox-4x32-10 initialisers: kind 0 constant a, 1 uniform [a,b), 2 normal(a,b), 3 truncated normal(a,b) |z|<=2
+ * (tf.truncated_normal_initializer / xavier / constant, distribute_tools.py:62,100,103,135,200,203). */
+int dtf_init(float* out, long long n, int kind, float a, float b, unsigned long long seed,
+             unsigned long long stream_id, void* stream);
+int dtf_fill_u32(void* p, long long n, unsigned int v, void* stream);
+
+/* ---- peer-memory collectives (csrc/comm.cu) ------------------------------------------------------------------- */
+
+int dtf_comm_flag_page_bytes(void);
+int dtf_comm_max_blocks(void);
+int dtf_comm_heap_alloc(size_t bytes, void** ptr_out, void* handle_out64);
+int dtf_comm_heap_free(void* ptr);
+int dtf_comm_create(int rank, int world, void* local_heap, size_t heap_bytes, const void* handles, void** comm_out);
+int dtf_comm_create_local(int rank, int world, void* const* heaps, size_t heap_bytes, void** comm_out);
+int dtf_comm_destroy(void* comm);
+void* dtf_comm_peer_ptr(void* comm, int r);
+
+/* K-AR: one-shot allreduce of grad[start, start+count) (heap offset grad_off) fused with x gscale and the optimizer
+ * update of the local replica. Replaces Tower.average_gradients + apply (distribute_tower.py:78-114). With
+ * master == NULL the averaged gradient is written to avg_out instead. */
+int dtf_comm_allreduce_optim(void* comm, size_t grad_off, long long start, long long count, int kind, float lr,
+                             float b1, float b2, float eps, float wd, float gscale, long long step, float* master,
+                             float* m, float* v, void* shadow, float* avg_out, int blocks, void* stream);
+/* K-RS-OPT: reduce-scatter into the owner shard fused with the owner-side optimizer, then all-gather of the new
+ * bf16 weights (and optionally fp32 masters) by peer stores. Replaces the worker->ps push, ps-side apply and
+ * ps->worker pull of SyncReplicasOptimizer / replica_device_setter (distribute_train.py:109-110,146-158). */
+int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long* bounds, int kind, float lr, float b1, float b2,
+                         float eps, float wd, float gscale, long long step, float* master, float* m, float* v,
+                         size_t shadow_off, size_t master_off, int blocks, void* stream);
+int dtf_comm_allgather_slices(void* comm, size_t buf_off, const long long* bounds16, int blocks, void* stream);
+/* K-ASYNC-PUSH / owner apply: asynchronous parameter-server mode (extension; the reference is sync-only,
+ * distribute_train.py:151). */
+int dtf_comm_async_push(void* comm, size_t grad_off, size_t mailbox_off, long long slice_cap, const long long* bounds,
+                        unsigned int version, int blocks, void* stream);
+int dtf_comm_async_apply(void* comm, size_t mailbox_off, long long slice_cap, const long long* bounds, int kind,
+                         float lr, float b1, float b2, float eps, float wd, float gscale, long long step,
+                         float* master, float* m, float* v, size_t shadow_off, unsigned int* applied_out_dev,
+                         int blocks, void* stream);
+/* Device-side barrier / liveness (token queue, done queue, init handshake: distribute_train.py:43-46,86-90,160-167). */
+int dtf_comm_barrier(void* comm, void* stream);
+int dtf_comm_heartbeat(void* comm, unsigned int beat, unsigned int* seen_out_dev, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTF_B200_H_ */
