@@ -73,3 +73,189 @@ def conv_wgrad(x, dy, KH, KW, stride=1, out=None):
         out = torch.zeros((KH * KW * C, Co), device=x.device, dtype=torch.float32)
     _lib.call("dtf_conv_wgrad_bf16", x, dy, out, n, H, W, C, OH, OW, KH, KW, Co, stride, pt, pl, _sp())
     return out
+
+
+# ------------------------------------------------------------------------------------------------ memory-bound ops
+def convert_input(src, c_pad=None, scale=1.0, shift=0.0):
+    """[..., C] fp32/uint8 -> [..., Cpad] bf16 (normalise + pad channels to a multiple of 8)."""
+    C = src.shape[-1]
+    if c_pad is None:
+        c_pad = (C + 7) // 8 * 8
+    src = src.contiguous()
+    out = torch.empty(src.shape[:-1] + (c_pad,), device=src.device, dtype=bf16)
+    _lib.call("dtf_convert_input", src, out, src.numel() // C, C, c_pad, scale, shift,
+              1 if src.dtype == torch.uint8 else 0, _sp())
+    return out
+
+
+def relu(x):
+    y = torch.empty_like(x)
+    _lib.call("dtf_relu_fwd", x, y, x.numel(), _sp())
+    return y
+
+
+def relu_bwd(dy, y):
+    dx = torch.empty_like(dy)
+    _lib.call("dtf_relu_bwd", dy, y, dx, dy.numel(), _sp())
+    return dx
+
+
+def add(a, b, relu=False):
+    z = torch.empty_like(a)
+    _lib.call("dtf_add", a, b, z, a.numel(), 1 if relu else 0, _sp())
+    return z
+
+
+def bias_grad(dy2d, out=None):
+    R, N = dy2d.shape
+    if out is None:
+        out = torch.zeros(N, device=dy2d.device, dtype=torch.float32)
+    _lib.call("dtf_bias_grad", dy2d, out, R, N, _sp())
+    return out
+
+
+def relu_bwd_bias_grad(dy2d, y2d, db=None):
+    R, N = dy2d.shape
+    if db is None:
+        db = torch.zeros(N, device=dy2d.device, dtype=torch.float32)
+    dz = torch.empty_like(dy2d)
+    _lib.call("dtf_relu_bwd_bias_grad", dy2d, y2d, dz, db, R, N, _sp())
+    return dz, db
+
+
+def pool_geometry(H, W, k, s):
+    OH, pt = same_pad(H, k[0], s[0])
+    OW, pl = same_pad(W, k[1], s[1])
+    return OH, OW, pt, pl
+
+
+def pool_fwd(x, k=(2, 2), s=(2, 2), is_max=True):
+    n, H, W, C = x.shape
+    OH, OW, pt, pl = pool_geometry(H, W, k, s)
+    y = torch.empty((n, OH, OW, C), device=x.device, dtype=bf16)
+    _lib.call("dtf_pool_fwd", x, y, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl, 1 if is_max else 0, _sp())
+    return y
+
+
+def pool_bwd(x, dy, k=(2, 2), s=(2, 2), is_max=True):
+    n, H, W, C = x.shape
+    OH, OW, pt, pl = pool_geometry(H, W, k, s)
+    dx = torch.empty_like(x)
+    _lib.call("dtf_pool_bwd", x, dy, dx, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl, 1 if is_max else 0, _sp())
+    return dx
+
+
+def lrn_fwd(x, radius=4, bias=1.0, alpha=0.001 / 9.0, beta=0.75):
+    y = torch.empty_like(x)
+    C = x.shape[-1]
+    _lib.call("dtf_lrn_fwd", x, y, x.numel() // C, C, radius, bias, alpha, beta, _sp())
+    return y
+
+
+def lrn_bwd(x, dy, radius=4, bias=1.0, alpha=0.001 / 9.0, beta=0.75):
+    dx = torch.empty_like(x)
+    C = x.shape[-1]
+    _lib.call("dtf_lrn_bwd", x, dy, dx, x.numel() // C, C, radius, bias, alpha, beta, _sp())
+    return dx
+
+
+def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, res=None, relu=False):
+    """Training-mode batch norm over rows of x2d [R, N]. Returns (y, mean, rstd)."""
+    R, N = x2d.shape
+    dev = x2d.device
+    stats = torch.zeros(2, N, device=dev, dtype=torch.float32)
+    _lib.call("dtf_bn_stats", x2d, stats, R, N, _sp())
+    mean = torch.empty(N, device=dev, dtype=torch.float32)
+    rstd = torch.empty_like(mean)
+    scale = torch.empty_like(mean)
+    shift = torch.empty_like(mean)
+    _lib.call("dtf_bn_finalize", stats, gamma, beta, mean, rstd, scale, shift, run_mean, run_var, N, R, eps, momentum,
+              _sp())
+    y = torch.empty_like(x2d)
+    _lib.call("dtf_bn_apply", x2d, res, y, scale, shift, R, N, 1 if relu else 0, _sp())
+    return y, mean, rstd
+
+
+def bn_eval_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, res=None, relu=False):
+    R, N = x2d.shape
+    scale = torch.empty(N, device=x2d.device, dtype=torch.float32)
+    shift = torch.empty_like(scale)
+    _lib.call("dtf_bn_fold", run_mean, run_var, gamma, beta, scale, shift, N, eps, _sp())
+    y = torch.empty_like(x2d)
+    _lib.call("dtf_bn_apply", x2d, res, y, scale, shift, R, N, 1 if relu else 0, _sp())
+    return y
+
+
+def bn_bwd(dy2d, y2d, x2d, mean, rstd, gamma, relu=False):
+    """Returns (dx, dz, dgamma, dbeta); dz = masked upstream gradient (also the residual-branch gradient)."""
+    R, N = x2d.shape
+    sums = torch.zeros(2, N, device=x2d.device, dtype=torch.float32)
+    dz = torch.empty_like(dy2d) if relu else dy2d
+    _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if relu else None, x2d, dz if relu else None, sums, mean, rstd, R, N,
+              1 if relu else 0, _sp())
+    dx = torch.empty_like(x2d)
+    _lib.call("dtf_bn_bwd_apply", dz, x2d, dx, sums, mean, rstd, gamma, R, N, _sp())
+    return dx, dz, sums[1], sums[0]
+
+
+_scratch = {}
+
+
+def loss_scratch(device, nfloats):
+    """Per-device zero-initialised scratch for the loss kernels (word 0 is the arrival counter)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device())
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nfloats:
+        buf = torch.zeros(max(nfloats, 1 + _lib.lib().dtf_loss_scratch_blocks(), 65537), device=device,
+                          dtype=torch.float32)
+        _scratch[key] = buf
+    return buf
+
+
+def softmax_xent(logits, labels, gscale=1.0, want_grad=True):
+    """Fused mean softmax cross-entropy + gradient. logits [B,C] bf16/fp32; labels int64 [B]."""
+    B, C = logits.shape
+    logits = logits.contiguous()
+    loss = torch.empty(1, device=logits.device, dtype=torch.float32)
+    dl = torch.empty_like(logits) if want_grad else None
+    _lib.call("dtf_softmax_xent", logits, labels, dl, loss, loss_scratch(logits.device, 1 + B), B, C, gscale,
+              1 if logits.dtype == bf16 else 0, _sp())
+    return loss, dl
+
+
+def mse(pred, target, gscale=1.0, want_grad=True):
+    pred = pred.contiguous()
+    target = target.contiguous()
+    loss = torch.empty(1, device=pred.device, dtype=torch.float32)
+    dp = torch.empty_like(pred) if want_grad else None
+    _lib.call("dtf_mse", pred, target, dp, loss, loss_scratch(pred.device, 0), pred.numel(), gscale,
+              1 if pred.dtype == bf16 else 0, _sp())
+    return loss, dp
+
+
+def l2_loss(w, scale=1.0):
+    out = torch.empty(1, device=w.device, dtype=torch.float32)
+    _lib.call("dtf_l2_loss", w, out, loss_scratch(w.device, 0), w.numel(), scale, _sp())
+    return out
+
+
+def top1_hits(logits, labels):
+    hits = torch.zeros(1, device=logits.device, dtype=torch.int32)
+    B, C = logits.shape
+    _lib.call("dtf_top1_hits", logits.contiguous(), labels, hits, B, C, 1 if logits.dtype == bf16 else 0, _sp())
+    return hits
+
+
+OPTIM_KINDS = {"sgd": 0, "momentum": 1, "adam": 2}
+
+
+def optim_step(kind, p, g, m, v, shadow, lr, b1=0.9, b2=0.999, eps=1e-8, wd=0.0, gscale=1.0, step=1):
+    _lib.call("dtf_optim_step", OPTIM_KINDS[kind], p, g, m, v, shadow, p.numel(), lr, b1, b2, eps, wd, gscale, step,
+              _sp())
+
+
+def init_(t, kind, a=0.0, b=1.0, seed=0, stream_id=0):
+    """kind: 'constant' | 'uniform' | 'normal' | 'truncated_normal' (fp32 tensor, in place)."""
+    k = {"constant": 0, "uniform": 1, "normal": 2, "truncated_normal": 3}[kind]
+    _lib.call("dtf_init", t, t.numel(), k, a, b, seed, stream_id, _sp())
+    return t

@@ -1,0 +1,63 @@
+"""Numerics of the tcgen05 GEMM / implicit-GEMM convolution kernels vs PyTorch fp32 references."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def raw():
+    from distributed_tensorflow_framework_b200.ops import raw as r
+    return r
+
+
+def rnd(*shape):
+    return torch.randn(*shape, device="cuda").to(torch.bfloat16)
+
+
+def close(got, ref, tol=2e-2):
+    got, ref = got.float(), ref.float()
+    assert not torch.isnan(got).any()
+    err = (got - ref).abs().max().item()
+    assert err / (ref.abs().max().item() + 1e-6) < tol
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (200, 192, 136), (128, 384, 4096), (1024, 64, 576), (128, 10, 192),
+                                   (4096, 256, 128)])
+def test_gemm(raw, M, N, K):
+    a, b, bias = rnd(M, K), rnd(K, N), torch.randn(N, device="cuda")
+    ref = a.float() @ b.float()
+    close(raw.gemm(a, b), ref)
+    close(raw.gemm(a, b, bias, relu=True, out_fp32=True), torch.relu(ref + bias), 1e-4)
+    at = a.t().contiguous()
+    close(raw.gemm(at, b, a_transposed=True), ref)
+    acc = torch.zeros(M, N, device="cuda")
+    raw.gemm(at, b, a_transposed=True, out=acc, accumulate=True)
+    close(acc, ref, 1e-4)
+
+
+CONVS = [(2, 16, 16, 64, 64, 3, 3, 1), (4, 32, 32, 8, 64, 5, 5, 1), (2, 28, 28, 128, 256, 3, 3, 2),
+         (2, 14, 14, 256, 512, 1, 1, 1), (2, 56, 56, 64, 128, 1, 1, 2), (2, 30, 30, 16, 32, 7, 7, 2),
+         (3, 17, 19, 32, 64, 3, 3, 2)]
+
+
+@pytest.mark.parametrize("n,H,W,Ci,Co,KH,KW,s", CONVS)
+def test_conv_family(raw, n, H, W, Ci, Co, KH, KW, s):
+    x = rnd(n, H, W, Ci)
+    w = (torch.randn(KH, KW, Ci, Co, device="cuda") * 0.05).to(torch.bfloat16)
+    bias = torch.randn(Co, device="cuda")
+    xf = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wf = w.float().permute(3, 2, 0, 1).requires_grad_(True)
+    OH, pt = raw.same_pad(H, KH, s)
+    OW, pl = raw.same_pad(W, KW, s)
+    pb = max((OH - 1) * s + KH - H, 0) - pt
+    pr = max((OW - 1) * s + KW - W, 0) - pl
+    yref = F.conv2d(F.pad(xf, (pl, pr, pt, pb)), wf, stride=s)
+    y = raw.conv_fprop(x, w.reshape(KH * KW * Ci, Co), bias, KH, KW, s, relu=True)
+    close(y, torch.relu(yref + bias.view(1, -1, 1, 1)).permute(0, 2, 3, 1))
+    dy = rnd(n, OH, OW, Co)
+    yref.backward(dy.float().permute(0, 3, 1, 2))
+    w_t = w.permute(0, 1, 3, 2).contiguous().reshape(KH * KW * Co, Ci)
+    close(raw.conv_dgrad(dy, w_t, (H, W), KH, KW, s), xf.grad.permute(0, 2, 3, 1))
+    close(raw.conv_wgrad(x, dy, KH, KW, s).view(KH, KW, Ci, Co), wf.grad.permute(2, 3, 1, 0), 3e-2)
