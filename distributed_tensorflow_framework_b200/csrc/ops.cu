@@ -945,3 +945,10 @@ extern "C" int dtf_fill_u32(void* p, long long n, unsigned int v, void* stream) 
   fill_u32_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>((uint32_t*)p, n, v);
   return DTF_CHECK_LAUNCH();
 }
+
+// 0 = not capturing, 1 = capturing, 2 = capture invalidated, -1 = query failed (debug aid for CUDA-graph capture)
+extern "C" int dtf_stream_capture_status(void* stream) {
+  cudaStreamCaptureStatus st;
+  if (cudaStreamIsCapturing(ST(stream), &st) != cudaSuccess) return -1;
+  return (int)st;
+}

@@ -1,0 +1,338 @@
+"""torch.autograd.Function wrappers around the sm_100a kernels (CUDA path only; the CPU path uses plain torch ops).
+
+Parameters enter a Function through their bf16 shadow leaf (requires_grad=True) so that autograd schedules the
+backward even for the first layer; the weight gradient is NOT returned to autograd: the wgrad / bias-grad kernels
+accumulate straight into the fp32 gradient arena (`Variable.grad`), then the store is told that the gradient is
+ready so the engine can start the bucket's collective while backward continues (replaces
+optimizer.compute_gradients of /root/reference/distribute_tower.py:26-27).
+"""
+import torch
+
+from ..ops import raw
+from . import variables as V
+
+bf16 = torch.bfloat16
+
+
+def _store_of(var):
+    return getattr(var, "_store", None) or V.default_store()
+
+
+def _ready(var):
+    st = getattr(var, "_store", None)
+    if st is not None:
+        st.notify_grad_ready(var)
+
+
+class ConvertInputFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, c_pad, scale, shift):
+        return raw.convert_input(x, c_pad, scale, shift)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return None, None, None, None
+
+
+def convert_input(x, c_pad=None, scale=1.0, shift=0.0):
+    return ConvertInputFn.apply(x, c_pad, scale, shift)
+
+
+class ConvFn(torch.autograd.Function):
+    """conv2d(SAME) + bias (+ ReLU) on the implicit-GEMM tcgen05 kernel."""
+
+    @staticmethod
+    def forward(ctx, x, w_shadow, b_shadow, wvar, bvar, stride, relu):
+        KH, KW, Ci, Co = wvar.store_shape
+        w2d = w_shadow.detach().view(KH * KW * Ci, Co)
+        bias = bvar.master if bvar is not None else None
+        y = raw.conv_fprop(x, w2d, bias, KH, KW, stride, relu=relu)
+        ctx.wvar, ctx.bvar, ctx.stride, ctx.relu = wvar, bvar, stride, relu
+        ctx.save_for_backward(x, y if relu else None)
+        ctx.x_needs_grad = x.requires_grad
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y = ctx.saved_tensors
+        wvar, bvar = ctx.wvar, ctx.bvar
+        KH, KW, Ci, Co = wvar.store_shape
+        dy = dy.contiguous()
+        n, OH, OW, _ = dy.shape
+        dy2 = dy.view(-1, Co)
+        if ctx.relu:
+            if bvar is not None:
+                dz2, _ = raw.relu_bwd_bias_grad(dy2, y.view(-1, Co), bvar.grad)
+            else:
+                dz2 = raw.relu_bwd(dy2, y.view(-1, Co))
+        else:
+            dz2 = dy2
+            if bvar is not None:
+                raw.bias_grad(dy2, bvar.grad)
+        dz = dz2.view(n, OH, OW, Co)
+        raw.conv_wgrad(x, dz, KH, KW, ctx.stride, out=wvar.grad.view(KH * KW * Ci, Co))
+        _ready(wvar)
+        if bvar is not None:
+            _ready(bvar)
+        dx = None
+        if ctx.x_needs_grad:
+            dx = raw.conv_dgrad(dz, wvar.shadow_t.view(KH * KW * Co, Ci), (x.shape[1], x.shape[2]), KH, KW, ctx.stride)
+        return dx, None, None, None, None, None, None
+
+
+def conv2d(x, wvar, bvar, stride=1, relu=False):
+    return ConvFn.apply(x, wvar.shadow, bvar.shadow if bvar is not None else None, wvar, bvar, stride, relu)
+
+
+class DeconvFn(torch.autograd.Function):
+    """conv2d_transpose(SAME): forward is the data-gradient GEMM; filter [KH,KW,Cout,Cin] (TF layout)."""
+
+    @staticmethod
+    def forward(ctx, x, w_shadow, wvar, out_hw, stride):
+        KH, KW, Cout, Cin = wvar.store_shape
+        y = raw.conv_dgrad(x, wvar.shadow_t.view(KH * KW * Cin, Cout), out_hw, KH, KW, stride)
+        ctx.wvar, ctx.stride = wvar, stride
+        ctx.save_for_backward(x)
+        ctx.x_needs_grad = x.requires_grad
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        wvar = ctx.wvar
+        KH, KW, Cout, Cin = wvar.store_shape
+        dy = dy.contiguous()
+        # dW[kh,kw,co,ci] = sum_p dy[p*s - pad + k, co] * x[p, ci]: the wgrad kernel with (dy, x) in the roles (x, dy)
+        raw.conv_wgrad(dy, x, KH, KW, ctx.stride, out=wvar.grad.view(KH * KW * Cout, Cin))
+        _ready(wvar)
+        dx = None
+        if ctx.x_needs_grad:
+            dx = raw.conv_fprop(dy, wvar.shadow.detach().view(KH * KW * Cout, Cin), None, KH, KW, ctx.stride)
+        return dx, None, None, None, None
+
+
+def conv2d_transpose(x, wvar, out_hw, stride=1):
+    return DeconvFn.apply(x, wvar.shadow, wvar, tuple(out_hw), stride)
+
+
+class LinearFn(torch.autograd.Function):
+    """act(x @ W + b), W stored [in, out] (TF FC_layer layout)."""
+
+    @staticmethod
+    def forward(ctx, x, w_shadow, b_shadow, wvar, bvar, relu, out_fp32):
+        w = w_shadow.detach()
+        y = raw.gemm(x, w, bvar.master if bvar is not None else None, relu=relu, out_fp32=out_fp32)
+        ctx.wvar, ctx.bvar, ctx.relu = wvar, bvar, relu
+        ctx.save_for_backward(x, y if relu else None)
+        ctx.x_needs_grad = x.requires_grad
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y = ctx.saved_tensors
+        wvar, bvar = ctx.wvar, ctx.bvar
+        dy = dy.contiguous()
+        if dy.dtype != bf16:
+            dy = dy.to(bf16)
+        N = dy.shape[1]
+        if N % 8 == 0:
+            if ctx.relu:
+                if bvar is not None:
+                    dz, _ = raw.relu_bwd_bias_grad(dy, y, bvar.grad)
+                else:
+                    dz = raw.relu_bwd(dy, y)
+            else:
+                dz = dy
+                if bvar is not None:
+                    raw.bias_grad(dy, bvar.grad)
+        else:  # tiny, unaligned heads (e.g. 10 logits): plain torch elementwise is fine here
+            dz = dy * (y > 0) if ctx.relu else dy
+            if bvar is not None:
+                bvar.grad.add_(dz.float().sum(0))
+        raw.gemm(x, dz, a_transposed=True, out=wvar.grad, accumulate=True)  # dW = x^T dz
+        _ready(wvar)
+        if bvar is not None:
+            _ready(bvar)
+        dx = None
+        if ctx.x_needs_grad:
+            dx = raw.gemm(dz, wvar.shadow_t)  # dz @ W^T, W^T stored [out, in]
+        return dx, None, None, None, None, None, None
+
+
+def linear(x, wvar, bvar, relu=False, out_fp32=False):
+    return LinearFn.apply(x, wvar.shadow, bvar.shadow if bvar is not None else None, wvar, bvar, relu, out_fp32)
+
+
+class PoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, s, is_max):
+        y = raw.pool_fwd(x, k, s, is_max)
+        ctx.k, ctx.s, ctx.is_max = k, s, is_max
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        return raw.pool_bwd(x, dy.contiguous(), ctx.k, ctx.s, ctx.is_max), None, None, None
+
+
+def pool2d(x, k=(2, 2), s=(2, 2), is_max=True):
+    return PoolFn.apply(x, tuple(k), tuple(s), is_max)
+
+
+class LRNFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, radius, bias, alpha, beta):
+        ctx.args = (radius, bias, alpha, beta)
+        ctx.save_for_backward(x)
+        return raw.lrn_fwd(x, radius, bias, alpha, beta)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        return raw.lrn_bwd(x, dy.contiguous(), *ctx.args), None, None, None, None
+
+
+def lrn(x, radius=4, bias=1.0, alpha=0.001 / 9.0, beta=0.75):
+    return LRNFn.apply(x, radius, bias, alpha, beta)
+
+
+class ReLUFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = raw.relu(x)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return raw.relu_bwd(dy.contiguous(), y)
+
+
+def relu(x):
+    return ReLUFn.apply(x)
+
+
+class AddFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b, relu):
+        y = raw.add(a, b, relu)
+        ctx.relu = relu
+        if relu:
+            ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy.contiguous()
+        if ctx.relu:
+            (y,) = ctx.saved_tensors
+            dy = raw.relu_bwd(dy, y)
+        return dy, dy, None
+
+
+def add(a, b, relu=False):
+    return AddFn.apply(a, b, relu)
+
+
+class BatchNormFn(torch.autograd.Function):
+    """Training-mode batch norm over the rows of x viewed as [R, N] (+ residual, + ReLU)."""
+
+    @staticmethod
+    def forward(ctx, x, res, g_shadow, gvar, bvar, run_mean, run_var, rows, eps, momentum, relu):
+        shape = x.shape
+        x2 = x.reshape(rows, -1)
+        res2 = res.reshape(rows, -1) if res is not None else None
+        gamma = gvar.master if gvar is not None else None
+        beta = bvar.master if bvar is not None else None
+        y2, mean, rstd = raw.bn_train_fwd(x2, gamma, beta, run_mean, run_var, eps, momentum, res2, relu)
+        ctx.gvar, ctx.bvar, ctx.relu, ctx.rows, ctx.has_res = gvar, bvar, relu, rows, res is not None
+        ctx.save_for_backward(x2, y2 if relu else None, mean, rstd)
+        return y2.view(shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, y2, mean, rstd = ctx.saved_tensors
+        gvar, bvar = ctx.gvar, ctx.bvar
+        shape = dy.shape
+        dy2 = dy.contiguous().view(ctx.rows, -1)
+        dx2, dz2, dgamma, dbeta = raw.bn_bwd(dy2, y2, x2, mean, rstd, gvar.master if gvar is not None else None,
+                                             ctx.relu)
+        if gvar is not None:
+            gvar.grad.add_(dgamma)
+            _ready(gvar)
+        if bvar is not None:
+            bvar.grad.add_(dbeta)
+            _ready(bvar)
+        dres = dz2.view(shape) if ctx.has_res else None
+        return dx2.view(shape), dres, None, None, None, None, None, None, None, None, None
+
+
+def batch_norm_train(x, rows, gvar=None, bvar=None, run_mean=None, run_var=None, eps=1e-3, momentum=0.1, res=None,
+                     relu=False):
+    return BatchNormFn.apply(x, res, gvar.shadow if gvar is not None else None, gvar, bvar, run_mean, run_var, rows,
+                             eps, momentum, relu)
+
+
+def batch_norm_eval(x, rows, gvar, bvar, run_mean, run_var, eps=1e-3, res=None, relu=False):
+    shape = x.shape
+    y = raw.bn_eval_fwd(x.reshape(rows, -1), gvar.master if gvar is not None else None,
+                        bvar.master if bvar is not None else None, run_mean, run_var, eps,
+                        res.reshape(rows, -1) if res is not None else None, relu)
+    return y.view(shape)
+
+
+class SoftmaxXentFn(torch.autograd.Function):
+    """Fused mean sparse softmax cross-entropy: forward also produces dlogits (scaled in backward)."""
+
+    @staticmethod
+    def forward(ctx, logits, labels):
+        loss, dl = raw.softmax_xent(logits, labels, 1.0, want_grad=True)
+        ctx.save_for_backward(dl)
+        return loss.view(())
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl * g.to(dl.dtype), None
+
+
+def softmax_xent(logits, labels):
+    return SoftmaxXentFn.apply(logits, labels)
+
+
+class MSEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, target):
+        loss, dp = raw.mse(pred, target, 1.0, want_grad=True)
+        ctx.save_for_backward(dp)
+        return loss.view(())
+
+    @staticmethod
+    def backward(ctx, g):
+        (dp,) = ctx.saved_tensors
+        return dp * g.to(dp.dtype), None
+
+
+def mse(pred, target):
+    return MSEFn.apply(pred, target)
+
+
+class L2Fn(torch.autograd.Function):
+    """wd * sum(w^2)/2 on the fp32 master (tf.nn.l2_loss weight-decay term, distribute_tools.py:63-65)."""
+
+    @staticmethod
+    def forward(ctx, w_shadow, wvar, wd):
+        ctx.wvar, ctx.wd = wvar, wd
+        return raw.l2_loss(wvar.master, wd).view(())
+
+    @staticmethod
+    def backward(ctx, g):
+        ctx.wvar.grad.add_(ctx.wvar.master * (g.float() * float(ctx.wd)))
+        return None, None, None
+
+
+def l2_loss(wvar, wd):
+    return L2Fn.apply(wvar.shadow, wvar, wd)

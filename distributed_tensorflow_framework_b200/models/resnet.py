@@ -1,0 +1,72 @@
+"""ResNet-18 / ResNet-50 (v1.5: stride on the 3x3 of the bottleneck) on the framework's layer library, NHWC,
+224x224x3 inputs -- BASELINE.json configs[2] (ResNet-50 bf16 sync data-parallel) and [4] (ResNet-18 async ps).
+The reference ships no ResNet; these are example plugins in its Model API (/root/reference/distribute_model.py:13-22)."""
+from ..engine import layers as L
+from ..engine.variables import variable_scope
+from ..plugins.input import SyntheticDataLoader
+from ..plugins.model import Model
+
+
+def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None):
+    y = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1])
+    return L.batch_norm_channel(name + "/bn", y, relu=relu, residual=residual)
+
+
+def _basic_block(name, x, cin, cout, stride):
+    with variable_scope(name):
+        shortcut = x
+        if stride != 1 or cin != cout:
+            shortcut = _conv_bn("shortcut", x, cin, cout, 1, stride, relu=False)
+        y = _conv_bn("conv1", x, cin, cout, 3, stride)
+        return _conv_bn("conv2", y, cout, cout, 3, 1, relu=True, residual=shortcut)
+
+
+def _bottleneck(name, x, cin, mid, stride):
+    cout = mid * 4
+    with variable_scope(name):
+        shortcut = x
+        if stride != 1 or cin != cout:
+            shortcut = _conv_bn("shortcut", x, cin, cout, 1, stride, relu=False)
+        y = _conv_bn("conv1", x, cin, mid, 1, 1)
+        y = _conv_bn("conv2", y, mid, mid, 3, stride)
+        return _conv_bn("conv3", y, mid, cout, 1, 1, relu=True, residual=shortcut)
+
+
+class _ResNet(Model):
+    num_classes = 1000
+    blocks = (2, 2, 2, 2)
+    bottleneck = False
+
+    def inference(self, images, *args, **kwargs):
+        x = _conv_bn("conv1", images, 3, 64, 7, 2)
+        x = L.pool("pool1", x, kernel=[1, 3, 3, 1], stride=[1, 2, 2, 1])
+        cin = 64
+        for stage, n in enumerate(self.blocks):
+            width = 64 * (2 ** stage)
+            for b in range(n):
+                stride = 2 if (b == 0 and stage > 0) else 1
+                name = "stage%d/block%d" % (stage + 1, b)
+                if self.bottleneck:
+                    x = _bottleneck(name, x, cin, width, stride)
+                    cin = width * 4
+                else:
+                    x = _basic_block(name, x, cin, width, stride)
+                    cin = width
+        x = L.global_avg_pool(x)
+        return L.fc_nonacti("logits", x, self.num_classes)
+
+
+class ResNet18(_ResNet):
+    blocks = (2, 2, 2, 2)
+    bottleneck = False
+
+
+class ResNet50(_ResNet):
+    blocks = (3, 4, 6, 3)
+    bottleneck = True
+
+
+class ImageNetSyntheticLoader(SyntheticDataLoader):
+    image_shape = (224, 224, 3)
+    num_classes = 1000
+    pool_batches = 2

@@ -1,0 +1,284 @@
+"""Python side of the peer-memory communication layer (csrc/comm.cu).
+
+* `SymmetricHeap`  -- one cudaMalloc'd heap per rank with identical layout everywhere; buffers are torch views at
+                      symmetric offsets, so a kernel can address a peer's copy as peer_base[r] + offset.
+* `Communicator`   -- exchanges CUDA IPC handles over the torch.distributed control plane (bootstrap only) and wraps
+                      the fused collectives: K-AR (allreduce+optimizer), K-RS-OPT (+all-gather by peer stores),
+                      async push/apply, device barrier, heartbeat.
+* `GradientEngine` -- binds a VariableStore to a communicator: arenas live in the heap, buckets of the gradient arena
+                      are reduced as soon as backward has produced them (on a side stream), fused with x1/N and the
+                      optimizer update.
+
+Replaces: cross-tower gather+mean (/root/reference/distribute_tower.py:78-114), SyncReplicasOptimizer push/apply/pull
+through the TF gRPC runtime (/root/reference/distribute_train.py:109-110,146-160) and the shared FIFOQueue barriers
+(/root/reference/distribute_train.py:43-46,86-90).
+"""
+import ctypes
+from typing import List, Optional
+
+import torch
+
+from ..ops import _lib
+
+_ALIGN = 256
+
+
+class _RawCuda(object):
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class SymmetricHeap(object):
+    def __init__(self, nbytes, device):
+        self.device = torch.device(device)
+        self.nbytes = int(nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+        ptr = ctypes.c_void_p()
+        self.handle = ctypes.create_string_buffer(64)
+        with torch.cuda.device(self.device):
+            _lib.call("dtf_comm_heap_alloc", self.nbytes, ctypes.byref(ptr), self.handle)
+        self.ptr = ptr.value
+        self._raw = _RawCuda(self.ptr, self.nbytes)
+        self.bytes = torch.as_tensor(self._raw, device=self.device)
+        self._top = _lib.lib().dtf_comm_flag_page_bytes()  # the flag page sits at offset 0
+        self.allocs = {}
+
+    def alloc(self, tag, numel, dtype):
+        """Bump allocation (deterministic => symmetric across ranks). Returns a zeroed flat tensor view."""
+        esize = torch.empty((), dtype=dtype).element_size()
+        off = (self._top + _ALIGN - 1) // _ALIGN * _ALIGN
+        nbytes = numel * esize
+        if off + nbytes > self.nbytes:
+            raise MemoryError("symmetric heap exhausted: need %d more bytes" % (off + nbytes - self.nbytes))
+        self._top = off + nbytes
+        self.allocs[tag] = (off, numel, dtype)
+        return self.bytes[off:off + nbytes].view(dtype)
+
+    def offset_of(self, tag):
+        return self.allocs[tag][0]
+
+    def free(self):
+        if self.ptr:
+            _lib.call("dtf_comm_heap_free", ctypes.c_void_p(self.ptr))
+            self.ptr = None
+
+
+class Communicator(object):
+    def __init__(self, heap: SymmetricHeap, rank: int, world: int, group=None, local_heaps: Optional[List] = None):
+        self.heap, self.rank, self.world = heap, rank, world
+        self.handle = ctypes.c_void_p()
+        self.stream = torch.cuda.Stream(device=heap.device)
+        self.blocks = 32
+        self._version = 0
+        if local_heaps is not None:  # single process driving several peer-enabled GPUs (tests)
+            arr = (ctypes.c_void_p * world)(*[h.ptr for h in local_heaps])
+            _lib.call("dtf_comm_create_local", rank, world, arr, heap.nbytes, ctypes.byref(self.handle))
+        else:
+            handles = bytes(heap.handle.raw)
+            if world > 1:
+                import torch.distributed as dist
+                gathered = [None] * world
+                dist.all_gather_object(gathered, handles, group=group)
+            else:
+                gathered = [handles]
+            blob = b"".join(gathered)
+            with torch.cuda.device(heap.device):
+                _lib.call("dtf_comm_create", rank, world, ctypes.c_void_p(heap.ptr), heap.nbytes, blob,
+                          ctypes.byref(self.handle))
+        self._snap = torch.zeros(8, device=heap.device, dtype=torch.int32)
+
+    def _s(self, stream=None):
+        return _lib.stream_ptr(stream)
+
+    @staticmethod
+    def _opt_args(opt, step, gscale):
+        from ..ops.raw import OPTIM_KINDS
+        return (OPTIM_KINDS[opt.kind], opt.learning_rate, opt.b1, opt.b2, opt.eps, opt.wd, gscale, step)
+
+    def allreduce_optim(self, grad_off, start, count, opt, step, master, m, v, shadow, gscale=None, stream=None):
+        """K-AR: grads[start:start+count) of every rank -> mean -> optimizer on the local replica."""
+        gscale = 1.0 / self.world if gscale is None else gscale
+        _lib.call("dtf_comm_allreduce_optim", self.handle, grad_off, start, count, *self._opt_args(opt, step, gscale),
+                  master, m, v, shadow, None, self.blocks, self._s(stream))
+
+    def allreduce_mean(self, grad_off, start, count, out, gscale=None, stream=None):
+        gscale = 1.0 / self.world if gscale is None else gscale
+        _lib.call("dtf_comm_allreduce_optim", self.handle, grad_off, start, count, 0, 0.0, 0.0, 0.0, 0.0, 0.0, gscale,
+                  1, None, None, None, None, out, self.blocks, self._s(stream))
+
+    def rs_optim_ag(self, grad_off, bounds, opt, step, master, m, v, shadow_off, master_off=None, gscale=None,
+                    stream=None):
+        """K-RS-OPT: reduce-scatter into the owner shard + owner update + all-gather of bf16 weights by stores."""
+        gscale = 1.0 / self.world if gscale is None else gscale
+        b = (ctypes.c_longlong * (self.world + 1))(*bounds)
+        _lib.call("dtf_comm_rs_optim_ag", self.handle, grad_off, b, *self._opt_args(opt, step, gscale), master, m, v,
+                  shadow_off, (1 << 64) - 1 if master_off is None else master_off, self.blocks, self._s(stream))
+
+    def allgather_slices(self, buf_off, bounds16, stream=None):
+        b = (ctypes.c_longlong * (self.world + 1))(*bounds16)
+        _lib.call("dtf_comm_allgather_slices", self.handle, buf_off, b, self.blocks, self._s(stream))
+
+    def async_push(self, grad_off, mailbox_off, slice_cap, bounds, stream=None):
+        self._version += 1
+        b = (ctypes.c_longlong * (self.world + 1))(*bounds)
+        _lib.call("dtf_comm_async_push", self.handle, grad_off, mailbox_off, slice_cap, b, self._version, self.blocks,
+                  self._s(stream))
+        return self._version
+
+    def async_apply(self, mailbox_off, slice_cap, bounds, opt, step, master, m, v, shadow_off, stream=None):
+        b = (ctypes.c_longlong * (self.world + 1))(*bounds)
+        _lib.call("dtf_comm_async_apply", self.handle, mailbox_off, slice_cap, b, *self._opt_args(opt, step, 1.0),
+                  master, m, v, shadow_off, self._snap, self.blocks, self._s(stream))
+        return self._snap
+
+    def barrier(self, stream=None):
+        _lib.call("dtf_comm_barrier", self.handle, self._s(stream))
+
+    def heartbeat(self, beat, stream=None):
+        seen = torch.zeros(8, device=self.heap.device, dtype=torch.int32)
+        _lib.call("dtf_comm_heartbeat", self.handle, beat, seen, self._s(stream))
+        return seen
+
+    def destroy(self):
+        if self.handle:
+            _lib.call("dtf_comm_destroy", self.handle)
+            self.handle = None
+
+
+class GradientEngine(object):
+    """Connects a finalized VariableStore to the fused gradient collectives.
+
+    algo: 'oneshot' (K-AR, replicated fp32 masters, bitwise-identical replicas), 'twoshot' (K-RS-OPT: each owner
+    updates its shard and pushes bf16 weights; parameter-server semantics), 'nccl' (baseline: ncclAllReduce +
+    separate optimizer kernel), 'local' (single replica: optimizer only), 'async' (K-ASYNC push/apply).
+    Buckets are contiguous ranges of the gradient arena in reverse layer order; a bucket's collective is enqueued
+    on the communication stream as soon as backward has produced all of its gradients.
+    """
+
+    def __init__(self, store, optimizer, rank=0, world=1, algo="auto", group=None, bucket_bytes=8 << 20,
+                 placement="bytes", heap_extra_bytes=0, overlap=True):
+        self.store, self.opt, self.rank, self.world, self.group = store, optimizer, rank, world, group
+        dev = store.device
+        n_est = sum((v.numel + 7) // 8 * 8 for v in store.trainable_variables())
+        if algo == "auto":
+            algo = "local" if world == 1 else ("oneshot" if n_est * 4 <= (16 << 20) else "twoshot")
+        self.algo = algo
+        self.overlap = overlap and algo in ("oneshot", "nccl")
+        self.comm = None
+        self.heap = None
+        use_heap = algo in ("oneshot", "twoshot", "async")
+        if use_heap:
+            mailbox = n_est * 4 * 1 if algo == "async" else 0
+            need = n_est * (4 + 4 + 2 + 2 + 4 + 4) + mailbox * max(world, 1) + (1 << 20) + heap_extra_bytes
+            self.heap = SymmetricHeap(need, dev)
+            store.finalize(allocator=self.heap.alloc, placement=placement, world=world, slots=optimizer.num_slots())
+            if algo == "async":
+                per = max(store.owner_bounds[i + 1] - store.owner_bounds[i] for i in range(world))
+                self.slice_cap = (per + 3) // 4 * 4
+                self.mailbox = self.heap.alloc("mailbox", self.slice_cap * world, torch.float32)
+            self.comm = Communicator(self.heap, rank, world, group)
+        else:
+            store.finalize(placement=placement, world=world, slots=optimizer.num_slots())
+        self.n = store.n_params
+        # buckets: contiguous [start, end) in arena order, flushed from the tail (last layers finish first)
+        per_bucket = max(bucket_bytes // 4, 1024)
+        tv = sorted(store.trainable_variables(), key=lambda v: v.offset)
+        self.buckets = []
+        cur_start, cur_vars = 0, []
+        for v in tv:
+            cur_vars.append(v)
+            end = v.offset + (v.numel + 7) // 8 * 8
+            if end - cur_start >= per_bucket:
+                self.buckets.append([cur_start, end, cur_vars])
+                cur_start, cur_vars = end, []
+        if cur_vars:
+            self.buckets.append([cur_start, self.n, cur_vars])
+        self._bucket_of = {}
+        for bi, (_, _, vs) in enumerate(self.buckets):
+            for v in vs:
+                self._bucket_of[v.name] = bi
+        self._pending = [0] * len(self.buckets)
+        self._launched = [False] * len(self.buckets)
+        self._step = 0
+        self.comm_stream = self.comm.stream if self.comm is not None else torch.cuda.Stream(device=dev)
+        if self.overlap:
+            store.grad_ready_hook = self._on_grad_ready
+        self.kernel_launches = 0
+
+    # ------------------------------------------------------------------ per-step protocol
+    def begin_step(self, step):
+        """Call before backward: zero the gradient arena and re-arm the buckets."""
+        self._step = step
+        self.store.zero_grads()
+        for bi, (_, _, vs) in enumerate(self.buckets):
+            self._pending[bi] = len(vs)
+            self._launched[bi] = False
+
+    def _on_grad_ready(self, var):
+        bi = self._bucket_of.get(var.name)
+        if bi is None or self._launched[bi]:
+            return
+        self._pending[bi] -= 1
+        if self._pending[bi] <= 0:
+            self._launch_bucket(bi)
+
+    def _launch_bucket(self, bi):
+        start, end, _ = self.buckets[bi]
+        self._launched[bi] = True
+        cur = torch.cuda.current_stream(self.store.device)
+        self.comm_stream.wait_stream(cur)
+        with torch.cuda.stream(self.comm_stream):
+            self._reduce_and_update(start, end - start)
+
+    def _reduce_and_update(self, start, count):
+        st, opt = self.store, self.opt
+        step = self._step
+        if self.algo == "oneshot":
+            self.comm.allreduce_optim(self.heap.offset_of("grad"), start, count, opt, step, st.master_arena,
+                                      st.slot_m, st.slot_v, st.shadow_arena, stream=self.comm_stream)
+        elif self.algo == "nccl":
+            import torch.distributed as dist
+            dist.all_reduce(st.grad_arena[start:start + count], group=self.group)
+            opt.apply_arena(st, step, 1.0 / self.world, start, count, refresh=False)
+        else:
+            raise RuntimeError(self.algo)
+
+    def finish_step(self):
+        """Call after backward: flush whatever has not been reduced yet, apply, refresh transposed shadows."""
+        st, opt = self.store, self.opt
+        step = self._step
+        cur = torch.cuda.current_stream(st.device)
+        if self.algo == "local":
+            opt.apply_arena(st, step, 1.0)
+            st.global_step = step
+            return
+        self.comm_stream.wait_stream(cur)
+        with torch.cuda.stream(self.comm_stream):
+            if self.algo in ("oneshot", "nccl"):
+                if self.overlap:
+                    for bi in range(len(self.buckets) - 1, -1, -1):
+                        if not self._launched[bi]:
+                            s, e, _ = self.buckets[bi]
+                            self._launched[bi] = True
+                            self._reduce_and_update(s, e - s)
+                else:
+                    self._reduce_and_update(0, self.n)
+            elif self.algo == "twoshot":
+                self.comm.rs_optim_ag(self.heap.offset_of("grad"), st.owner_bounds, opt, step, st.master_arena,
+                                      st.slot_m, st.slot_v, self.heap.offset_of("shadow"),
+                                      stream=self.comm_stream)
+            elif self.algo == "async":
+                self.comm.async_push(self.heap.offset_of("grad"), self.heap.offset_of("mailbox"), self.slice_cap,
+                                     st.owner_bounds, stream=self.comm_stream)
+                self.comm.async_apply(self.heap.offset_of("mailbox"), self.slice_cap, st.owner_bounds, opt, step,
+                                      st.master_arena, st.slot_m, st.slot_v, self.heap.offset_of("shadow"),
+                                      stream=self.comm_stream)
+            st.refresh_transposed_shadows()
+        cur.wait_stream(self.comm_stream)
+        st.global_step = step
+
+    def gather_masters(self):
+        """Make every rank's fp32 master arena complete (owner-sharded modes) -- used before checkpointing."""
+        if self.algo in ("twoshot", "async") and self.world > 1:
+            b16 = [b // 4 for b in self.store.owner_bounds]  # fp32 elements -> 16-byte units
+            self.comm.allgather_slices(self.heap.offset_of("master"), b16)
+            torch.cuda.current_stream().synchronize()

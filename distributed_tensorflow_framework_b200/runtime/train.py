@@ -1,0 +1,191 @@
+"""Train operator: parameter-server / worker roles, tower loop, synchronous (or async) replicas, monitored session.
+
+Parity: /root/reference/distribute_train.py:22-221 -- `Train.train(pre_fn, post_fn, init_fn, pre_process_fn,
+post_process_fn, parse_data_dir_fn, *args, **kwargs)` and `Train.run()`. Attributes are injected by the entry script
+(/root/reference/distribute.py:110-127): task_index, job_name, optimizer, server, cluster, data_loader, input_mode,
+batch_size, epoch_num, sample_number, model_dir, data_dir, net, loss, gpu_num.
+
+Behavioural fixes: `(raw, gt) = pre_process_fn(raw, gt, ...)` (Q7); the log line reports real
+seconds per batch (Q8); one shared global step (Q9); the placeholder queue is built once and every tower is fed
+(Q10); the ps exits on a timeout and workers signal the done queue on any stop (Q19).
+"""
+import os
+import time
+
+import torch
+
+from ..api import annotations
+from ..api import constants as constant
+from ..api import flags
+from ..api import log as logger
+from ..engine.trainer import Trainer
+from ..io.events import EventFileWriter
+from ..plugins import input as Input
+from . import hooks as H
+from .cluster import DoneQueue
+from .session import MonitoredTrainingSession, Saver, Scaffold
+from .sync_replicas import AsyncReplicasOptimizer, SyncReplicasOptimizer
+
+
+def _sync_mode():
+    m = (flags.FLAGS.sync_mode or "").lower()
+    if m:
+        return m
+    if not flags.FLAGS.sync_replicas:
+        return "async"
+    return "sync"
+
+
+@annotations.get_advice(pre_fn=None)
+class Train(object):
+    """Attributes injected by the IoC container: data_loader, input_mode, batch_size, epoch_num, sample_number,
+    model_dir, data_dir, net, optimizer, loss, gpu_num, cluster, server, job_name, task_index; optional advices
+    pre_fn, post_fn, pre_process_fn, post_process_fn, init_fn, parse_data_dir_fn."""
+
+    @staticmethod
+    def _create_done_queue(server, num_workers):
+        return DoneQueue(server, num_workers)
+
+    def _pick_device(self):
+        if self.job_name == "ps" or self.gpu_num == 0 or not torch.cuda.is_available():
+            return torch.device("cpu"), 1 if self.gpu_num == 0 else max(self.gpu_num, 1)
+        local = int(os.environ.get("LOCAL_RANK", self.task_index % max(torch.cuda.device_count(), 1)))
+        torch.cuda.set_device(local)
+        return torch.device("cuda", local), self.gpu_num
+
+    def _next_host_batch(self, name_queue, placeholder_queue):
+        if self.input_mode == Input.InputOptions.PLACEHOLDER:
+            return self.data_loader.load_placeholder_data(placeholder_queue)
+        return self.data_loader.load_train_batch(name_queue)
+
+    def train(self, pre_fn=None, post_fn=None, init_fn=None, pre_process_fn=None, post_process_fn=None,
+              parse_data_dir_fn=None, *args, **kwargs):
+        is_chief = self.task_index == 0
+        replicas_to_aggregate = flags.FLAGS.replicas_to_aggregate
+        total_step = self.epoch_num * (self.sample_number // self.batch_size)
+        num_workers = max(self.cluster.num_tasks("worker"), 1)
+        kill_ps_queue = Train._create_done_queue(self.server, num_workers)
+        data_dir = self.data_dir if parse_data_dir_fn is None else parse_data_dir_fn(self.data_dir)
+
+        # ---------------------------------------------------------------- parameter server role
+        if self.job_name == "ps":
+            # Parameters live on the owner shards of the worker GPUs; a ps process only keeps the reference's
+            # life cycle: block until every worker has signalled the done queue (with a timeout, Q19).
+            kill_ps_queue.wait_all(timeout_s=getattr(self, "ps_timeout_s", 24 * 3600))
+            return
+
+        # ---------------------------------------------------------------- worker role
+        device, num_devices = self._pick_device()
+        group = self.server.init_process_group() if num_workers > 1 else None
+        pre_train_result = None if pre_fn is None else pre_fn(args, kwargs)
+
+        mode = _sync_mode()
+        if replicas_to_aggregate is None:
+            replicas_to_aggregate = num_workers
+        if mode == "sync" and replicas_to_aggregate < num_workers:
+            mode = "backup"
+        algo = flags.FLAGS.comm_algo
+        if mode == "async" and device.type == "cuda" and num_workers > 1:
+            algo = "async"
+        elif device.type == "cuda" and num_workers > 1 and getattr(self, "ps_equivalent", False) and algo == "auto":
+            algo = "twoshot"
+        base_opt = self.optimizer
+        trainer = Trainer(self.net, self.loss, base_opt, device=device, rank=self.task_index, world=num_workers,
+                          group=group, gpu_num=num_devices, algo=algo, placement=flags.FLAGS.placement,
+                          use_cuda_graph=getattr(self, "use_cuda_graph", False), pre_process_fn=pre_process_fn,
+                          post_process_fn=post_process_fn, pre_train_result=pre_train_result,
+                          seed=getattr(self, "seed", 0))
+        self.trainer = trainer
+
+        # input pipeline (one logical pipeline per tower, like distribute_train.py:119-128)
+        name_queue = placeholder_queue = None
+        if self.input_mode == Input.InputOptions.TF_RECORD:
+            name_queue = Input.FilenameQueue([data_dir] if isinstance(data_dir, str) else list(data_dir), shuffle=True)
+        elif self.input_mode == Input.InputOptions.DATAPATHLOADER:
+            name_queue = self.data_loader.create_name_queue(data_dir)
+        elif self.input_mode == Input.InputOptions.PLACEHOLDER:
+            self.data_loader.load_train_batch()  # placeholder specs (informational)
+            placeholder_queue = self.data_loader.load_queue_for_placeholder(data_dir)  # built once (Q10)
+
+        first = [self._next_host_batch(name_queue, placeholder_queue) for _ in range(num_devices)]
+        trainer.build(first[0][0], first[0][1])
+        store = trainer.store
+
+        if mode == "async":
+            optimizer = AsyncReplicasOptimizer(base_opt, total_num_replicas=num_workers, engine=trainer.engine)
+        else:
+            optimizer = SyncReplicasOptimizer(base_opt, use_locking=False, replicas_to_aggregate=replicas_to_aggregate,
+                                              total_num_replicas=num_workers, name="sync_replicas",
+                                              engine=trainer.engine, group=group, server=self.server)
+        trainer.sync_optimizer = optimizer
+        sync_replicas_hook = optimizer.make_session_run_hook(is_chief)
+
+        if is_chief:
+            logger.info("Worker %d: Initializing session..." % self.task_index)
+        else:
+            logger.info("Worker %d: Waiting for session to be initialized..." % self.task_index)
+
+        writer = EventFileWriter(self.model_dir) if (is_chief and self.model_dir) else None
+        saver = Saver(store, base_opt, num_shards=1,
+                      gather_fn=trainer.engine.gather_masters if trainer.engine is not None else None)
+
+        def barrier():
+            if group is not None:
+                import torch.distributed as dist
+                dist.barrier(group=group)
+
+        session_hooks = [H.StopAtStepHook(last_step=total_step)]
+        if sync_replicas_hook is not None:
+            session_hooks.append(sync_replicas_hook)
+        session_hooks += list(getattr(self, "extra_hooks", []))
+        pending = {"batches": first}
+        state = {"loss": None}
+
+        def train_step():
+            batches = pending.pop("batches", None)
+            if batches is None:
+                batches = [self._next_host_batch(name_queue, placeholder_queue) for _ in range(num_devices)]
+            loss = trainer.step(batches)
+            state["loss"] = loss
+            return {"loss": loss, "summaries": trainer.last_summaries}
+
+        with MonitoredTrainingSession(master=self.server.target, is_chief=is_chief, checkpoint_dir=self.model_dir,
+                                      scaffold=Scaffold(init_op=None, init_fn=init_fn), hooks=session_hooks,
+                                      save_checkpoint_secs=flags.FLAGS.save_checkpoint_secs,
+                                      config={"allow_soft_placement": True, "log_device_placement": False},
+                                      stop_grace_period_secs=60, log_step_count_steps=100, store=store,
+                                      optimizer=base_opt, saver=saver, summary_writer=writer,
+                                      barrier_fn=barrier) as sess:
+            logger.info("Worker %d: Session initialization complete." % self.task_index)
+            self.session = sess
+            while not sess.should_stop():
+                if sess.global_step >= total_step:
+                    break
+                start = time.time()
+                values = sess.run(train_step)
+                step = sess.global_step
+                if step % 10 == 0:
+                    loss_value = float(values["loss"])  # device->host sync only on logging steps
+                    duration = time.time() - start
+                    num_examples_per_step = self.batch_size * max(self.gpu_num, 1)
+                    examples_per_sec = num_examples_per_step / max(duration, 1e-9)
+                    sec_per_batch = duration / max(self.gpu_num, 1)
+                    format_str = ("step %d, loss = %.8f (%.1f examples/sec; %.3f sec/batch)")
+                    logger.info(format_str % (step, loss_value, examples_per_sec, sec_per_batch))
+                if step >= total_step:
+                    break
+            self.final_loss = float(state["loss"]) if state["loss"] is not None else None
+            sess.close()
+        kill_ps_queue.enqueue()
+        logger.info("kill_ps_enqueue_op done....")
+        if writer is not None:
+            writer.close()
+
+        if post_fn is not None:
+            post_fn(args, kwargs)
+
+    def run(self):
+        g = lambda n: getattr(self, n, None)  # noqa: E731
+        self.train(pre_fn=g("pre_fn"), post_fn=g("post_fn"), pre_process_fn=g("pre_process_fn"),
+                   post_process_fn=g("post_process_fn"), init_fn=g("init_fn"),
+                   parse_data_dir_fn=g("parse_data_dir_fn"))

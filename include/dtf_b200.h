@@ -116,6 +116,8 @@ int dtf_tap_transpose(const void* src, void* dst, const void* descs_dev, int nde
 int dtf_init(float* out, long long n, int kind, float a, float b, unsigned long long seed,
              unsigned long long stream_id, void* stream);
 int dtf_fill_u32(void* p, long long n, unsigned int v, void* stream);
+/* 0 = not capturing, 1 = capturing, 2 = capture invalidated, -1 = query failed. */
+int dtf_stream_capture_status(void* stream);
 
 /* ---- peer-memory collectives (csrc/comm.cu) ------------------------------------------------------------------- */
 
