@@ -40,6 +40,7 @@ class Trainer(object):
         self._graph = None
         self._static_in = None
         self._loss_buf = None
+        self._graph_launches = 0
         self.last_summaries = {}
         self.last_logits = None
 
@@ -160,8 +161,11 @@ class Trainer(object):
             import torch.distributed as dist
             dist.barrier(group=self.group)
         self._graph = torch.cuda.CUDAGraph()
+        from ..ops import _lib
+        n0 = _lib.launch_count
         with torch.cuda.graph(self._graph, stream=s, capture_error_mode="thread_local"):
             self._loss_buf = self._step_body(self._static_in)
+        self._graph_launches = _lib.launch_count - n0  # kernels of ours replayed by every graph launch
         # capture does not execute: undo the step increments of the capture pass
         self.store.global_step -= 1
 
