@@ -952,3 +952,66 @@ extern "C" int dtf_stream_capture_status(void* stream) {
   if (cudaStreamIsCapturing(ST(stream), &st) != cudaSuccess) return -1;
   return (int)st;
 }
+
+// ------------------------------------------------------------------------------------------- allocation-free variant
+// dtf_softmax_xent_noalloc: the fused softmax cross-entropy of dtf_softmax_xent for callers that must not (or cannot)
+// allocate device memory. Examples: a host application that has already handed all of the GPU's memory to its own
+// pool, so that a cudaMalloc from a plug-in fails or fragments the pool; a serving or training loop with a
+// latency budget, where cudaMalloc / cudaFree would stall the device; a sandboxed extension point whose contract
+// forbids allocation after start-up. Such callers own their input and output buffers already; the only thing
+// dtf_softmax_xent still asks them for is its scratch area (one arrival counter plus one partial loss per row), and
+// this variant takes that from a fixed array that lives inside the library instead.
+//
+// Limits and rules:
+//   * at most DTF_XENT_NOALLOC_MAX_ROWS rows per call (larger B is refused with DTF_ERR_TOO_LARGE, nothing is launched);
+//   * the array (256 KiB + one word) is part of the loaded library image: every GPU that loads the library keeps it
+//     resident until the process exits, whether or not this entry point is ever called;
+//   * all calls on one GPU share the array. It still holds the previous call's partial losses; the only word that
+//     has to start at zero, the arrival counter, is cleared on the caller's stream before each launch. Two calls that
+//     may run on the GPU at the same time (different streams, or different host threads) race on the array and
+//     produce wrong losses: serialise them;
+//   * the first call on each GPU resolves the device address of the array (a host-side symbol is not a device
+//     pointer) while that GPU is current. Make that first call during start-up, before any stream capture begins.
+//   * no cudaMalloc / cudaFree / allocating library routine is called, on the first call or later.
+#define DTF_XENT_NOALLOC_MAX_ROWS 65536
+static __device__ __align__(256) float g_xent_noalloc_scratch[1 + DTF_XENT_NOALLOC_MAX_ROWS];
+
+#include <mutex>
+namespace {
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[64] = {};  // per device: device address of g_xent_noalloc_scratch, resolved on first use
+}  // namespace
+
+extern "C" int dtf_softmax_xent_noalloc_max_rows(void) { return DTF_XENT_NOALLOC_MAX_ROWS; }
+
+extern "C" int dtf_softmax_xent_noalloc(const void* logits, const long long* labels, void* dlogits, float* loss,
+                                        int B, int C, float gscale, int is_bf16, void* stream) {
+  if (B <= 0 || C <= 0) return DTF_ERR_ARG;
+  if (B > DTF_XENT_NOALLOC_MAX_ROWS) return DTF_ERR_TOO_LARGE;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DTF_ERR_CUDA;
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (g_noalloc_ptr[dev] == nullptr) {
+      // In host code the array's name only stands for the symbol; the address a kernel may dereference has to be
+      // asked for, with the target device current.
+      float* p = nullptr;
+      if (cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_xent_noalloc_scratch) != cudaSuccess || p == nullptr)
+        return DTF_ERR_CUDA;
+      g_noalloc_ptr[dev] = p;
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  cudaStream_t st = ST(stream);
+  // the arrival counter must be zero when the kernel starts, whatever an earlier (possibly aborted) call left behind
+  if (cudaMemsetAsync(scratch, 0, sizeof(float), st) != cudaSuccess) return DTF_ERR_CUDA;
+  const int blocks = (B + 7) / 8;
+  if (is_bf16)
+    softmax_xent_kernel<__nv_bfloat16><<<blocks, 256, 0, st>>>(
+        (const __nv_bfloat16*)logits, labels, (__nv_bfloat16*)dlogits, loss, scratch, B, C, gscale);
+  else
+    softmax_xent_kernel<float><<<blocks, 256, 0, st>>>((const float*)logits, labels, (float*)dlogits, loss, scratch,
+                                                       B, C, gscale);
+  return DTF_CHECK_LAUNCH();
+}

@@ -102,6 +102,19 @@ int dtf_mse(const void* pred, const void* target, void* dpred, float* loss, floa
             int is_bf16, void* stream);
 /* out = 0.5 * scale * sum(w^2): tf.nn.l2_loss weight-decay term (distribute_tools.py:63-65). */
 int dtf_l2_loss(const float* w, float* out, float* scratch, long long n, float scale, void* stream);
+/* Allocation-free variant of dtf_softmax_xent (no counterpart in the reference, which has no native code or
+ * allocation contract at all). For callers that cannot allocate device memory -- a host application that already
+ * owns all GPU memory through its own pool, a latency-bound loop where cudaMalloc would stall the device, a plug-in
+ * contract that forbids allocation after start-up: the scratch area comes from a fixed array inside the library
+ * (256 KiB + 4 B per GPU, resident from library load to process exit) instead of from the caller. At most
+ * dtf_softmax_xent_noalloc_max_rows() = 65536 rows per call; a larger B returns DTF_ERR_TOO_LARGE and launches
+ * nothing. The first call on each GPU resolves the array's device address: make it at start-up with that GPU
+ * current, before any stream capture. All calls on a GPU share the array (it keeps the previous call's partial
+ * losses; the arrival counter is cleared on the caller's stream before each launch), so calls that can overlap on
+ * the GPU race: serialise them. Neither cudaMalloc, cudaFree nor any allocating routine is called. */
+int dtf_softmax_xent_noalloc_max_rows(void);
+int dtf_softmax_xent_noalloc(const void* logits, const long long* labels, void* dlogits, float* loss, int B, int C,
+                             float gscale, int is_bf16, void* stream);
 int dtf_top1_hits(const void* logits, const long long* labels, unsigned int* hits, int B, int C, int is_bf16,
                   void* stream);
 
