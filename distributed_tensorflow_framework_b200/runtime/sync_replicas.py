@@ -90,8 +90,11 @@ class InProcessParameterServer(object):
     # ---- chief side
     def start_chief_queue_runner(self, num_tokens=-1):
         if num_tokens == -1:
-            num_tokens = self.total_num_replicas
-        for _ in range(num_tokens):  # init tokens: let every worker take its first step
+            # TF seeds the queue with `replicas_to_aggregate` tokens, which lets every worker run one step ahead of
+            # the aggregation and makes its second push stale. Here only the tokens that are NEEDED for progress are
+            # seeded (replicas_to_aggregate > total_num_replicas), so workers move in lock-step with the global step.
+            num_tokens = max(0, self.replicas_to_aggregate - self.total_num_replicas)
+        for _ in range(num_tokens):
             self.token_queue.put(self.global_step)
         if self._runner is None:
             self._runner = threading.Thread(target=self._chief_loop, daemon=True)
