@@ -29,7 +29,7 @@ class CifarCNN(nn.Module):
 
 
 def _cbr(cin, cout, k, s):
-    return nn.Sequential(nn.Conv2d(cin, cout, k, s, k // 2, bias=True), nn.BatchNorm2d(cout, eps=1e-3))
+    return nn.Sequential(nn.Conv2d(cin, cout, k, s, k // 2, bias=False), nn.BatchNorm2d(cout, eps=1e-3))
 
 
 class Bottleneck(nn.Module):

@@ -128,11 +128,61 @@ igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       const uint32_t row_off = r * 128;
       const uint32_t sw = r & 7;
       int it = 0;
+      // Fast path: with C a multiple of 64 every k-block (64 channels = 128 B) lies inside ONE filter tap, so the
+      // tap is tracked with counters (no divisions) and the bounds test is done once per k-block.
+      const bool one_tap_per_kb = (p.C & 63) == 0;
+      const int cpb = p.C >> 6;  // k-blocks per tap
+      int f_tap = 0, f_cblk = 0, f_kh = 0, f_kw = 0;
+      if (one_tap_per_kb) {
+        f_tap = kb0 / cpb;
+        f_cblk = kb0 - f_tap * cpb;
+        f_kh = f_tap / p.KW;
+        f_kw = f_tap - f_kh * p.KW;
+      }
       for (int kb = kb0; kb < kb1; ++kb, ++it) {
         const int s = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
         const uint32_t dst_row = a_stage(s) + row_off;
+        if (one_tap_per_kb) {
+          const char* srcp = reinterpret_cast<const char*>(p.src);
+          uint32_t nbytes = 0;
+          if (row_ok) {
+            int iy, ix;
+            bool ok;
+            if (p.geo == GEO_FPROP) {
+              iy = py * p.stride - p.pad_h + f_kh;
+              ix = px * p.stride - p.pad_w + f_kw;
+              ok = (iy >= 0) && (iy < p.H) && (ix >= 0) && (ix < p.W);
+            } else {
+              const int ty = py + p.pad_h - f_kh;
+              const int tx = px + p.pad_w - f_kw;
+              if (p.stride == 1) {
+                iy = ty;
+                ix = tx;
+                ok = (ty >= 0) && (tx >= 0) && (iy < p.H) && (ix < p.W);
+              } else {
+                iy = ty / p.stride;
+                ix = tx / p.stride;
+                ok = (ty >= 0) && (tx >= 0) && (iy * p.stride == ty) && (ix * p.stride == tx) && (iy < p.H) &&
+                     (ix < p.W);
+              }
+            }
+            if (ok) {
+              srcp = reinterpret_cast<const char*>(img + ((size_t)iy * p.W + ix) * p.C + (f_cblk << 6));
+              nbytes = 16;
+            }
+          }
+#pragma unroll
+          for (int c = 0; c < 8; ++c) cp_async16(dst_row + ((c ^ sw) << 4), srcp + (nbytes ? c * 16 : 0), nbytes);
+          if (++f_cblk == cpb) {
+            f_cblk = 0;
+            if (++f_kw == p.KW) {
+              f_kw = 0;
+              ++f_kh;
+            }
+          }
+        } else {
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
           const int k = kb * BLOCK_K + c * 8;
@@ -163,6 +213,7 @@ igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             }
           }
           cp_async16(dst_row + ((c ^ sw) << 4), srcp, nbytes);
+        }
         }
         cp_async_commit();
         if (it >= GATHER_LAG) {

@@ -145,34 +145,52 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
   const long long r0 = (long long)blockIdx.y * rows_per_block;
   const long long r1 = min(R, r0 + rows_per_block);
   if (active) {
-    for (long long r = r0 + row_lane; r < r1; r += rpp) {
-      const long long off = r * N + (long long)col_chunk * 8;
-      float g[8];
-      unpack8(ld8(in0 + off), g);
-      if (MODE == 1 || (MODE == 3 && relu)) {
-        float y[8];
-        unpack8(ld8(in1 + off), y);
+    constexpr int U = 4;  // rows in flight per thread (memory-level parallelism)
+    for (long long rb = r0 + row_lane; rb < r1; rb += (long long)rpp * U) {
+      BF8 b0[U], b1[U], b2[U];
+      bool ok[U];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) g[j] = y[j] > 0.f ? g[j] : 0.f;
+      for (int u = 0; u < U; ++u) {
+        const long long r = rb + (long long)u * rpp;
+        ok[u] = r < r1;
+        if (ok[u]) {
+          const long long off = r * N + (long long)col_chunk * 8;
+          b0[u] = ld8(in0 + off);
+          if (MODE == 1 || (MODE == 3 && relu)) b1[u] = ld8(in1 + off);
+          if (MODE == 3) b2[u] = ld8(in2 + off);
+        }
       }
-      if ((MODE == 1 || MODE == 3) && out != nullptr) st8(out + off, pack8(g));
-      if (MODE == 2) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          a0[j] += g[j];
-          a1[j] = fmaf(g[j], g[j], a1[j]);
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        const long long off = (rb + (long long)u * rpp) * N + (long long)col_chunk * 8;
+        float g[8];
+        unpack8(b0[u], g);
+        if (MODE == 1 || (MODE == 3 && relu)) {
+          float y[8];
+          unpack8(b1[u], y);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = y[j] > 0.f ? g[j] : 0.f;
         }
-      } else if (MODE == 3) {
-        float x[8];
-        unpack8(ld8(in2 + off), x);
+        if ((MODE == 1 || MODE == 3) && out != nullptr) st8(out + off, pack8(g));
+        if (MODE == 2) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          a0[j] += g[j];
-          a1[j] = fmaf(g[j], (x[j] - mu[j]) * rs[j], a1[j]);
+          for (int j = 0; j < 8; ++j) {
+            a0[j] += g[j];
+            a1[j] = fmaf(g[j], g[j], a1[j]);
+          }
+        } else if (MODE == 3) {
+          float x[8];
+          unpack8(b2[u], x);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            a0[j] += g[j];
+            a1[j] = fmaf(g[j], (x[j] - mu[j]) * rs[j], a1[j]);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a0[j] += g[j];
         }
-      } else {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) a0[j] += g[j];
       }
     }
   }
@@ -206,9 +224,9 @@ static int launch_colreduce(const void* in0, const void* in1, const void* in2, v
   const int gx = (cpr + 255) / 256;
   const int cprg = cpr < 256 ? cpr : 256;
   const int rpp = 256 / cprg;
-  long long want_blocks = 148 * 8 / gx;
+  long long want_blocks = 148 * 16 / gx;
   long long rows_per_block = (R + want_blocks - 1) / want_blocks;
-  const long long min_rows = (long long)rpp * 8;
+  const long long min_rows = (long long)rpp * 16;
   if (rows_per_block < min_rows) rows_per_block = min_rows;
   const int gy = (int)((R + rows_per_block - 1) / rows_per_block);
   colreduce_kernel<MODE><<<dim3(gx, gy), 256, 0, st>>>(
@@ -280,11 +298,23 @@ __global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_
     st8(y + i * 8, pack8(f));
   }
 }
-// dx = gamma*rstd * (dz - sum_dz/R - xhat * sum_dz_xhat/R);  sums: [2][N]
+// dx = gamma*rstd * (dz - sum_dz/R - xhat * sum_dz_xhat/R), folded into dx = A[c]*dz + B[c]*x + C[c]
+// coef: [3][N] workspace = {A, B, C}; sums: [2][N] = {sum dz, sum dz*xhat}
+__global__ void bn_bwd_coef_kernel(const float* __restrict__ sums, const float* __restrict__ mean,
+                                   const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                   float* __restrict__ coef, int N, float inv_R) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= N) return;
+  const float rs = rstd[c], mu = mean[c];
+  const float g = (gamma ? gamma[c] : 1.f) * rs;
+  const float s0 = sums[c] * inv_R, s1 = sums[N + c] * inv_R;
+  coef[c] = g;
+  coef[N + c] = -g * rs * s1;
+  coef[2 * N + c] = g * (mu * rs * s1 - s0);
+}
 __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x,
-                                    __nv_bfloat16* __restrict__ dx, const float* __restrict__ sums,
-                                    const float* __restrict__ mean, const float* __restrict__ rstd,
-                                    const float* __restrict__ gamma, long long total8, int N, float inv_R) {
+                                    __nv_bfloat16* __restrict__ dx, const float* __restrict__ coef, long long total8,
+                                    int N) {
   const int cpr = N / 8;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8;
        i += (long long)gridDim.x * blockDim.x) {
@@ -292,22 +322,24 @@ __global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const 
     float g[8], xv[8];
     unpack8(ld8(dz + i * 8), g);
     unpack8(ld8(x + i * 8), xv);
+    float A[8], B[8], C[8];
+    *reinterpret_cast<float4*>(A) = *reinterpret_cast<const float4*>(coef + c0);
+    *reinterpret_cast<float4*>(A + 4) = *reinterpret_cast<const float4*>(coef + c0 + 4);
+    *reinterpret_cast<float4*>(B) = *reinterpret_cast<const float4*>(coef + N + c0);
+    *reinterpret_cast<float4*>(B + 4) = *reinterpret_cast<const float4*>(coef + N + c0 + 4);
+    *reinterpret_cast<float4*>(C) = *reinterpret_cast<const float4*>(coef + 2 * N + c0);
+    *reinterpret_cast<float4*>(C + 4) = *reinterpret_cast<const float4*>(coef + 2 * N + c0 + 4);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = c0 + j;
-      const float rs = rstd[c];
-      const float xhat = (xv[j] - mean[c]) * rs;
-      const float ga = gamma ? gamma[c] : 1.f;
-      g[j] = ga * rs * (g[j] - sums[c] * inv_R - xhat * sums[N + c] * inv_R);
-    }
+    for (int j = 0; j < 8; ++j) g[j] = fmaf(A[j], g[j], fmaf(B[j], xv[j], C[j]));
     st8(dx + i * 8, pack8(g));
   }
 }
 
 // ------------------------------------------------------------------------------------------- pooling (NHWC)
-__global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int n_img, int H,
-                                int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt, int pl,
-                                int is_max) {
+// idx (optional, max pooling): position of the first maximum inside the window (dy*kw + dx), one byte per output.
+__global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                uint8_t* __restrict__ idx, int n_img, int H, int W, int C, int OH, int OW, int kh,
+                                int kw, int sh, int sw, int pt, int pl, int is_max) {
   const int cpr = C / 8;
   const long long total = (long long)n_img * OH * OW * cpr;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -319,8 +351,12 @@ __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
     const int oh = (int)(t % OH);
     const int n = (int)(t / OH);
     float a[8];
+    uint32_t am[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a[j] = is_max ? -INFINITY : 0.f;
+    for (int j = 0; j < 8; ++j) {
+      a[j] = is_max ? -INFINITY : 0.f;
+      am[j] = 0;
+    }
     int cnt = 0;
     for (int dy = 0; dy < kh; ++dy) {
       const int ih = oh * sh - pt + dy;
@@ -330,8 +366,19 @@ __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
         if (iw < 0 || iw >= W) continue;
         float f[8];
         unpack8(ld8(x + (((long long)n * H + ih) * W + iw) * C + c0), f);
+        if (is_max) {
+          const uint32_t pos = dy * kw + dx;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) a[j] = is_max ? fmaxf(a[j], f[j]) : a[j] + f[j];
+          for (int j = 0; j < 8; ++j) {
+            if (f[j] > a[j] || cnt == 0) {  // first maximum wins (row-major scan), like ATen / cuDNN
+              a[j] = f[j];
+              am[j] = pos;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a[j] += f[j];
+        }
         ++cnt;
       }
     }
@@ -339,13 +386,18 @@ __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
       const float inv = cnt > 0 ? 1.f / cnt : 0.f;  // TF SAME avg-pool excludes padding from the divisor
 #pragma unroll
       for (int j = 0; j < 8; ++j) a[j] *= inv;
+    } else if (idx != nullptr) {
+      uint2 pk;
+      pk.x = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+      pk.y = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
+      *reinterpret_cast<uint2*>(idx + i * 8) = pk;
     }
     st8(y + i * 8, pack8(a));
   }
 }
-// Gather-style backward (deterministic, no atomics): each input element visits the windows that cover it.
-// Max: gradient goes to the first maximum of the window in row-major scan order (matches ATen / cuDNN).
-__global__ void pool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+// Gather-style backward (deterministic, no atomics): each input element visits the (few) windows that cover it.
+// Max: the window's recorded argmax decides; Avg: dy / (valid elements of the window).
+__global__ void pool_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ dy,
                                 __nv_bfloat16* __restrict__ dx, int n_img, int H, int W, int C, int OH, int OW, int kh,
                                 int kw, int sh, int sw, int pt, int pl, int is_max) {
   const int cpr = C / 8;
@@ -361,38 +413,22 @@ __global__ void pool_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_
     float g[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[j] = 0.f;
-    float xs[8];
-    if (is_max) unpack8(ld8(x + i * 8), xs);
     const int oh_lo = max(0, (h + pt - kh + sh) / sh), oh_hi = min(OH - 1, (h + pt) / sh);
     const int ow_lo = max(0, (w + pl - kw + sw) / sw), ow_hi = min(OW - 1, (w + pl) / sw);
     for (int oh = oh_lo; oh <= oh_hi; ++oh) {
       for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        const long long o = (((long long)n * OH + oh) * OW + ow) * C + c0;
         float d[8];
-        unpack8(ld8(dy + (((long long)n * OH + oh) * OW + ow) * C + c0), d);
+        unpack8(ld8(dy + o), d);
         const int ih0 = oh * sh - pt, iw0 = ow * sw - pl;
         if (is_max) {
-          // is (h,w) the first max of this window?
-          bool win[8];
+          const uint32_t pos = (h - ih0) * kw + (w - iw0);
+          const uint2 pk = *reinterpret_cast<const uint2*>(idx + o);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) win[j] = true;
-          for (int ddy = 0; ddy < kh; ++ddy) {
-            const int ih = ih0 + ddy;
-            if (ih < 0 || ih >= H) continue;
-            for (int ddx = 0; ddx < kw; ++ddx) {
-              const int iw = iw0 + ddx;
-              if (iw < 0 || iw >= W) continue;
-              if (ih == h && iw == w) continue;
-              float f[8];
-              unpack8(ld8(x + (((long long)n * H + ih) * W + iw) * C + c0), f);
-              const bool before = (ih < h) || (ih == h && iw < w);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                if (before ? (f[j] >= xs[j]) : (f[j] > xs[j])) win[j] = false;
-              }
-            }
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t a = ((j < 4 ? pk.x : pk.y) >> ((j & 3) * 8)) & 0xff;
+            g[j] += (a == pos) ? d[j] : 0.f;
           }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] += win[j] ? d[j] : 0.f;
         } else {
           const int h0 = max(ih0, 0), h1 = min(ih0 + kh, H), w0 = max(iw0, 0), w1 = min(iw0 + kw, W);
           const float inv = 1.f / ((h1 - h0) * (w1 - w0));
@@ -836,27 +872,30 @@ extern "C" int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, v
   return launch_colreduce<3>(dy, y, x, dz, sums, mean, rstd, R, N, relu, ST(stream));
 }
 extern "C" int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* sums, const float* mean,
-                                const float* rstd, const float* gamma, long long R, int N, void* stream) {
+                                const float* rstd, const float* gamma, float* coef, long long R, int N, void* stream) {
   if (N % 8) return DTF_ERR_ALIGN;
   const long long total8 = R * (N / 8);
+  bn_bwd_coef_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(sums, mean, rstd, gamma, coef, N, 1.f / (float)R);
   bn_bwd_apply_kernel<<<grid_for(total8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)x,
-                                                                     (__nv_bfloat16*)dx, sums, mean, rstd, gamma,
-                                                                     total8, N, 1.f / (float)R);
+                                                                     (__nv_bfloat16*)dx, coef, total8, N);
   return DTF_CHECK_LAUNCH();
 }
-extern "C" int dtf_pool_fwd(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int kh, int kw,
-                            int sh, int sw, int pt, int pl, int is_max, void* stream) {
+extern "C" int dtf_pool_fwd(const void* x, void* y, void* idx, int n_img, int H, int W, int C, int OH, int OW, int kh,
+                            int kw, int sh, int sw, int pt, int pl, int is_max, void* stream) {
   if (C % 8) return DTF_ERR_ALIGN;
+  if (kh * kw > 255) return DTF_ERR_UNSUPPORTED;
   const long long total = (long long)n_img * OH * OW * (C / 8);
-  pool_fwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n_img, H,
-                                                                W, C, OH, OW, kh, kw, sh, sw, pt, pl, is_max);
+  pool_fwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y,
+                                                                (uint8_t*)idx, n_img, H, W, C, OH, OW, kh, kw, sh, sw,
+                                                                pt, pl, is_max);
   return DTF_CHECK_LAUNCH();
 }
-extern "C" int dtf_pool_bwd(const void* x, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW,
+extern "C" int dtf_pool_bwd(const void* idx, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW,
                             int kh, int kw, int sh, int sw, int pt, int pl, int is_max, void* stream) {
   if (C % 8) return DTF_ERR_ALIGN;
+  if (is_max && idx == nullptr) return DTF_ERR_ARG;
   const long long total = (long long)n_img * H * W * (C / 8);
-  pool_bwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
+  pool_bwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const uint8_t*)idx, (const __nv_bfloat16*)dy,
                                                                 (__nv_bfloat16*)dx, n_img, H, W, C, OH, OW, kh, kw,
                                                                 sh, sw, pt, pl, is_max);
   return DTF_CHECK_LAUNCH();

@@ -166,15 +166,15 @@ def linear(x, wvar, bvar, relu=False, out_fp32=False):
 class PoolFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, k, s, is_max):
-        y = raw.pool_fwd(x, k, s, is_max)
-        ctx.k, ctx.s, ctx.is_max = k, s, is_max
-        ctx.save_for_backward(x)
+        y, idx = raw.pool_fwd(x, k, s, is_max, want_idx=x.requires_grad)
+        ctx.k, ctx.s, ctx.is_max, ctx.in_shape = k, s, is_max, tuple(x.shape)
+        ctx.save_for_backward(idx)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        (x,) = ctx.saved_tensors
-        return raw.pool_bwd(x, dy.contiguous(), ctx.k, ctx.s, ctx.is_max), None, None, None
+        (idx,) = ctx.saved_tensors
+        return raw.pool_bwd(idx, dy.contiguous(), ctx.in_shape, ctx.k, ctx.s, ctx.is_max), None, None, None
 
 
 def pool2d(x, k=(2, 2), s=(2, 2), is_max=True):

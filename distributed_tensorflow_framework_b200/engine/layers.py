@@ -127,14 +127,15 @@ def conv_eval(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stri
     return conv(layer_name, x, in_channels, out_channels, kernel_size, stride)
 
 
-def conv_nonacti(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1]):
-    """conv2d + bias, Xavier init, variables `weights_nonacti` / `biases_nonacti` -- distribute_tools.py:93-106."""
+def conv_nonacti(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1], use_bias=True):
+    """conv2d + bias, Xavier init, variables `weights_nonacti` / `biases_nonacti` -- distribute_tools.py:93-106.
+    `use_bias=False` (extension) drops the bias for convolutions that feed a batch norm, where it is redundant."""
     with variable_scope(layer_name):
         shape = [kernel_size[0], kernel_size[1], in_channels, out_channels]
         store = [kernel_size[0], kernel_size[1], _pad8(in_channels), _pad8(out_channels)] if x.is_cuda else None
         w = _get("weights_nonacti", shape, XavierInitializer(), kind="conv_w", store_shape=store)
         b = _get("biases_nonacti", [out_channels], ConstantInitializer(0.0), kind="bias",
-                 store_shape=[_pad8(out_channels)] if x.is_cuda else None)
+                 store_shape=[_pad8(out_channels)] if x.is_cuda else None) if use_bias else None
         return _conv_impl(x, w, b, stride, relu=False)
 
 

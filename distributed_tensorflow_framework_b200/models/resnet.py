@@ -8,7 +8,7 @@ from ..plugins.model import Model
 
 
 def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None):
-    y = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1])
+    y = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1], use_bias=False)
     return L.batch_norm_channel(name + "/bn", y, relu=relu, residual=residual)
 
 

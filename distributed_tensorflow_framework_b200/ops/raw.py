@@ -41,6 +41,8 @@ def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=No
 def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False):
     n, H, W, C = x.shape
     n_out = w2d.shape[1]
+    if KH == 1 and KW == 1 and stride == 1:  # a 1x1 convolution is a dense GEMM: TMA-fed A operand, no gather
+        return gemm(x.view(-1, C), w2d, bias, relu=relu, out_fp32=out_fp32).view(n, H, W, n_out)
     OH, pt = same_pad(H, KH, stride)
     OW, pl = same_pad(W, KW, stride)
     out = torch.empty((n, OH, OW, n_out), device=x.device, dtype=torch.float32 if out_fp32 else bf16)
@@ -55,6 +57,8 @@ def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False):
     n, OH, OW, Co = dy.shape
     H, W = in_hw
     Ci = w2d_t.shape[1]
+    if KH == 1 and KW == 1 and stride == 1:
+        return gemm(dy.view(-1, Co), w2d_t, bias, relu=relu).view(n, H, W, Ci)
     _, pt = same_pad(H, KH, stride)
     _, pl = same_pad(W, KW, stride)
     dx = torch.empty((n, H, W, Ci), device=dy.device, dtype=bf16)
@@ -71,6 +75,8 @@ def conv_wgrad(x, dy, KH, KW, stride=1, out=None):
     _, pl = same_pad(W, KW, stride)
     if out is None:
         out = torch.zeros((KH * KW * C, Co), device=x.device, dtype=torch.float32)
+    if KH == 1 and KW == 1 and stride == 1:  # dW = x^T dy: dense MN-major A operand, split over pixels
+        return gemm(x.view(-1, C), dy.view(-1, Co), a_transposed=True, out=out, accumulate=True)
     _lib.call("dtf_conv_wgrad_bf16", x, dy, out, n, H, W, C, OH, OW, KH, KW, Co, stride, pt, pl, _sp())
     return out
 
@@ -129,19 +135,21 @@ def pool_geometry(H, W, k, s):
     return OH, OW, pt, pl
 
 
-def pool_fwd(x, k=(2, 2), s=(2, 2), is_max=True):
+def pool_fwd(x, k=(2, 2), s=(2, 2), is_max=True, want_idx=True):
+    """Returns (y, idx); idx (uint8 argmax positions) is None for average pooling."""
     n, H, W, C = x.shape
     OH, OW, pt, pl = pool_geometry(H, W, k, s)
     y = torch.empty((n, OH, OW, C), device=x.device, dtype=bf16)
-    _lib.call("dtf_pool_fwd", x, y, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl, 1 if is_max else 0, _sp())
-    return y
+    idx = torch.empty((n, OH, OW, C), device=x.device, dtype=torch.uint8) if (is_max and want_idx) else None
+    _lib.call("dtf_pool_fwd", x, y, idx, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl, 1 if is_max else 0, _sp())
+    return y, idx
 
 
-def pool_bwd(x, dy, k=(2, 2), s=(2, 2), is_max=True):
-    n, H, W, C = x.shape
+def pool_bwd(idx, dy, in_shape, k=(2, 2), s=(2, 2), is_max=True):
+    n, H, W, C = in_shape
     OH, OW, pt, pl = pool_geometry(H, W, k, s)
-    dx = torch.empty_like(x)
-    _lib.call("dtf_pool_bwd", x, dy, dx, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl, 1 if is_max else 0, _sp())
+    dx = torch.empty(tuple(in_shape), device=dy.device, dtype=bf16)
+    _lib.call("dtf_pool_bwd", idx, dy, dx, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl, 1 if is_max else 0, _sp())
     return dx
 
 
@@ -194,7 +202,8 @@ def bn_bwd(dy2d, y2d, x2d, mean, rstd, gamma, relu=False):
     _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if relu else None, x2d, dz if relu else None, sums, mean, rstd, R, N,
               1 if relu else 0, _sp())
     dx = torch.empty_like(x2d)
-    _lib.call("dtf_bn_bwd_apply", dz, x2d, dx, sums, mean, rstd, gamma, R, N, _sp())
+    coef = torch.empty(3, N, device=x2d.device, dtype=torch.float32)
+    _lib.call("dtf_bn_bwd_apply", dz, x2d, dx, sums, mean, rstd, gamma, coef, R, N, _sp())
     return dx, dz, sums[1], sums[0]
 
 

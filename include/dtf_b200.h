@@ -77,13 +77,15 @@ int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, co
                  int relu, void* stream);
 int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* sums, const float* mean,
                       const float* rstd, long long R, int N, int relu, void* stream);
+/* coef: [3][N] float workspace (per-channel folded coefficients, written by the call). */
 int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* sums, const float* mean, const float* rstd,
-                     const float* gamma, long long R, int N, void* stream);
+                     const float* gamma, float* coef, long long R, int N, void* stream);
 
-/* pool (distribute_tools.py:160-165): max / avg, TF SAME semantics via explicit top/left padding. */
-int dtf_pool_fwd(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
-                 int pt, int pl, int is_max, void* stream);
-int dtf_pool_bwd(const void* x, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW, int kh,
+/* pool (distribute_tools.py:160-165): max / avg, TF SAME semantics via explicit top/left padding. Max pooling
+ * records the in-window position of the first maximum (one byte per output element, `idx`) for the backward. */
+int dtf_pool_fwd(const void* x, void* y, void* idx, int n_img, int H, int W, int C, int OH, int OW, int kh, int kw,
+                 int sh, int sw, int pt, int pl, int is_max, void* stream);
+int dtf_pool_bwd(const void* idx, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW, int kh,
                  int kw, int sh, int sw, int pt, int pl, int is_max, void* stream);
 
 /* norm / tf.nn.lrn (distribute_tools.py:183-187): y = x / (bias + alpha * sum_{|j-c|<=radius} x_j^2)^beta. */

@@ -69,11 +69,11 @@ def test_pool(raw, k, s, is_max):
         num = F.avg_pool2d(F.pad(xf, (pl, pr, pt, pb)), k, s, divisor_override=1)
         cnt = F.avg_pool2d(F.pad(torch.ones_like(xf), (pl, pr, pt, pb)), k, s, divisor_override=1)
         ref = num / cnt
-    y = raw.pool_fwd(x, k, s, is_max)
+    y, idx = raw.pool_fwd(x, k, s, is_max)
     close(y, ref.permute(0, 2, 3, 1))
     dy = rnd(n, OH, OW, C)
     ref.backward(dy.float().permute(0, 3, 1, 2))
-    close(raw.pool_bwd(x, dy, k, s, is_max), xf.grad.permute(0, 2, 3, 1))
+    close(raw.pool_bwd(idx, dy, x.shape, k, s, is_max), xf.grad.permute(0, 2, 3, 1))
 
 
 def test_lrn(raw):
