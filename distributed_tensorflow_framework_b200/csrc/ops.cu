@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(256)
 colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __restrict__ in1,
                  const __nv_bfloat16* __restrict__ in2, __nv_bfloat16* __restrict__ out, float* __restrict__ acc,
                  const float* __restrict__ mean, const float* __restrict__ rstd, long long R, int N, int relu,
-                 int rows_per_block) {
+                 int rows_per_block, float* __restrict__ part) {
   constexpr int NACC = (MODE >= 2) ? 2 : 1;
   const int cpr = N / 8;
   const int cg0 = blockIdx.x * 256;
@@ -145,7 +145,7 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
   const long long r0 = (long long)blockIdx.y * rows_per_block;
   const long long r1 = min(R, r0 + rows_per_block);
   if (active) {
-    constexpr int U = 4;  // rows in flight per thread (memory-level parallelism)
+    constexpr int U = (MODE == 3) ? 4 : 8;  // rows in flight per thread (memory-level parallelism)
     for (long long rb = r0 + row_lane; rb < r1; rb += (long long)rpp * U) {
       BF8 b0[U], b1[U], b2[U];
       bool ok[U];
@@ -210,42 +210,110 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
       for (int l = 0; l < rpp; ++l)
 #pragma unroll
         for (int j = 0; j < 8; ++j) s[j] += red[q][tid + l * cprg][j];
+      if (part != nullptr) {
+        // deterministic path: per-row-block partials [gridDim.y][NACC][N], summed later in a fixed order
+        float* o = part + ((size_t)blockIdx.y * NACC + q) * N + (size_t)(cg0 + tid) * 8;
+        *reinterpret_cast<float4*>(o) = make_float4(s[0], s[1], s[2], s[3]);
+        *reinterpret_cast<float4*>(o + 4) = make_float4(s[4], s[5], s[6], s[7]);
+      } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) atomicAdd(acc + (size_t)q * N + (size_t)(cg0 + tid) * 8 + j, s[j]);
+        for (int j = 0; j < 8; ++j) atomicAdd(acc + (size_t)q * N + (size_t)(cg0 + tid) * 8 + j, s[j]);
+      }
     }
   }
 }
 
-template <int MODE>
-static int launch_colreduce(const void* in0, const void* in1, const void* in2, void* out, float* acc,
-                            const float* mean, const float* rstd, long long R, int N, int relu, cudaStream_t st) {
-  if (N % 8) return DTF_ERR_ALIGN;
+static void colreduce_geometry(long long R, int N, int* gx_out, int* gy_out, int* rows_per_block_out) {
   const int cpr = N / 8;
   const int gx = (cpr + 255) / 256;
   const int cprg = cpr < 256 ? cpr : 256;
   const int rpp = 256 / cprg;
-  long long want_blocks = 148 * 16 / gx;
+  long long want_blocks = 148 * 2 / gx;
+  if (want_blocks < 1) want_blocks = 1;
   long long rows_per_block = (R + want_blocks - 1) / want_blocks;
-  const long long min_rows = (long long)rpp * 16;
+  const long long min_rows = (long long)rpp * 8;
   if (rows_per_block < min_rows) rows_per_block = min_rows;
-  const int gy = (int)((R + rows_per_block - 1) / rows_per_block);
+  *gx_out = gx;
+  *gy_out = (int)((R + rows_per_block - 1) / rows_per_block);
+  *rows_per_block_out = (int)rows_per_block;
+}
+
+// row-walking elementwise kernels: more blocks than the reductions (no partials to combine afterwards)
+static void elementwise_geometry(long long R, int N, int* gx_out, int* gy_out, int* rows_per_block_out) {
+  const int cpr = N / 8;
+  const int gx = (cpr + 255) / 256;
+  const int cprg = cpr < 256 ? cpr : 256;
+  const int rpp = 256 / cprg;
+  long long want_blocks = 148 * 8 / gx;
+  if (want_blocks < 1) want_blocks = 1;
+  long long rows_per_block = (R + want_blocks - 1) / want_blocks;
+  const long long min_rows = (long long)rpp * 4;
+  if (rows_per_block < min_rows) rows_per_block = min_rows;
+  *gx_out = gx;
+  *gy_out = (int)((R + rows_per_block - 1) / rows_per_block);
+  *rows_per_block_out = (int)rows_per_block;
+}
+
+template <int MODE>
+static int launch_colreduce(const void* in0, const void* in1, const void* in2, void* out, float* acc, float* part,
+                            const float* mean, const float* rstd, long long R, int N, int relu, cudaStream_t st) {
+  if (N % 8) return DTF_ERR_ALIGN;
+  int gx, gy, rows_per_block;
+  colreduce_geometry(R, N, &gx, &gy, &rows_per_block);
   colreduce_kernel<MODE><<<dim3(gx, gy), 256, 0, st>>>(
       (const __nv_bfloat16*)in0, (const __nv_bfloat16*)in1, (const __nv_bfloat16*)in2, (__nv_bfloat16*)out, acc, mean,
-      rstd, R, N, relu, (int)rows_per_block);
+      rstd, R, N, relu, rows_per_block, part);
   return DTF_CHECK_LAUNCH();
 }
 
+// out[q][c] (+)= sum_b part[b][q][c]: fixed summation order => bitwise reproducible. One block per 32 columns;
+// 8 warps split the row-blocks, then combine through shared memory.
+template <int NACC>
+__device__ __forceinline__ void reduce_partials(const float* __restrict__ part, int nblk, int N, int c, float (&s)[NACC]) {
+  constexpr int NW = 32;  // warps per block (blockDim.x == 1024)
+  __shared__ float sm[NACC][NW][33];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < NACC; ++q) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    if (c < N) {
+      const float* p = part + (size_t)q * N + c;
+      const size_t st = (size_t)NACC * N;
+      int b = w;
+      for (; b + 3 * NW < nblk; b += 4 * NW) {
+        a0 += p[(size_t)b * st];
+        a1 += p[(size_t)(b + NW) * st];
+        a2 += p[(size_t)(b + 2 * NW) * st];
+        a3 += p[(size_t)(b + 3 * NW) * st];
+      }
+      for (; b < nblk; b += NW) a0 += p[(size_t)b * st];
+    }
+    sm[q][w][lane] = (a0 + a1) + (a2 + a3);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < NACC; ++q) {
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < NW; ++k) a += sm[q][k][lane];
+    s[q] = a;
+  }
+}
+
 // ------------------------------------------------------------------------------------------- batch norm
-// stats: [2][N] = {sum, sumsq}. Produces mean, rstd and folded scale/shift; updates running stats (momentum m).
-__global__ void bn_finalize_kernel(const float* __restrict__ stats, const float* __restrict__ gamma,
-                                   const float* __restrict__ beta, float* __restrict__ mean, float* __restrict__ rstd,
-                                   float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ run_mean,
-                                   float* __restrict__ run_var, int N, float inv_R, float eps, float momentum,
-                                   float unbias) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= N) return;
-  const float mu = stats[c] * inv_R;
-  float var = stats[N + c] * inv_R - mu * mu;
+// part: [nblk][2][N] partial {sum, sumsq}. Produces mean, rstd and folded scale/shift; updates running stats.
+// Launch: 1024 threads (32 warps x 32 columns) per block, grid = ceil(N / 32).
+__global__ void __launch_bounds__(1024)
+bn_finalize_kernel(const float* __restrict__ part, int nblk, const float* __restrict__ gamma,
+                   const float* __restrict__ beta, float* __restrict__ mean, float* __restrict__ rstd,
+                   float* __restrict__ scale, float* __restrict__ shift, float* __restrict__ run_mean,
+                   float* __restrict__ run_var, int N, float inv_R, float eps, float momentum, float unbias) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  float s[2];
+  reduce_partials<2>(part, nblk, N, c, s);
+  if (threadIdx.x >= 32 || c >= N) return;
+  const float mu = s[0] * inv_R;
+  float var = s[1] * inv_R - mu * mu;
   var = fmaxf(var, 0.f);
   const float rs = rsqrtf(var + eps);
   mean[c] = mu;
@@ -270,68 +338,125 @@ __global__ void bn_fold_kernel(const float* __restrict__ run_mean, const float* 
   shift[c] = b - run_mean[c] * g * rs;
 }
 // y = x*scale[c] + shift[c] (+res) (relu)
-__global__ void bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
-                                __nv_bfloat16* __restrict__ y, const float* __restrict__ scale,
-                                const float* __restrict__ shift, long long total8, int N, int relu) {
+// Row-walking elementwise kernels share the column-reduction geometry: a thread owns one 8-channel chunk, keeps the
+// per-channel coefficients in registers and streams rows with U independent 16-byte loads in flight.
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                __nv_bfloat16* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
+                long long R, int N, int relu, int rows_per_block) {
   const int cpr = N / 8;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cpr) * 8;
-    float f[8];
-    unpack8(ld8(x + i * 8), f);
-    const float4 s0 = *reinterpret_cast<const float4*>(scale + c0), s1 = *reinterpret_cast<const float4*>(scale + c0 + 4);
-    const float4 h0 = *reinterpret_cast<const float4*>(shift + c0), h1 = *reinterpret_cast<const float4*>(shift + c0 + 4);
-    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-    const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+  const int cg0 = blockIdx.x * 256;
+  const int cprg = min(256, cpr - cg0);
+  const int rpp = 256 / cprg;
+  const int tid = threadIdx.x;
+  if (tid >= rpp * cprg) return;
+  const int col_chunk = cg0 + (tid % cprg);
+  const int row_lane = tid / cprg;
+  float sc[8], sh[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
-    if (res) {
-      float r[8];
-      unpack8(ld8(res + i * 8), r);
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = scale[col_chunk * 8 + j];
+    sh[j] = shift[col_chunk * 8 + j];
+  }
+  const long long r0 = (long long)blockIdx.y * rows_per_block;
+  const long long r1 = min(R, r0 + rows_per_block);
+  constexpr int U = 4;
+  for (long long rb = r0 + row_lane; rb < r1; rb += (long long)rpp * U) {
+    BF8 xb[U], rbuf[U];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    for (int u = 0; u < U; ++u) {
+      const long long r = rb + (long long)u * rpp;
+      if (r < r1) {
+        const long long off = r * N + (long long)col_chunk * 8;
+        xb[u] = ld8(x + off);
+        if (res) rbuf[u] = ld8(res + off);
+      }
     }
-    if (relu) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+    for (int u = 0; u < U; ++u) {
+      const long long r = rb + (long long)u * rpp;
+      if (r >= r1) continue;
+      float f[8];
+      unpack8(xb[u], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fmaf(f[j], sc[j], sh[j]);
+      if (res) {
+        float q[8];
+        unpack8(rbuf[u], q);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] += q[j];
+      }
+      if (relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
+      st8(y + r * N + (long long)col_chunk * 8, pack8(f));
     }
-    st8(y + i * 8, pack8(f));
   }
 }
 // dx = gamma*rstd * (dz - sum_dz/R - xhat * sum_dz_xhat/R), folded into dx = A[c]*dz + B[c]*x + C[c]
 // coef: [3][N] workspace = {A, B, C}; sums: [2][N] = {sum dz, sum dz*xhat}
-__global__ void bn_bwd_coef_kernel(const float* __restrict__ sums, const float* __restrict__ mean,
-                                   const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                   float* __restrict__ coef, int N, float inv_R) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= N) return;
+__global__ void __launch_bounds__(1024)
+bn_bwd_coef_kernel(const float* __restrict__ part, int nblk, const float* __restrict__ mean,
+                   const float* __restrict__ rstd, const float* __restrict__ gamma, float* __restrict__ coef,
+                   float* __restrict__ dgamma_acc, float* __restrict__ dbeta_acc, int N, float inv_R) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  float s[2];
+  reduce_partials<2>(part, nblk, N, c, s);
+  if (threadIdx.x >= 32 || c >= N) return;
   const float rs = rstd[c], mu = mean[c];
   const float g = (gamma ? gamma[c] : 1.f) * rs;
-  const float s0 = sums[c] * inv_R, s1 = sums[N + c] * inv_R;
+  const float s0 = s[0] * inv_R, s1 = s[1] * inv_R;
   coef[c] = g;
   coef[N + c] = -g * rs * s1;
   coef[2 * N + c] = g * (mu * rs * s1 - s0);
+  if (dbeta_acc) dbeta_acc[c] += s[0];    // d beta  = sum dz
+  if (dgamma_acc) dgamma_acc[c] += s[1];  // d gamma = sum dz * xhat
 }
-__global__ void bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x,
-                                    __nv_bfloat16* __restrict__ dx, const float* __restrict__ coef, long long total8,
-                                    int N) {
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x,
+                    __nv_bfloat16* __restrict__ dx, const float* __restrict__ coef, long long R, int N,
+                    int rows_per_block) {
   const int cpr = N / 8;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total8;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cpr) * 8;
-    float g[8], xv[8];
-    unpack8(ld8(dz + i * 8), g);
-    unpack8(ld8(x + i * 8), xv);
-    float A[8], B[8], C[8];
-    *reinterpret_cast<float4*>(A) = *reinterpret_cast<const float4*>(coef + c0);
-    *reinterpret_cast<float4*>(A + 4) = *reinterpret_cast<const float4*>(coef + c0 + 4);
-    *reinterpret_cast<float4*>(B) = *reinterpret_cast<const float4*>(coef + N + c0);
-    *reinterpret_cast<float4*>(B + 4) = *reinterpret_cast<const float4*>(coef + N + c0 + 4);
-    *reinterpret_cast<float4*>(C) = *reinterpret_cast<const float4*>(coef + 2 * N + c0);
-    *reinterpret_cast<float4*>(C + 4) = *reinterpret_cast<const float4*>(coef + 2 * N + c0 + 4);
+  const int cg0 = blockIdx.x * 256;
+  const int cprg = min(256, cpr - cg0);
+  const int rpp = 256 / cprg;
+  const int tid = threadIdx.x;
+  if (tid >= rpp * cprg) return;
+  const int col_chunk = cg0 + (tid % cprg);
+  const int row_lane = tid / cprg;
+  float A[8], B[8], C[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) g[j] = fmaf(A[j], g[j], fmaf(B[j], xv[j], C[j]));
-    st8(dx + i * 8, pack8(g));
+  for (int j = 0; j < 8; ++j) {
+    A[j] = coef[col_chunk * 8 + j];
+    B[j] = coef[N + col_chunk * 8 + j];
+    C[j] = coef[2 * N + col_chunk * 8 + j];
+  }
+  const long long r0 = (long long)blockIdx.y * rows_per_block;
+  const long long r1 = min(R, r0 + rows_per_block);
+  constexpr int U = 4;
+  for (long long rb = r0 + row_lane; rb < r1; rb += (long long)rpp * U) {
+    BF8 gb[U], xb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long r = rb + (long long)u * rpp;
+      if (r < r1) {
+        const long long off = r * N + (long long)col_chunk * 8;
+        gb[u] = ld8(dz + off);
+        xb[u] = ld8(x + off);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long r = rb + (long long)u * rpp;
+      if (r >= r1) continue;
+      float g[8], xv[8];
+      unpack8(gb[u], g);
+      unpack8(xb[u], xv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) g[j] = fmaf(A[j], g[j], fmaf(B[j], xv[j], C[j]));
+      st8(dx + r * N + (long long)col_chunk * 8, pack8(g));
+    }
   }
 }
 
@@ -834,23 +959,31 @@ extern "C" int dtf_add(const void* a, const void* b, void* z, long long n, int r
 }
 // db[N] += colsum(dy[R,N])   (db must be zeroed by the caller when starting a new accumulation)
 extern "C" int dtf_bias_grad(const void* dy, float* db, long long R, int N, void* stream) {
-  return launch_colreduce<0>(dy, nullptr, nullptr, nullptr, db, nullptr, nullptr, R, N, 0, ST(stream));
+  return launch_colreduce<0>(dy, nullptr, nullptr, nullptr, db, nullptr, nullptr, nullptr, R, N, 0, ST(stream));
 }
 // dz = dy * (y > 0); db[N] += colsum(dz)
 extern "C" int dtf_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db, long long R, int N,
                                       void* stream) {
-  return launch_colreduce<1>(dy, y, nullptr, dz, db, nullptr, nullptr, R, N, 1, ST(stream));
+  return launch_colreduce<1>(dy, y, nullptr, dz, db, nullptr, nullptr, nullptr, R, N, 1, ST(stream));
 }
-// stats[2][N] += {sum x, sum x^2}
-extern "C" int dtf_bn_stats(const void* x, float* stats, long long R, int N, void* stream) {
-  return launch_colreduce<2>(x, nullptr, nullptr, nullptr, stats, nullptr, nullptr, R, N, 0, ST(stream));
+// Number of row-blocks the column reductions use for an [R, N] matrix: partial buffers are [blocks][2][N] floats.
+extern "C" int dtf_colreduce_blocks(long long R, int N) {
+  if (N % 8 || N <= 0 || R <= 0) return 0;
+  int gx, gy, rpb;
+  colreduce_geometry(R, N, &gx, &gy, &rpb);
+  return gy;
 }
-extern "C" int dtf_bn_finalize(const float* stats, const float* gamma, const float* beta, float* mean, float* rstd,
+// part[blocks][2][N] = per-row-block {sum x, sum x^2} (no atomics: deterministic)
+extern "C" int dtf_bn_stats(const void* x, float* part, long long R, int N, void* stream) {
+  return launch_colreduce<2>(x, nullptr, nullptr, nullptr, nullptr, part, nullptr, nullptr, R, N, 0, ST(stream));
+}
+extern "C" int dtf_bn_finalize(const float* part, const float* gamma, const float* beta, float* mean, float* rstd,
                                float* scale, float* shift, float* run_mean, float* run_var, int N, long long R,
                                float eps, float momentum, void* stream) {
   const float unbias = R > 1 ? (float)R / (float)(R - 1) : 1.f;
-  bn_finalize_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(stats, gamma, beta, mean, rstd, scale, shift, run_mean,
-                                                              run_var, N, 1.f / (float)R, eps, momentum, unbias);
+  bn_finalize_kernel<<<(N + 31) / 32, 1024, 0, ST(stream)>>>(part, dtf_colreduce_blocks(R, N), gamma, beta, mean, rstd,
+                                                            scale, shift, run_mean, run_var, N, 1.f / (float)R, eps,
+                                                            momentum, unbias);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma, const float* beta,
@@ -861,23 +994,28 @@ extern "C" int dtf_bn_fold(const float* run_mean, const float* run_var, const fl
 extern "C" int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift,
                             long long R, int N, int relu, void* stream) {
   if (N % 8) return DTF_ERR_ALIGN;
-  const long long total8 = R * (N / 8);
-  bn_apply_kernel<<<grid_for(total8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)res,
-                                                                 (__nv_bfloat16*)y, scale, shift, total8, N, relu);
+  int gx, gy, rpb;
+  elementwise_geometry(R, N, &gx, &gy, &rpb);
+  bn_apply_kernel<<<dim3(gx, gy), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)res,
+                                                        (__nv_bfloat16*)y, scale, shift, R, N, relu, rpb);
   return DTF_CHECK_LAUNCH();
 }
-// sums[2][N] += {sum dz, sum dz*xhat}; dz (optional output) = relu ? dy*(y>0) : dy
-extern "C" int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* sums,
+// part[blocks][2][N] = per-row-block {sum dz, sum dz*xhat}; dz (optional output) = relu ? dy*(y>0) : dy
+extern "C" int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* part,
                                  const float* mean, const float* rstd, long long R, int N, int relu, void* stream) {
-  return launch_colreduce<3>(dy, y, x, dz, sums, mean, rstd, R, N, relu, ST(stream));
+  return launch_colreduce<3>(dy, y, x, dz, nullptr, part, mean, rstd, R, N, relu, ST(stream));
 }
-extern "C" int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* sums, const float* mean,
-                                const float* rstd, const float* gamma, float* coef, long long R, int N, void* stream) {
+// dx from dz, x and the partial sums; dgamma_acc / dbeta_acc (optional) receive += the parameter gradients.
+extern "C" int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* part, const float* mean,
+                                const float* rstd, const float* gamma, float* coef, float* dgamma_acc,
+                                float* dbeta_acc, long long R, int N, void* stream) {
   if (N % 8) return DTF_ERR_ALIGN;
-  const long long total8 = R * (N / 8);
-  bn_bwd_coef_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(sums, mean, rstd, gamma, coef, N, 1.f / (float)R);
-  bn_bwd_apply_kernel<<<grid_for(total8, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)x,
-                                                                     (__nv_bfloat16*)dx, coef, total8, N);
+  bn_bwd_coef_kernel<<<(N + 31) / 32, 1024, 0, ST(stream)>>>(part, dtf_colreduce_blocks(R, N), mean, rstd, gamma, coef,
+                                                            dgamma_acc, dbeta_acc, N, 1.f / (float)R);
+  int gx, gy, rpb;
+  elementwise_geometry(R, N, &gx, &gy, &rpb);
+  bn_bwd_apply_kernel<<<dim3(gx, gy), 256, 0, ST(stream)>>>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)x,
+                                                            (__nv_bfloat16*)dx, coef, R, N, rpb);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_pool_fwd(const void* x, void* y, void* idx, int n_img, int H, int W, int C, int OH, int OW, int kh,

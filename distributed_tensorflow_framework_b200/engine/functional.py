@@ -258,13 +258,13 @@ class BatchNormFn(torch.autograd.Function):
         gvar, bvar = ctx.gvar, ctx.bvar
         shape = dy.shape
         dy2 = dy.contiguous().view(ctx.rows, -1)
-        dx2, dz2, dgamma, dbeta = raw.bn_bwd(dy2, y2, x2, mean, rstd, gvar.master if gvar is not None else None,
-                                             ctx.relu)
+        # the coefficient kernel adds d gamma / d beta straight into the gradient arena
+        dx2, dz2, _, _ = raw.bn_bwd(dy2, y2, x2, mean, rstd, gvar.master if gvar is not None else None, ctx.relu,
+                                    dgamma_acc=gvar.grad if gvar is not None else None,
+                                    dbeta_acc=bvar.grad if bvar is not None else None)
         if gvar is not None:
-            gvar.grad.add_(dgamma)
             _ready(gvar)
         if bvar is not None:
-            bvar.grad.add_(dbeta)
             _ready(bvar)
         dres = dz2.view(shape) if ctx.has_res else None
         return dx2.view(shape), dres, None, None, None, None, None, None, None, None, None

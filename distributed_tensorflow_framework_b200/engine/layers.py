@@ -217,8 +217,8 @@ def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momen
     configs of BASELINE.json; optionally fused with a residual add and ReLU)."""
     C = x.shape[-1]
     with variable_scope(layer_name):
-        gamma = _get("gamma", [C], ConstantInitializer(1.0), kind="bias")
-        beta = _get("beta", [C], ConstantInitializer(0.0), kind="bias")
+        beta = _get("beta", [C], ConstantInitializer(0.0), kind="bias")  # beta first: [beta | gamma] are adjacent in
+        gamma = _get("gamma", [C], ConstantInitializer(1.0), kind="bias")  # the arenas (see BatchNormFn.backward)
         rm = _get("moving_mean", [C], ConstantInitializer(0.0), trainable=False)
         rv = _get("moving_variance", [C], ConstantInitializer(1.0), trainable=False)
     rows = x.numel() // C

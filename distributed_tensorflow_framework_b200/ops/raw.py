@@ -167,17 +167,20 @@ def lrn_bwd(x, dy, radius=4, bias=1.0, alpha=0.001 / 9.0, beta=0.75):
     return dx
 
 
+def _part(R, N, device):
+    nblk = _lib.lib().dtf_colreduce_blocks(R, N)
+    return torch.empty(nblk, 2, N, device=device, dtype=torch.float32)
+
+
 def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, res=None, relu=False):
     """Training-mode batch norm over rows of x2d [R, N]. Returns (y, mean, rstd)."""
     R, N = x2d.shape
     dev = x2d.device
-    stats = torch.zeros(2, N, device=dev, dtype=torch.float32)
-    _lib.call("dtf_bn_stats", x2d, stats, R, N, _sp())
-    mean = torch.empty(N, device=dev, dtype=torch.float32)
-    rstd = torch.empty_like(mean)
-    scale = torch.empty_like(mean)
-    shift = torch.empty_like(mean)
-    _lib.call("dtf_bn_finalize", stats, gamma, beta, mean, rstd, scale, shift, run_mean, run_var, N, R, eps, momentum,
+    part = _part(R, N, dev)
+    _lib.call("dtf_bn_stats", x2d, part, R, N, _sp())
+    stat = torch.empty(4, N, device=dev, dtype=torch.float32)
+    mean, rstd, scale, shift = stat[0], stat[1], stat[2], stat[3]
+    _lib.call("dtf_bn_finalize", part, gamma, beta, mean, rstd, scale, shift, run_mean, run_var, N, R, eps, momentum,
               _sp())
     y = torch.empty_like(x2d)
     _lib.call("dtf_bn_apply", x2d, res, y, scale, shift, R, N, 1 if relu else 0, _sp())
@@ -194,17 +197,23 @@ def bn_eval_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, res=None, relu=Fa
     return y
 
 
-def bn_bwd(dy2d, y2d, x2d, mean, rstd, gamma, relu=False):
-    """Returns (dx, dz, dgamma, dbeta); dz = masked upstream gradient (also the residual-branch gradient)."""
+def bn_bwd(dy2d, y2d, x2d, mean, rstd, gamma, relu=False, dgamma_acc=None, dbeta_acc=None):
+    """Returns (dx, dz, dgamma, dbeta); dz = masked upstream gradient (also the residual-branch gradient).
+    The parameter gradients are ADDED into dgamma_acc / dbeta_acc (pass gradient-arena views to avoid extra passes);
+    fresh zero buffers are used when they are not given."""
     R, N = x2d.shape
-    sums = torch.zeros(2, N, device=x2d.device, dtype=torch.float32)
+    dev = x2d.device
+    if dgamma_acc is None:
+        acc = torch.zeros(2, N, device=dev, dtype=torch.float32)
+        dgamma_acc, dbeta_acc = acc[0], acc[1]
+    part = _part(R, N, dev)
     dz = torch.empty_like(dy2d) if relu else dy2d
-    _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if relu else None, x2d, dz if relu else None, sums, mean, rstd, R, N,
+    _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if relu else None, x2d, dz if relu else None, part, mean, rstd, R, N,
               1 if relu else 0, _sp())
     dx = torch.empty_like(x2d)
-    coef = torch.empty(3, N, device=x2d.device, dtype=torch.float32)
-    _lib.call("dtf_bn_bwd_apply", dz, x2d, dx, sums, mean, rstd, gamma, coef, R, N, _sp())
-    return dx, dz, sums[1], sums[0]
+    coef = torch.empty(3, N, device=dev, dtype=torch.float32)
+    _lib.call("dtf_bn_bwd_apply", dz, x2d, dx, part, mean, rstd, gamma, coef, dgamma_acc, dbeta_acc, R, N, _sp())
+    return dx, dz, dgamma_acc, dbeta_acc
 
 
 _scratch = {}

@@ -67,19 +67,23 @@ int dtf_relu_bwd_bias_grad(const void* dy, const void* y, void* dz, float* db, l
 
 /* Batch norm over the rows of x[R,N]: per-channel BN uses R = batch*H*W, N = C; the reference's literal
  * batch_norm (moments over axis 0, no affine, eps 1e-3; distribute_tools.py:168-180) uses R = batch, N = H*W*C. */
-int dtf_bn_stats(const void* x, float* stats, long long R, int N, void* stream);
-int dtf_bn_finalize(const float* stats, const float* gamma, const float* beta, float* mean, float* rstd, float* scale,
+/* The column reductions write per-row-block partial sums part[dtf_colreduce_blocks(R,N)][2][N] (no atomics); the
+ * finalize / coefficient kernels add them up in a fixed order, so batch-norm results are bitwise reproducible. */
+int dtf_colreduce_blocks(long long R, int N);
+int dtf_bn_stats(const void* x, float* part, long long R, int N, void* stream);
+int dtf_bn_finalize(const float* part, const float* gamma, const float* beta, float* mean, float* rstd, float* scale,
                     float* shift, float* run_mean, float* run_var, int N, long long R, float eps, float momentum,
                     void* stream);
 int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma, const float* beta, float* scale,
                 float* shift, int N, float eps, void* stream);
 int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift, long long R, int N,
                  int relu, void* stream);
-int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* sums, const float* mean,
+int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* part, const float* mean,
                       const float* rstd, long long R, int N, int relu, void* stream);
-/* coef: [3][N] float workspace (per-channel folded coefficients, written by the call). */
-int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* sums, const float* mean, const float* rstd,
-                     const float* gamma, float* coef, long long R, int N, void* stream);
+/* coef: [3][N] float workspace. dgamma_acc / dbeta_acc (may be NULL) receive += sum dz*xhat / sum dz. */
+int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* part, const float* mean, const float* rstd,
+                     const float* gamma, float* coef, float* dgamma_acc, float* dbeta_acc, long long R, int N,
+                     void* stream);
 
 /* pool (distribute_tools.py:160-165): max / avg, TF SAME semantics via explicit top/left padding. Max pooling
  * records the in-window position of the first maximum (one byte per output element, `idx`) for the backward. */
