@@ -151,9 +151,21 @@ allreduce_optim_kernel(CommCtx c, size_t grad_off, long long start, long long co
 struct Bounds {
   long long b[MAX_RANKS + 1];
 };
+// element ranges whose bf16 weights are NOT pushed to the peers (consumers pull them with K-AG-GEMM instead)
+struct NoPush {
+  int n;
+  long long lo[8], hi[8];
+};
+__device__ __forceinline__ bool in_nopush(const NoPush& np, long long i) {
+  bool hit = false;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (k < np.n && i >= np.lo[k] && i < np.hi[k]) hit = true;
+  return hit;
+}
 __global__ void __launch_bounds__(512)
 rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float* master, float* m, float* v,
-                   size_t shadow_off, size_t master_off) {
+                   size_t shadow_off, size_t master_off, NoPush np) {
   block_barrier(c);
   const long long start = bounds.b[c.rank];
   const long long n4 = (bounds.b[c.rank + 1] - start) >> 2;
@@ -162,9 +174,10 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float
     const float4 g = reduce_peers(c, grad_off, i >> 2);
     const float4 p = optim4(o, master, m, v, i, g);
     const uint2 pb = pack4_bf16(p);
+    const bool local_only = in_nopush(np, i);
 #pragma unroll
     for (int r = 0; r < MAX_RANKS; ++r) {
-      if (r < c.world) {
+      if (r < c.world && (!local_only || r == c.rank)) {
         *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[r] + shadow_off) + i) = pb;
         if (master_off != (size_t)-1 && r != c.rank)
           *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.peer[r] + master_off) + i) = p;
@@ -380,7 +393,7 @@ extern "C" int dtf_comm_allreduce_optim(void* comm, size_t grad_off, long long s
 extern "C" int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long* bounds, int kind, float lr,
                                     float b1, float b2, float eps, float wd, float gscale, long long step,
                                     float* master, float* m, float* v, size_t shadow_off, size_t master_off,
-                                    int blocks, void* stream) {
+                                    int n_nopush, const long long* nopush_ranges, int blocks, void* stream) {
   DtfComm* c = reinterpret_cast<DtfComm*>(comm);
   Bounds b;
   long long maxn = 0;
@@ -392,8 +405,16 @@ extern "C" int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long
   if ((grad_off & 15) || (shadow_off & 15)) return DTF_ERR_ALIGN;
   const OptimArgs o = make_optim(kind, lr, b1, b2, eps, wd, gscale, step);
   const int grid = comm_grid(maxn >> 2, blocks);
+  NoPush np;
+  np.n = 0;
+  if (n_nopush < 0 || n_nopush > 8) return DTF_ERR_ARG;
+  for (int k = 0; k < n_nopush; ++k) {
+    np.lo[k] = nopush_ranges[2 * k];
+    np.hi[k] = nopush_ranges[2 * k + 1];
+    np.n = k + 1;
+  }
   rs_optim_ag_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
-                                                           master_off);
+                                                           master_off, np);
   return DTF_CHECK_LAUNCH();
 }
 // bounds16 in units of 16 bytes relative to buf_off

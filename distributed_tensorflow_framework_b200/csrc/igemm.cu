@@ -65,10 +65,33 @@ struct PixelCoord {
   int n, y, x;
 };
 
+// K-AG-GEMM support: the B operand (weights) is sharded over the ranks of a parameter-server group and is NOT
+// gathered beforehand: the TMA producer picks, per k-block (mode 1: B sharded by rows / K) or per n-tile (mode 2:
+// B sharded by columns / N), the tensor map that points into the OWNER's symmetric heap, so weight tiles cross
+// NVLink straight into shared memory while tcgen05.mma consumes the previous stages.
+struct PeerMaps {
+  CUtensorMap m[8];
+};
+struct AgSel {
+  int mode;          // 0: plain (single map), 1: owner by k-block, 2: owner by n-tile
+  int world;
+  long long unit;    // arena elements covered by one k-block (mode 1) or by one n-tile (mode 2)
+  long long b_off;   // arena element offset of the weight matrix
+  long long bounds[9];
+};
+__device__ __forceinline__ int ag_owner(const AgSel& ag, long long idx) {
+  const long long e = ag.b_off + idx * ag.unit;
+  int o = 0;
+#pragma unroll
+  for (int r = 1; r < 8; ++r)
+    if (r < ag.world && e >= ag.bounds[r]) o = r;
+  return o;
+}
+
 template <int BN, int STAGES, int AMODE>
-__global__ void __launch_bounds__(NUM_THREADS)
-igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-             const IgemmParams p) {
+__device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUtensorMap* tma_b_list, const AgSel& ag,
+                                           const IgemmParams& p) {
+  const CUtensorMap& tma_b = tma_b_list[0];
   using L = SmemLayout<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -384,6 +407,9 @@ igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         const uint32_t ph = (it / STAGES) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
         mbar_arrive_expect_tx(&full_bar[s], kGather ? L::B_BYTES : L::STAGE_BYTES);
+        const CUtensorMap* bmap = tma_b_list;
+        if (ag.mode == 1) bmap = tma_b_list + ag_owner(ag, kb);
+        else if (ag.mode == 2) bmap = tma_b_list + ag_owner(ag, tile_n);
         if constexpr (AMODE == A_TMA_K) {
           tma_load_2d(a_stage(s), &tma_a, &full_bar[s], kb * BLOCK_K, tile_m * BLOCK_M);
         } else if constexpr (AMODE == A_TMA_MN) {
@@ -392,7 +418,7 @@ igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         }
 #pragma unroll
         for (int j = 0; j < BN / 64; ++j)
-          tma_load_2d(b_stage(s) + j * 8192, &tma_b, &full_bar[s], tile_n * BN + j * 64, kb * BLOCK_K);
+          tma_load_2d(b_stage(s) + j * 8192, bmap, &full_bar[s], tile_n * BN + j * 64, kb * BLOCK_K);
       }
     }
     __syncwarp();
@@ -404,6 +430,22 @@ igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     tc_fence_after();
     tmem_dealloc<BN>(tmem_base);
   }
+}
+
+template <int BN, int STAGES, int AMODE>
+__global__ void __launch_bounds__(NUM_THREADS)
+igemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+             const IgemmParams p) {
+  AgSel ag;
+  ag.mode = 0;
+  igemm_body<BN, STAGES, AMODE>(tma_a, &tma_b, ag, p);
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(NUM_THREADS)
+igemm_ag_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ PeerMaps pm,
+                const __grid_constant__ AgSel ag, const IgemmParams p) {
+  igemm_body<BN, STAGES, A_TMA_K>(tma_a, pm.m, ag, p);
 }
 
 // --------------------------------------------------------------------------- SIMT fallback (tiny / unaligned)
@@ -575,4 +617,62 @@ extern "C" int dtf_conv_wgrad_bf16(const void* x, const void* dy, float* dw, int
   p.kb_per_split = (total_kb + splits - 1) / splits;
   const int eff_splits = (total_kb + p.kb_per_split - 1) / p.kb_per_split;
   return dispatch_bn<A_GATHER_MN>(ta, tb, p, eff_splits, stream);
+}
+
+// K-AG-GEMM: C[M,N] = act(A[M,K] * B[K,N] + bias) where B lives SHARDED in the symmetric heaps of a rank group:
+// peer_b[r] is rank r's mapping of the matrix (same offset in every heap), `bounds` (world+1 arena element offsets)
+// gives each rank's owned range and b_arena_off the arena offset of B's first element. shard_by_n = 0: the matrix is
+// the row-major [K,N] weight itself (owner changes along K, boundaries multiples of 64 rows); shard_by_n = 1: the
+// matrix is a transposed shadow [K,N] = W^T of a weight W[N,K] whose owners are row ranges of W, i.e. column ranges
+// here (boundaries multiples of the N tile). No gather pass, no local copy: tiles come over NVLink by TMA.
+extern "C" int dtf_gemm_bf16_ag(const void* A, const void* const* peer_b, void* C, const float* bias, int M, int N,
+                                int K, int lda, int ldb, int ldc, int flags, int world, const long long* bounds,
+                                long long b_arena_off, int shard_by_n, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (world < 1 || world > 8 || M <= 0 || N <= 0 || K <= 0) return DTF_ERR_ARG;
+  if (!aligned16(A) || (lda % 8) || (ldb % 8)) return DTF_ERR_ALIGN;
+  CUtensorMap ta;
+  PeerMaps pm;
+  int rc = make_map_2d(&ta, A, M, K, lda, 128);
+  if (rc) return rc;
+  for (int r = 0; r < world; ++r) {
+    if (!aligned16(peer_b[r])) return DTF_ERR_ALIGN;
+    rc = make_map_2d(&pm.m[r], peer_b[r], K, N, ldb, 64);
+    if (rc) return rc;
+  }
+  for (int r = world; r < 8; ++r) pm.m[r] = pm.m[0];
+  const bool small_n = N <= 64;
+  AgSel ag;
+  ag.mode = shard_by_n ? 2 : 1;
+  ag.world = world;
+  ag.b_off = b_arena_off;
+  // mode 1: one k-block = 64 rows of B = 64*ldb elements of W. mode 2: one n-tile = BN columns of W^T = BN rows of W,
+  // and a row of W has K elements (W is [N, K] row-major with leading dimension K).
+  ag.unit = shard_by_n ? (long long)(small_n ? 64 : 128) * K : (long long)BLOCK_K * ldb;
+  for (int r = 0; r <= 8; ++r) ag.bounds[r] = bounds[r <= world ? r : world];
+  IgemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.out = C; p.ldc = ldc; p.bias = bias; p.relu = flags & 1; p.out_fp32 = (flags >> 1) & 1; p.atomic = 0;
+  p.kb_per_split = (K + BLOCK_K - 1) / BLOCK_K;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  static bool attr64[64] = {}, attr128[64] = {};
+  if (small_n) {
+    using L = SmemLayout<64, 4>;
+    auto kern = igemm_ag_kernel<64, 4>;
+    if (!attr64[dev & 63]) {
+      if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) != cudaSuccess) return DTF_ERR_CUDA;
+      attr64[dev & 63] = true;
+    }
+    kern<<<dim3(1, (M + BLOCK_M - 1) / BLOCK_M, 1), NUM_THREADS, L::TOTAL, stream>>>(ta, pm, ag, p);
+  } else {
+    using L = SmemLayout<128, 3>;
+    auto kern = igemm_ag_kernel<128, 3>;
+    if (!attr128[dev & 63]) {
+      if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) != cudaSuccess) return DTF_ERR_CUDA;
+      attr128[dev & 63] = true;
+    }
+    kern<<<dim3((N + 127) / 128, (M + BLOCK_M - 1) / BLOCK_M, 1), NUM_THREADS, L::TOTAL, stream>>>(ta, pm, ag, p);
+  }
+  return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }

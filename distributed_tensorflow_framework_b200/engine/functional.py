@@ -121,7 +121,11 @@ class LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w_shadow, b_shadow, wvar, bvar, relu, out_fp32):
         w = w_shadow.detach()
-        y = raw.gemm(x, w, bvar.master if bvar is not None else None, relu=relu, out_fp32=out_fp32)
+        ag = getattr(wvar, "ag", None)
+        if ag is not None:  # parameter-server pull fused into this GEMM: weight tiles come from their owners
+            y = raw.gemm_ag(x, ag, False, bvar.master if bvar is not None else None, relu=relu, out_fp32=out_fp32)
+        else:
+            y = raw.gemm(x, w, bvar.master if bvar is not None else None, relu=relu, out_fp32=out_fp32)
         ctx.wvar, ctx.bvar, ctx.relu = wvar, bvar, relu
         ctx.save_for_backward(x, y if relu else None)
         ctx.x_needs_grad = x.requires_grad
@@ -155,7 +159,11 @@ class LinearFn(torch.autograd.Function):
             _ready(bvar)
         dx = None
         if ctx.x_needs_grad:
-            dx = raw.gemm(dz, wvar.shadow_t)  # dz @ W^T, W^T stored [out, in]
+            ag = getattr(wvar, "ag", None)
+            if ag is not None:
+                dx = raw.gemm_ag(dz, ag, True)
+            else:
+                dx = raw.gemm(dz, wvar.shadow_t)  # dz @ W^T, W^T stored [out, in]
         return dx, None, None, None, None, None, None
 
 

@@ -38,6 +38,27 @@ def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=No
     return out
 
 
+def gemm_ag(a, ag, transposed_shadow, bias=None, relu=False, out_fp32=False):
+    """K-AG-GEMM: act(A @ B + bias) with B pulled tile by tile from the owners' heaps (see dtf_gemm_bf16_ag).
+    `ag`: dict(world, bounds, off, peers=[ptr per rank], peers_t=[...], shape=(in, out)) attached to an FC variable."""
+    import ctypes
+    M, K = a.shape
+    fin, fout = ag["shape"]
+    if transposed_shadow:  # B = W^T [out, in]
+        assert K == fout
+        N, ptrs = fin, ag["peers_t"]
+    else:
+        assert K == fin
+        N, ptrs = fout, ag["peers"]
+    out = torch.empty((M, N), device=a.device, dtype=torch.float32 if out_fp32 else bf16)
+    arr = (ctypes.c_void_p * ag["world"])(*ptrs)
+    bounds = (ctypes.c_longlong * 9)(*(list(ag["bounds"]) + [ag["bounds"][-1]] * (9 - len(ag["bounds"]))))
+    flags = (1 if relu else 0) | (2 if out_fp32 else 0)
+    _lib.call("dtf_gemm_bf16_ag", a, arr, out, bias, M, N, K, a.stride(0), N, out.stride(0), flags, ag["world"],
+              bounds, ag["off"], 1 if transposed_shadow else 0, _sp())
+    return out
+
+
 def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False):
     n, H, W, C = x.shape
     n_out = w2d.shape[1]

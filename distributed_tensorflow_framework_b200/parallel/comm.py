@@ -106,12 +106,19 @@ class Communicator(object):
                   1, None, None, None, None, out, self.blocks, self._s(stream))
 
     def rs_optim_ag(self, grad_off, bounds, opt, step, master, m, v, shadow_off, master_off=None, gscale=None,
-                    stream=None):
-        """K-RS-OPT: reduce-scatter into the owner shard + owner update + all-gather of bf16 weights by stores."""
+                    stream=None, nopush=()):
+        """K-RS-OPT: reduce-scatter into the owner shard + owner update + all-gather of bf16 weights by stores.
+        `nopush`: up to 8 (lo, hi) element ranges that stay owner-local (pulled later by K-AG-GEMM)."""
         gscale = 1.0 / self.world if gscale is None else gscale
         b = (ctypes.c_longlong * (self.world + 1))(*bounds)
+        flat = [x for r in nopush for x in r]
+        npr = (ctypes.c_longlong * max(len(flat), 1))(*flat) if flat else None
         _lib.call("dtf_comm_rs_optim_ag", self.handle, grad_off, b, *self._opt_args(opt, step, gscale), master, m, v,
-                  shadow_off, (1 << 64) - 1 if master_off is None else master_off, self.blocks, self._s(stream))
+                  shadow_off, (1 << 64) - 1 if master_off is None else master_off, len(nopush), npr, self.blocks,
+                  self._s(stream))
+
+    def peer_ptr(self, r):
+        return _lib.lib().dtf_comm_peer_ptr(self.handle, r)
 
     def allgather_slices(self, buf_off, bounds16, stream=None):
         b = (ctypes.c_longlong * (self.world + 1))(*bounds16)
@@ -165,6 +172,9 @@ class GradientEngine(object):
         self.overlap = overlap and algo in ("oneshot", "nccl")
         self.comm = None
         self.heap = None
+        self.pull = algo == "twoshot_pull"
+        if self.pull:
+            algo = self.algo = "twoshot"
         use_heap = algo in ("oneshot", "twoshot", "async")
         if use_heap:
             mailbox = n_est * 4 * 1 if algo == "async" else 0
@@ -176,6 +186,9 @@ class GradientEngine(object):
                 self.slice_cap = (per + 3) // 4 * 4
                 self.mailbox = self.heap.alloc("mailbox", self.slice_cap * world, torch.float32)
             self.comm = Communicator(self.heap, rank, world, group)
+            self.nopush = []
+            if self.pull and world > 1:
+                self._setup_pull()
         else:
             store.finalize(placement=placement, world=world, slots=optimizer.num_slots())
         self.n = store.n_params
@@ -203,6 +216,33 @@ class GradientEngine(object):
         if self.overlap:
             store.grad_ready_hook = self._on_grad_ready
         self.kernel_launches = 0
+
+    def _setup_pull(self):
+        """Parameter-server PULL fused into the consumer (K-AG-GEMM): large FC weights are not broadcast after the
+        owner update; the forward / dX GEMMs read each tile from its owner's heap. Owner boundaries that fall inside
+        such a matrix are snapped to multiples of 128 weight rows so that every k-block / n-tile has one owner."""
+        st = self.store
+        fcs = [v for v in st.trainable_variables() if v.kind == "fc_w" and v.store_shape[0] % 128 == 0
+               and v.store_shape[1] % 8 == 0 and v.numel >= (1 << 16)][:8]
+        if not fcs:
+            return
+        bounds = list(st.owner_bounds)
+        for v in fcs:
+            fin, fout = v.store_shape
+            unit = 128 * fout
+            for i in range(1, self.world):
+                if v.offset < bounds[i] < v.offset + v.numel:
+                    k = int(round((bounds[i] - v.offset) / float(unit)))
+                    bounds[i] = v.offset + min(max(k, 0), fin // 128) * unit
+        for i in range(1, self.world + 1):
+            bounds[i] = max(bounds[i], bounds[i - 1])
+        st.owner_bounds = bounds
+        sh_off, sht_off = self.heap.offset_of("shadow"), self.heap.offset_of("shadow_t")
+        for v in fcs:
+            v.ag = dict(world=self.world, bounds=bounds, off=v.offset, shape=tuple(v.store_shape),
+                        peers=[self.comm.peer_ptr(r) + sh_off + 2 * v.offset for r in range(self.world)],
+                        peers_t=[self.comm.peer_ptr(r) + sht_off + 2 * v.offset for r in range(self.world)])
+            self.nopush.append((v.offset, v.offset + v.numel))
 
     # ------------------------------------------------------------------ per-step protocol
     def begin_step(self, step):
@@ -265,7 +305,7 @@ class GradientEngine(object):
             elif self.algo == "twoshot":
                 self.comm.rs_optim_ag(self.heap.offset_of("grad"), st.owner_bounds, opt, step, st.master_arena,
                                       st.slot_m, st.slot_v, self.heap.offset_of("shadow"),
-                                      stream=self.comm_stream)
+                                      stream=self.comm_stream, nopush=self.nopush)
             elif self.algo == "async":
                 self.comm.async_push(self.heap.offset_of("grad"), self.heap.offset_of("mailbox"), self.slice_cap,
                                      st.owner_bounds, stream=self.comm_stream)
@@ -273,6 +313,10 @@ class GradientEngine(object):
                                       st.master_arena, st.slot_m, st.slot_v, self.heap.offset_of("shadow"),
                                       stream=self.comm_stream)
             st.refresh_transposed_shadows()
+            if self.algo == "twoshot" and self.nopush:
+                # peers pull the (transposed) shadows of these matrices from their owners: every rank must have
+                # refreshed its own columns before anybody's next forward / backward starts
+                self.comm.barrier(stream=self.comm_stream)
         cur.wait_stream(self.comm_stream)
         st.global_step = step
 

@@ -34,6 +34,15 @@ extern "C" {
 int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
                   int ldc, int flags, void* stream);
 
+/* K-AG-GEMM: the all-gather of parameter-server weights fused into the consuming GEMM. B is sharded over the heaps
+ * of `world` ranks (peer_b[r] = rank r's mapping of the matrix, `bounds` = owned arena ranges, b_arena_off = arena
+ * offset of the matrix); the TMA producer reads every tile from its OWNER over NVLink, no gather pass and no local
+ * copy. shard_by_n 0: owners are row (K) ranges, multiples of 64 rows; 1: owners are column (N) ranges of a
+ * transposed shadow, multiples of the N tile. Replaces the ps->worker variable pull (distribute_train.py:109-110). */
+int dtf_gemm_bf16_ag(const void* A, const void* const* peer_b, void* C, const float* bias, int M, int N, int K, int lda,
+                     int ldb, int ldc, int flags, int world, const long long* bounds, long long b_arena_off,
+                     int shard_by_n, void* stream);
+
 /* Implicit-GEMM convolution on NHWC bf16. geo 0: forward conv (gather from x[n_img,H,W,C], output pixel grid PHxPW);
  * geo 1: data gradient / transposed conv (gather from dy[n_img,H,W,C], output grid PHxPW is the input image grid).
  * W2d is the row-major [KH*KW*C, n_out] filter matrix. flags: bit0 relu, bit1 fp32 output.
@@ -156,11 +165,12 @@ int dtf_comm_allreduce_optim(void* comm, size_t grad_off, long long start, long 
                              float b1, float b2, float eps, float wd, float gscale, long long step, float* master,
                              float* m, float* v, void* shadow, float* avg_out, int blocks, void* stream);
 /* K-RS-OPT: reduce-scatter into the owner shard fused with the owner-side optimizer, then all-gather of the new
- * bf16 weights (and optionally fp32 masters) by peer stores. Replaces the worker->ps push, ps-side apply and
+ * bf16 weights (except the `nopush_ranges` [lo,hi) element ranges, which consumers pull with dtf_gemm_bf16_ag) (and optionally fp32 masters) by peer stores. Replaces the worker->ps push, ps-side apply and
  * ps->worker pull of SyncReplicasOptimizer / replica_device_setter (distribute_train.py:109-110,146-158). */
 int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long* bounds, int kind, float lr, float b1, float b2,
                          float eps, float wd, float gscale, long long step, float* master, float* m, float* v,
-                         size_t shadow_off, size_t master_off, int blocks, void* stream);
+                         size_t shadow_off, size_t master_off, int n_nopush, const long long* nopush_ranges, int blocks,
+                         void* stream);
 int dtf_comm_allgather_slices(void* comm, size_t buf_off, const long long* bounds16, int blocks, void* stream);
 /* K-ASYNC-PUSH / owner apply: asynchronous parameter-server mode (extension; the reference is sync-only,
  * distribute_train.py:151). */

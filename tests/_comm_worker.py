@@ -113,7 +113,8 @@ def main():
     dist.barrier()
 
     # ---- Trainer level: data-parallel CIFAR CNN, every algorithm
-    for algo in ("oneshot", "twoshot", "nccl", "async"):
+    curves = {}
+    for algo in ("oneshot", "twoshot", "twoshot_pull", "nccl", "async"):
         torch.manual_seed(100 + rank)
         x = torch.rand(32, 32, 32, 3)
         y = torch.randint(0, 10, (32,))
@@ -123,9 +124,14 @@ def main():
         losses = [float(tr.step((x, y))) for _ in range(12)]
         check(all(l == l for l in losses), "%s: NaN loss" % algo)
         check(losses[-1] < losses[0], "%s: loss did not decrease %s" % (algo, losses))
+        curves[algo] = losses
+        if algo == "twoshot_pull":
+            check(len(tr.engine.nopush) == 2, "pull mode should cover local3 and local4 weights")
+            diff = max(abs(a - b) for a, b in zip(losses, curves["twoshot"]))
+            check(diff < 2e-2, "K-AG-GEMM pull path deviates from the push path: %s vs %s" % (losses, curves["twoshot"]))
         torch.cuda.synchronize()
         dist.barrier()
-        if algo != "async":
+        if algo not in ("async", "twoshot_pull"):
             sh = tr.store.shadow_arena
             g = [torch.empty_like(sh) for _ in range(world)]
             dist.all_gather(g, sh)
