@@ -1,0 +1,297 @@
+// K-CONV (halo variant): stride-1 KxK convolution (fprop and data gradient) on NHWC bf16 with C % 64 == 0.
+//
+// The gather kernel of igemm.cu re-reads every input pixel KH*KW times through L2. Here a CTA owns R whole image
+// rows; ONE 4-D TMA load brings the (R+KH-1) x (W+KW-1) x 64-channel halo tile into shared memory (TMA zero-fills
+// the SAME padding), laid out as a linear array of 128-byte pixel rows with row pitch Wp = W+KW-1. In that "padded
+// linear" space the GEMM row of output pixel (y, x) is m = (y-y0)*Wp + x and the input it needs for filter tap
+// (kh, kw) sits at m + kh*Wp + kw: every tap is the SAME shared-memory buffer viewed at a different start address.
+// So the A operand of all KH*KW taps is one smem tile, consumed by tcgen05.mma through shifted descriptors; only the
+// small weight tiles stream per tap. Rows with x >= W are padding rows of the GEMM and are dropped in the epilogue.
+// The data gradient is the same kernel on dy with per-tap-transposed filters and mirrored tap shifts.
+//
+// Replaces tf.nn.conv2d / its input gradient for 3x3 layers (/root/reference/distribute_tools.py:69-121).
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include "ptx.cuh"
+#include "dtf_internal.h"
+
+namespace dtf {
+namespace halo {
+
+constexpr int BLOCK_M = 128;
+constexpr int NUM_THREADS = 192;  // warps 0-3 epilogue, warp 4 MMA, warp 5 TMA
+constexpr int A_STAGES = 2;
+
+struct Params {
+  int n_img, H, W, C, n_out;
+  int KH, KW;
+  int Wp;            // W + KW - 1
+  int R;             // image rows per tile
+  int tiles_per_img;
+  int org_x, org_y;  // halo origin relative to the first output row of the tile (fprop: -pad_w, -pad_h)
+  int mirror;        // 1: data gradient (tap shifts mirrored)
+  int a_stage_bytes;
+  int a_tx_bytes;
+  int base_off_mode;
+  void* out;
+  const float* bias;
+  int relu;
+};
+
+template <int BN, int B_STAGES>
+__global__ void __launch_bounds__(NUM_THREADS)
+conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int B_BYTES = BN * 64 * 2;
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t a_base = smem_base;
+  const uint32_t b_base = smem_base + A_STAGES * p.a_stage_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + A_STAGES * p.a_stage_bytes + B_STAGES * B_BYTES);
+  uint64_t* a_full = bars;
+  uint64_t* a_empty = a_full + A_STAGES;
+  uint64_t* b_full = a_empty + A_STAGES;
+  uint64_t* b_empty = b_full + B_STAGES;
+  uint64_t* tmem_full = b_empty + B_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile_n = blockIdx.x;
+  const int img = blockIdx.y / p.tiles_per_img;
+  const int y0 = (blockIdx.y - img * p.tiles_per_img) * p.R;
+  const int ntaps = p.KH * p.KW;
+  const int ncblk = p.C >> 6;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < A_STAGES; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
+    }
+    for (int s = 0; s < B_STAGES; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 4) tmem_alloc<BN>(tmem_slot);
+  if (warp == 5 && lane == 0) {
+    tma_prefetch_desc(&tma_x);
+    tma_prefetch_desc(&tma_w);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 5) {
+    if (lane == 0) {
+      int bit = 0;
+      for (int cb = 0; cb < ncblk; ++cb) {
+        const int as = cb % A_STAGES;
+        mbar_wait(&a_empty[as], ((cb / A_STAGES) & 1) ^ 1);
+        mbar_arrive_expect_tx(&a_full[as], p.a_tx_bytes);
+        tma_load_4d(a_base + as * p.a_stage_bytes, &tma_x, &a_full[as], cb * 64, p.org_x, y0 + p.org_y, img);
+        for (int t = 0; t < ntaps; ++t, ++bit) {
+          const int bs = bit % B_STAGES;
+          mbar_wait(&b_empty[bs], ((bit / B_STAGES) & 1) ^ 1);
+          mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)
+            tma_load_2d(b_base + bs * B_BYTES + j * 8192, &tma_w, &b_full[bs], tile_n * BN + j * 64, t * p.C + cb * 64);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 4) {
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, /*a_mn=*/false, /*b_mn=*/true);
+    int bit = 0;
+    for (int cb = 0; cb < ncblk; ++cb) {
+      const int as = cb % A_STAGES;
+      mbar_wait(&a_full[as], (cb / A_STAGES) & 1);
+      for (int t = 0; t < ntaps; ++t, ++bit) {
+        const int bs = bit % B_STAGES;
+        mbar_wait(&b_full[bs], (bit / B_STAGES) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+          int kh = t / p.KW, kw = t - kh * p.KW;
+          if (p.mirror) {
+            kh = p.KH - 1 - kh;
+            kw = p.KW - 1 - kw;
+          }
+          const uint32_t a_tap = a_base + as * p.a_stage_bytes + (uint32_t)(kh * p.Wp + kw) * 128u;
+          const uint32_t boff = p.base_off_mode ? ((a_tap >> 7) & 7u) : 0u;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t adesc = make_smem_desc_off(a_tap + k * 32, 16, 1024, boff);
+            const uint64_t bdesc = make_smem_desc(b_base + bs * B_BYTES + k * 2048, 8192, 1024);
+            umma_bf16(tmem_base, adesc, bdesc, idesc, (bit > 0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&b_empty[bs]);
+          if (t == ntaps - 1) umma_commit(&a_empty[as]);
+        }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) umma_commit(tmem_full);
+    __syncwarp();
+  } else {
+    // epilogue: GEMM row m -> (y, x) in the padded-linear space of this tile
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const int m = threadIdx.x;
+    const int ry = m / p.Wp;
+    const int x = m - ry * p.Wp;
+    const int y = y0 + ry;
+    const bool valid = (ry < p.R) && (x < p.W) && (y < p.H);
+    const size_t pix = ((size_t)img * p.H + y) * p.W + x;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 32; ++cc) {
+      uint32_t v[32];
+      tmem_ld32(lane_addr + cc * 32, v);
+      tmem_ld_wait();
+      const int n0 = tile_n * BN + cc * 32;
+      if (valid && n0 < p.n_out) {
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.n_out) f[j] += __ldg(p.bias + n0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + pix * p.n_out + n0;
+        if (n0 + 32 <= p.n_out) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 q;
+            q.x = pack_bf16x2(f[j], f[j + 1]);
+            q.y = pack_bf16x2(f[j + 2], f[j + 3]);
+            q.z = pack_bf16x2(f[j + 4], f[j + 5]);
+            q.w = pack_bf16x2(f[j + 6], f[j + 7]);
+            *reinterpret_cast<uint4*>(o + j) = q;
+          }
+        } else {
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.n_out) o[j] = __float2bfloat16(f[j]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<BN>(tmem_base);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(sym);
+  return fn;
+}
+
+template <int BN, int B_STAGES>
+static int launch(const CUtensorMap& tx, const CUtensorMap& tw, const Params& p, cudaStream_t stream) {
+  const int smem = A_STAGES * p.a_stage_bytes + B_STAGES * BN * 128 + 256 + 1024;
+  if (smem > 227 * 1024) return DTF_ERR_TOO_LARGE;
+  auto kern = conv_halo_kernel<BN, B_STAGES>;
+  static int attr[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr[dev & 63] < smem) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return DTF_ERR_CUDA;
+    attr[dev & 63] = smem;
+  }
+  dim3 grid((p.n_out + BN - 1) / BN, p.n_img * p.tiles_per_img);
+  kern<<<grid, NUM_THREADS, smem, stream>>>(tx, tw, p);
+  return DTF_CHECK_LAUNCH();
+}
+
+}  // namespace halo
+}  // namespace dtf
+
+using namespace dtf;
+
+// 1 if dtf_conv_halo_bf16 supports the geometry (stride 1, C % 64 == 0, tile utilisation >= 70 %).
+extern "C" int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int n_out) {
+  if ((C & 63) || (n_out & 7) || KH * KW < 2 || KH > 7 || KW > 7) return 0;
+  const int Wp = W + KW - 1;
+  if (Wp > 128) return 0;
+  int R = 128 / Wp;
+  if (R > H) R = H;
+  if (R < 1) return 0;
+  const int tiles = (H + R - 1) / R;
+  const double util = (double)(H * W) / (double)(tiles * 128);
+  if (util < 0.70) return 0;
+  if ((R + KH - 1) > 256) return 0;
+  return 1;
+}
+
+// src: x (fprop) or dy (mirror = 1, data gradient) [n_img, H, W, C]; W2d: [KH*KW*C, n_out] row-major bf16 (HWIO for
+// fprop, per-tap transposed filters for the gradient); out [n_img, H, W, n_out] bf16. SAME padding, stride 1.
+// flags: bit0 relu, bit8 use the descriptor base-offset field for the shifted tap views.
+extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H,
+                                  int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags,
+                                  void* stream_) {
+  using namespace dtf::halo;
+  if (!dtf_conv_halo_supported(H, W, C, KH, KW, n_out)) return DTF_ERR_UNSUPPORTED;
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return DTF_ERR_DRIVER;
+  Params p{};
+  p.n_img = n_img; p.H = H; p.W = W; p.C = C; p.n_out = n_out; p.KH = KH; p.KW = KW;
+  p.Wp = W + KW - 1;
+  p.R = 128 / p.Wp;
+  if (p.R > H) p.R = H;
+  p.tiles_per_img = (H + p.R - 1) / p.R;
+  p.mirror = mirror;
+  p.org_x = mirror ? -(KW - 1 - pad_w) : -pad_w;
+  p.org_y = mirror ? -(KH - 1 - pad_h) : -pad_h;
+  const int halo_rows = p.R + KH - 1;
+  p.a_tx_bytes = halo_rows * p.Wp * 128;
+  const int span = (128 + (KH - 1) * p.Wp + (KW - 1)) * 128;
+  p.a_stage_bytes = ((span > p.a_tx_bytes ? span : p.a_tx_bytes) + 1023) & ~1023;
+  p.base_off_mode = (flags >> 8) & 1;
+  p.out = out; p.bias = bias; p.relu = flags & 1;
+  CUtensorMap tx, tw;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n_img};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.Wp, (cuuint32_t)halo_rows, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    if (fn(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(src), dims, strides, box, es,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return DTF_ERR_TENSORMAP;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)n_out, (cuuint64_t)KH * KW * C};
+    cuuint64_t strides[1] = {(cuuint64_t)n_out * 2};
+    cuuint32_t box[2] = {64, 64};
+    cuuint32_t es[2] = {1, 1};
+    if (fn(&tw, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(W2d), dims, strides, box, es,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return DTF_ERR_TENSORMAP;
+  }
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (n_out <= 64) return launch<64, 4>(tx, tw, p, stream);
+  return launch<128, 4>(tx, tw, p, stream);
+}

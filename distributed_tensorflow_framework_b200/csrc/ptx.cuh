@@ -169,3 +169,20 @@ __device__ __forceinline__ void red_add_f32(float* addr, float v) {
 }
 
 }  // namespace dtf
+
+namespace dtf {
+__device__ __forceinline__ void tma_load_4d(uint32_t dst_smem, const void* tmap, uint64_t* bar, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];\n" ::
+          "r"(dst_smem),
+      "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+// Same as make_smem_desc but for a start address that is only 128-byte aligned inside the 1024-byte swizzle pattern:
+// the 3-bit "matrix base offset" field (bits 49..51) carries (addr >> 7) & 7.
+__device__ __forceinline__ uint64_t make_smem_desc_off(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                       uint32_t base_offset) {
+  return make_smem_desc(smem_addr, lbo_bytes, sbo_bytes) | (static_cast<uint64_t>(base_offset & 7) << 49);
+}
+}  // namespace dtf

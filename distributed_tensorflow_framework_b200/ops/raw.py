@@ -9,6 +9,7 @@ import torch
 from . import _lib
 
 bf16 = torch.bfloat16
+USE_HALO = True  # stride-1 KxK convolutions with C % 64 == 0 use the halo-tile kernel (csrc/conv_halo.cu)
 
 
 def same_pad(in_size, k, stride):
@@ -67,6 +68,10 @@ def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False):
     OH, pt = same_pad(H, KH, stride)
     OW, pl = same_pad(W, KW, stride)
     out = torch.empty((n, OH, OW, n_out), device=x.device, dtype=torch.float32 if out_fp32 else bf16)
+    if stride == 1 and not out_fp32 and USE_HALO and _lib.lib().dtf_conv_halo_supported(H, W, C, KH, KW, n_out):
+        # halo-tile kernel: one TMA load per tile, all taps are shifted views of the same shared-memory tile
+        _lib.call("dtf_conv_halo_bf16", x, w2d, out, bias, n, H, W, C, KH, KW, n_out, pt, pl, 0, 1 if relu else 0, _sp())
+        return out
     flags = (1 if relu else 0) | (2 if out_fp32 else 0)
     _lib.call("dtf_conv_igemm_bf16", x, w2d, out, bias, n, H, W, C, OH, OW, KH, KW, n_out, stride, pt, pl, 0, flags,
               _sp())
@@ -83,6 +88,9 @@ def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False):
     _, pt = same_pad(H, KH, stride)
     _, pl = same_pad(W, KW, stride)
     dx = torch.empty((n, H, W, Ci), device=dy.device, dtype=bf16)
+    if stride == 1 and USE_HALO and _lib.lib().dtf_conv_halo_supported(H, W, Co, KH, KW, Ci):
+        _lib.call("dtf_conv_halo_bf16", dy, w2d_t, dx, bias, n, H, W, Co, KH, KW, Ci, pt, pl, 1, 1 if relu else 0, _sp())
+        return dx
     _lib.call("dtf_conv_igemm_bf16", dy, w2d_t, dx, bias, n, OH, OW, Co, H, W, KH, KW, Ci, stride, pt, pl, 1,
               1 if relu else 0, _sp())
     return dx

@@ -51,6 +51,14 @@ int dtf_conv_igemm_bf16(const void* src, const void* W2d, void* out, const float
                         int C, int PH, int PW, int KH, int KW, int n_out, int stride, int pad_h, int pad_w, int geo,
                         int flags, void* stream);
 
+/* Halo-tile convolution (csrc/conv_halo.cu): stride-1 KxK conv / data gradient with C % 64 == 0. One 4-D TMA load per
+ * (tile, 64-channel block) brings a zero-padded halo into shared memory and all KH*KW taps are shifted tcgen05
+ * descriptor views of it (KH*KW times less L2 traffic than the gather kernel). mirror = 1: data gradient with
+ * per-tap transposed filters. flags: bit0 relu, bit8 descriptor base-offset mode. */
+int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int n_out);
+int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H, int W, int C,
+                       int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags, void* stream);
+
 /* Filter gradient dW[KH*KW*C, n_out] (fp32, red.add accumulated; zero it first) from x[n_img,H,W,C] and
  * dy[n_img,PH,PW,n_out]. Backward of the conv layers above (TF autodiff, distribute_tower.py:26-27). */
 int dtf_conv_wgrad_bf16(const void* x, const void* dy, float* dw, int n_img, int H, int W, int C, int PH, int PW,
