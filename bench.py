@@ -51,7 +51,7 @@ class ClockSampler(object):
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu_index)], stdout=subprocess.PIPE,
+                                          "-lms", "20", "-i", str(self.gpu_index)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -65,6 +65,9 @@ class ClockSampler(object):
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        t0 = time.time()
+        while not self.lines and time.time() - t0 < 1.0:  # very short timed regions: wait for the first sample
+            time.sleep(0.02)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -227,7 +230,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch_nccl"])
-    ap.add_argument("--config", default=os.environ.get("DTF_BENCH_CONFIG", "cifar10"), choices=sorted(CONFIGS))
+    ap.add_argument("--config", default=os.environ.get("DTF_BENCH_CONFIG", "resnet50"), choices=sorted(CONFIGS))
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the config's)")
     ap.add_argument("--algo", default="auto")
     ap.add_argument("--no-graph", action="store_true")

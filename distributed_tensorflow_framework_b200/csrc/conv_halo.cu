@@ -27,8 +27,10 @@ constexpr int A_STAGES = 2;
 struct Params {
   int n_img, H, W, C, n_out;
   int KH, KW;
-  int Wp;            // W + KW - 1
+  int Wp;            // Wt + KW - 1: row pitch of the padded-linear tile space
+  int Wt;            // output columns per tile
   int R;             // image rows per tile
+  int tiles_x;       // tiles along the image width
   int tiles_per_img;
   int org_x, org_y;  // halo origin relative to the first output row of the tile (fprop: -pad_w, -pad_h)
   int mirror;        // 1: data gradient (tap shifts mirrored)
@@ -60,7 +62,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tile_n = blockIdx.x;
   const int img = blockIdx.y / p.tiles_per_img;
-  const int y0 = (blockIdx.y - img * p.tiles_per_img) * p.R;
+  const int t_in_img = blockIdx.y - img * p.tiles_per_img;
+  const int y0 = (t_in_img / p.tiles_x) * p.R;
+  const int x0 = (t_in_img % p.tiles_x) * p.Wt;
   const int ntaps = p.KH * p.KW;
   const int ncblk = p.C >> 6;
 
@@ -93,7 +97,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
         const int as = cb % A_STAGES;
         mbar_wait(&a_empty[as], ((cb / A_STAGES) & 1) ^ 1);
         mbar_arrive_expect_tx(&a_full[as], p.a_tx_bytes);
-        tma_load_4d(a_base + as * p.a_stage_bytes, &tma_x, &a_full[as], cb * 64, p.org_x, y0 + p.org_y, img);
+        tma_load_4d(a_base + as * p.a_stage_bytes, &tma_x, &a_full[as], cb * 64, x0 + p.org_x, y0 + p.org_y, img);
         for (int t = 0; t < ntaps; ++t, ++bit) {
           const int bs = bit % B_STAGES;
           mbar_wait(&b_empty[bs], ((bit / B_STAGES) & 1) ^ 1);
@@ -143,9 +147,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     tc_fence_after();
     const int m = threadIdx.x;
     const int ry = m / p.Wp;
-    const int x = m - ry * p.Wp;
+    const int xx = m - ry * p.Wp;
+    const int x = x0 + xx;
     const int y = y0 + ry;
-    const bool valid = (ry < p.R) && (x < p.W) && (y < p.H);
+    const bool valid = (ry < p.R) && (xx < p.Wt) && (x < p.W) && (y < p.H);
     const size_t pix = ((size_t)img * p.H + y) * p.W + x;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
 #pragma unroll 1
@@ -230,19 +235,33 @@ static int launch(const CUtensorMap& tx, const CUtensorMap& tw, const Params& p,
 
 using namespace dtf;
 
-// 1 if dtf_conv_halo_bf16 supports the geometry (stride 1, C % 64 == 0, tile utilisation >= 70 %).
+// Choose the tile shape (Wt output columns x R rows, (Wt+KW-1)*R <= 128 GEMM rows) with the best utilisation.
+static double halo_plan(int H, int W, int KH, int KW, int* Wt_out, int* R_out) {
+  double best = 0.0;
+  int bw = 0, br = 0;
+  for (int Wt = 1; Wt <= W && Wt + KW - 1 <= 128; ++Wt) {
+    const int Wp = Wt + KW - 1;
+    int R = 128 / Wp;
+    if (R > H) R = H;
+    if (R < 1 || R + KH - 1 > 256) continue;
+    const long long tiles = (long long)((W + Wt - 1) / Wt) * ((H + R - 1) / R);
+    const double util = (double)H * W / (double)(tiles * 128);
+    if (util > best + 1e-9) {
+      best = util;
+      bw = Wt;
+      br = R;
+    }
+  }
+  *Wt_out = bw;
+  *R_out = br;
+  return best;
+}
+
+// 1 if dtf_conv_halo_bf16 supports the geometry (stride 1, C % 64 == 0, tile utilisation >= 60 %).
 extern "C" int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int n_out) {
   if ((C & 63) || (n_out & 7) || KH * KW < 2 || KH > 7 || KW > 7) return 0;
-  const int Wp = W + KW - 1;
-  if (Wp > 128) return 0;
-  int R = 128 / Wp;
-  if (R > H) R = H;
-  if (R < 1) return 0;
-  const int tiles = (H + R - 1) / R;
-  const double util = (double)(H * W) / (double)(tiles * 128);
-  if (util < 0.70) return 0;
-  if ((R + KH - 1) > 256) return 0;
-  return 1;
+  int Wt, R;
+  return halo_plan(H, W, KH, KW, &Wt, &R) >= 0.60 ? 1 : 0;
 }
 
 // src: x (fprop) or dy (mirror = 1, data gradient) [n_img, H, W, C]; W2d: [KH*KW*C, n_out] row-major bf16 (HWIO for
@@ -257,10 +276,10 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
   if (!fn) return DTF_ERR_DRIVER;
   Params p{};
   p.n_img = n_img; p.H = H; p.W = W; p.C = C; p.n_out = n_out; p.KH = KH; p.KW = KW;
-  p.Wp = W + KW - 1;
-  p.R = 128 / p.Wp;
-  if (p.R > H) p.R = H;
-  p.tiles_per_img = (H + p.R - 1) / p.R;
+  halo_plan(H, W, KH, KW, &p.Wt, &p.R);
+  p.Wp = p.Wt + KW - 1;
+  p.tiles_x = (W + p.Wt - 1) / p.Wt;
+  p.tiles_per_img = p.tiles_x * ((H + p.R - 1) / p.R);
   p.mirror = mirror;
   p.org_x = mirror ? -(KW - 1 - pad_w) : -pad_w;
   p.org_y = mirror ? -(KH - 1 - pad_h) : -pad_h;

@@ -108,6 +108,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
   const int kb0 = blockIdx.z * p.kb_per_split;
   const int kb1 = min(total_kb, kb0 + p.kb_per_split);
   constexpr bool kGather = (AMODE == A_GATHER_K || AMODE == A_GATHER_MN);
+  constexpr int LAG = (GATHER_LAG < STAGES - 1) ? GATHER_LAG : STAGES - 1;  // must stay below the ring depth
   constexpr bool kAMn = (AMODE == A_TMA_MN || AMODE == A_GATHER_MN);
 
   if (threadIdx.x == 0) {
@@ -239,15 +240,15 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
         }
         }
         cp_async_commit();
-        if (it >= GATHER_LAG) {
-          cp_async_wait<GATHER_LAG>();
+        if (it >= LAG) {
+          cp_async_wait<LAG>();
           fence_proxy_async_smem();
-          mbar_arrive(&full_bar[(it - GATHER_LAG) % STAGES]);
+          mbar_arrive(&full_bar[(it - LAG) % STAGES]);
         }
       }
       cp_async_wait<0>();
       fence_proxy_async_smem();
-      for (int j = max(0, it - GATHER_LAG); j < it; ++j) mbar_arrive(&full_bar[j % STAGES]);
+      for (int j = max(0, it - LAG); j < it; ++j) mbar_arrive(&full_bar[j % STAGES]);
     } else if constexpr (AMODE == A_GATHER_MN) {
       // A^T tile: [2 atoms][64 reduction rows (pixels)][64 M' elements = 128 B]
       const int krow = threadIdx.x & 63;
@@ -293,15 +294,15 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
           cp_async16(dst_row + ((c ^ sw) << 4), srcp, ok ? 16u : 0u);
         }
         cp_async_commit();
-        if (it >= GATHER_LAG) {
-          cp_async_wait<GATHER_LAG>();
+        if (it >= LAG) {
+          cp_async_wait<LAG>();
           fence_proxy_async_smem();
-          mbar_arrive(&full_bar[(it - GATHER_LAG) % STAGES]);
+          mbar_arrive(&full_bar[(it - LAG) % STAGES]);
         }
       }
       cp_async_wait<0>();
       fence_proxy_async_smem();
-      for (int j = max(0, it - GATHER_LAG); j < it; ++j) mbar_arrive(&full_bar[j % STAGES]);
+      for (int j = max(0, it - LAG); j < it; ++j) mbar_arrive(&full_bar[j % STAGES]);
     }
 
     // ----------------------------------------------------- epilogue: TMEM -> registers -> global
@@ -524,7 +525,14 @@ static int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, const Igem
 template <int AMODE>
 static int dispatch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
                        cudaStream_t stream) {
-  if (p.N <= 64) return launch_igemm<64, 4, AMODE>(ta, tb, p, splits, stream);
+  // few k-blocks per tile: a deep ring is useless, so use 2 stages and let more CTAs share an SM (their
+  // prologues / epilogues overlap with each other's main loops)
+  const bool shallow = p.kb_per_split <= 2;
+  if (p.N <= 64) {
+    if (shallow) return launch_igemm<64, 2, AMODE>(ta, tb, p, splits, stream);
+    return launch_igemm<64, 4, AMODE>(ta, tb, p, splits, stream);
+  }
+  if (shallow) return launch_igemm<128, 2, AMODE>(ta, tb, p, splits, stream);
   return launch_igemm<128, 3, AMODE>(ta, tb, p, splits, stream);
 }
 

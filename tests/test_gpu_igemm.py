@@ -38,7 +38,7 @@ def test_gemm(raw, M, N, K):
 
 
 CONVS = [(2, 16, 16, 64, 64, 3, 3, 1), (2, 56, 56, 64, 64, 3, 3, 1), (3, 28, 28, 128, 128, 3, 3, 1),
-         (2, 14, 14, 256, 128, 3, 3, 1), (2, 17, 19, 64, 192, 3, 3, 1), (2, 12, 12, 64, 64, 5, 5, 1), (4, 32, 32, 8, 64, 5, 5, 1), (2, 28, 28, 128, 256, 3, 3, 2),
+         (2, 14, 14, 256, 128, 3, 3, 1), (2, 17, 19, 64, 192, 3, 3, 1), (2, 12, 12, 64, 64, 5, 5, 1), (1, 40, 150, 64, 64, 3, 3, 1), (2, 64, 64, 128, 64, 3, 3, 1), (2, 7, 7, 64, 64, 3, 3, 1), (4, 32, 32, 8, 64, 5, 5, 1), (2, 28, 28, 128, 256, 3, 3, 2),
          (2, 14, 14, 256, 512, 1, 1, 1), (2, 56, 56, 64, 128, 1, 1, 2), (2, 30, 30, 16, 32, 7, 7, 2),
          (3, 17, 19, 32, 64, 3, 3, 2)]
 
