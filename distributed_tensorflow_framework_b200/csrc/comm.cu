@@ -114,6 +114,32 @@ __device__ __forceinline__ float4 reduce_peers(const CommCtx& c, size_t grad_off
   return s;
 }
 
+// Remote loads cost ~2 us each: keep U independent 16-byte loads per peer in flight per thread. q0 is the first
+// float4 index of this thread, `stride` the distance between its U elements, n4 the range length (indices relative
+// to base4). Sums are formed in rank order, so every rank computes bit-identical results.
+constexpr int COMM_U = 4;
+__device__ __forceinline__ void reduce_peers_u(const CommCtx& c, size_t grad_off, long long base4, long long q0,
+                                               long long stride, long long n4, float4 (&s)[COMM_U]) {
+#pragma unroll
+  for (int u = 0; u < COMM_U; ++u) s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int r = 0; r < MAX_RANKS; ++r) {
+    if (r < c.world) {
+      const float4* g = reinterpret_cast<const float4*>(c.peer[r] + grad_off) + base4;
+      float4 v[COMM_U];
+#pragma unroll
+      for (int u = 0; u < COMM_U; ++u) {
+        const long long q = q0 + u * stride;
+        v[u] = (q < n4) ? ld_cg_f4(g + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < COMM_U; ++u) {
+        s[u].x += v[u].x; s[u].y += v[u].y; s[u].z += v[u].z; s[u].w += v[u].w;
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ float4 optim4(const OptimArgs& o, float* master, float* m, float* v, long long i,
                                          float4 g) {
   float4 p = *reinterpret_cast<float4*>(master + i);
@@ -132,14 +158,23 @@ allreduce_optim_kernel(CommCtx c, size_t grad_off, long long start, long long co
                        float* m, float* v, __nv_bfloat16* shadow, float* avg_out) {
   block_barrier(c);
   const long long n4 = count >> 2;
-  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < n4; q += (long long)gridDim.x * blockDim.x) {
-    const long long i = start + (q << 2);
-    const float4 g = reduce_peers(c, grad_off, i >> 2);
-    if (master != nullptr) {
-      const float4 p = optim4(o, master, m, v, i, g);
-      if (shadow) *reinterpret_cast<uint2*>(shadow + i) = pack4_bf16(p);
-    } else {
-      *reinterpret_cast<float4*>(avg_out + i) = make_float4(g.x * o.gscale, g.y * o.gscale, g.z * o.gscale, g.w * o.gscale);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long q0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * COMM_U) {
+    float4 gs[COMM_U];
+    reduce_peers_u(c, grad_off, start >> 2, q0, stride, n4, gs);
+#pragma unroll
+    for (int u = 0; u < COMM_U; ++u) {
+      const long long q = q0 + u * stride;
+      if (q >= n4) continue;
+      const long long i = start + (q << 2);
+      const float4 g = gs[u];
+      if (master != nullptr) {
+        const float4 p = optim4(o, master, m, v, i, g);
+        if (shadow) *reinterpret_cast<uint2*>(shadow + i) = pack4_bf16(p);
+      } else {
+        *reinterpret_cast<float4*>(avg_out + i) =
+            make_float4(g.x * o.gscale, g.y * o.gscale, g.z * o.gscale, g.w * o.gscale);
+      }
     }
   }
   block_barrier(c);  // nobody may overwrite its gradient bucket while a peer still reads it
@@ -169,18 +204,25 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float
   block_barrier(c);
   const long long start = bounds.b[c.rank];
   const long long n4 = (bounds.b[c.rank + 1] - start) >> 2;
-  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < n4; q += (long long)gridDim.x * blockDim.x) {
-    const long long i = start + (q << 2);
-    const float4 g = reduce_peers(c, grad_off, i >> 2);
-    const float4 p = optim4(o, master, m, v, i, g);
-    const uint2 pb = pack4_bf16(p);
-    const bool local_only = in_nopush(np, i);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long q0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * COMM_U) {
+    float4 gs[COMM_U];
+    reduce_peers_u(c, grad_off, start >> 2, q0, stride, n4, gs);
 #pragma unroll
-    for (int r = 0; r < MAX_RANKS; ++r) {
-      if (r < c.world && (!local_only || r == c.rank)) {
-        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[r] + shadow_off) + i) = pb;
-        if (master_off != (size_t)-1 && r != c.rank)
-          *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.peer[r] + master_off) + i) = p;
+    for (int u = 0; u < COMM_U; ++u) {
+      const long long q = q0 + u * stride;
+      if (q >= n4) continue;
+      const long long i = start + (q << 2);
+      const float4 p = optim4(o, master, m, v, i, gs[u]);
+      const uint2 pb = pack4_bf16(p);
+      const bool local_only = in_nopush(np, i);
+#pragma unroll
+      for (int r = 0; r < MAX_RANKS; ++r) {
+        if (r < c.world && (!local_only || r == c.rank)) {
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[r] + shadow_off) + i) = pb;
+          if (master_off != (size_t)-1 && r != c.rank)
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.peer[r] + master_off) + i) = p;
+        }
       }
     }
   }

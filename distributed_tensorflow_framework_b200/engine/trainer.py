@@ -23,7 +23,7 @@ from .tower import Tower
 class Trainer(object):
     def __init__(self, net, loss, optimizer, device="cpu", rank=0, world=1, group=None, gpu_num=1, algo="auto",
                  placement="bytes", use_cuda_graph=False, seed=0, sync_optimizer=None, pre_process_fn=None,
-                 post_process_fn=None, pre_train_result=None, bucket_bytes=8 << 20, overlap=True):
+                 post_process_fn=None, pre_train_result=None, bucket_bytes=4 << 20, overlap=True):
         self.net, self.loss, self.optimizer = net, loss, optimizer
         self.device = torch.device(device)
         self.rank, self.world, self.group = rank, world, group

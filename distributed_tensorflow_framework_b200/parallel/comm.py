@@ -67,7 +67,7 @@ class Communicator(object):
         self.heap, self.rank, self.world = heap, rank, world
         self.handle = ctypes.c_void_p()
         self.stream = torch.cuda.Stream(device=heap.device)
-        self.blocks = 32
+        self.blocks = 64
         self._version = 0
         if local_heaps is not None:  # single process driving several peer-enabled GPUs (tests)
             arr = (ctypes.c_void_p * world)(*[h.ptr for h in local_heaps])
@@ -161,7 +161,7 @@ class GradientEngine(object):
     on the communication stream as soon as backward has produced all of its gradients.
     """
 
-    def __init__(self, store, optimizer, rank=0, world=1, algo="auto", group=None, bucket_bytes=8 << 20,
+    def __init__(self, store, optimizer, rank=0, world=1, algo="auto", group=None, bucket_bytes=4 << 20,
                  placement="bytes", heap_extra_bytes=0, overlap=True):
         self.store, self.opt, self.rank, self.world, self.group = store, optimizer, rank, world, group
         dev = store.device
@@ -169,7 +169,7 @@ class GradientEngine(object):
         if algo == "auto":
             algo = "local" if world == 1 else ("oneshot" if n_est * 4 <= (16 << 20) else "twoshot")
         self.algo = algo
-        self.overlap = overlap and algo in ("oneshot", "nccl")
+        self.overlap = overlap and algo in ("oneshot", "nccl", "twoshot", "twoshot_pull")
         self.comm = None
         self.heap = None
         self.pull = algo == "twoshot_pull"
@@ -279,6 +279,13 @@ class GradientEngine(object):
             import torch.distributed as dist
             dist.all_reduce(st.grad_arena[start:start + count], group=self.group)
             opt.apply_arena(st, step, 1.0 / self.world, start, count, refresh=False)
+        elif self.algo == "twoshot":
+            # the bucket is split among its owners: owner bounds clamped to [start, start + count)
+            end = start + count
+            bounds = [min(max(b, start), end) for b in st.owner_bounds]
+            self.comm.rs_optim_ag(self.heap.offset_of("grad"), bounds, opt, step, st.master_arena, st.slot_m,
+                                  st.slot_v, self.heap.offset_of("shadow"), stream=self.comm_stream,
+                                  nopush=self.nopush)
         else:
             raise RuntimeError(self.algo)
 
@@ -293,7 +300,7 @@ class GradientEngine(object):
             return
         self.comm_stream.wait_stream(cur)
         with torch.cuda.stream(self.comm_stream):
-            if self.algo in ("oneshot", "nccl"):
+            if self.algo in ("oneshot", "nccl", "twoshot"):
                 if self.overlap:
                     for bi in range(len(self.buckets) - 1, -1, -1):
                         if not self._launched[bi]:
@@ -302,10 +309,6 @@ class GradientEngine(object):
                             self._reduce_and_update(s, e - s)
                 else:
                     self._reduce_and_update(0, self.n)
-            elif self.algo == "twoshot":
-                self.comm.rs_optim_ag(self.heap.offset_of("grad"), st.owner_bounds, opt, step, st.master_arena,
-                                      st.slot_m, st.slot_v, self.heap.offset_of("shadow"),
-                                      stream=self.comm_stream, nopush=self.nopush)
             elif self.algo == "async":
                 self.comm.async_push(self.heap.offset_of("grad"), self.heap.offset_of("mailbox"), self.slice_cap,
                                      st.owner_bounds, stream=self.comm_stream)
