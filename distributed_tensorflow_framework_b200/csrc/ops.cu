@@ -108,6 +108,44 @@ __global__ void add_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloa
   }
 }
 
+// ------------------------------------------------------------------------------------------- strided pixel sampling
+// y[n, oh, ow, :] = x[n, oh*s, ow*s, :] (forward of a 1x1 stride-s convolution's input selection), and its adjoint:
+// dx[n, h, w, :] = dy[n, h/s, w/s, :] if h % s == 0 and w % s == 0 else 0.
+__global__ void subsample_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int n_img, int H,
+                                 int W, int C, int OH, int OW, int s) {
+  const int cpr = C / 8;
+  const long long total = (long long)n_img * OH * OW * cpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cpr) * 8;
+    long long t = i / cpr;
+    const int ow = (int)(t % OW);
+    t /= OW;
+    const int oh = (int)(t % OH);
+    const int n = (int)(t / OH);
+    st8(y + i * 8, ld8(x + (((long long)n * H + oh * s) * W + ow * s) * C + c0));
+  }
+}
+__global__ void upsample_zero_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int n_img,
+                                     int H, int W, int C, int OH, int OW, int s) {
+  const int cpr = C / 8;
+  const long long total = (long long)n_img * H * W * cpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cpr) * 8;
+    long long t = i / cpr;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    BF8 v;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v.v[j] = __floats2bfloat162_rn(0.f, 0.f);
+    if ((h % s) == 0 && (w % s) == 0) v = ld8(dy + (((long long)n * OH + h / s) * OW + w / s) * C + c0);
+    st8(dx + i * 8, v);
+  }
+}
+
 // ------------------------------------------------------------------------------------------- column reductions
 // Matrix [R, N] bf16 (N % 8 == 0). Each thread owns one 8-column chunk and walks rows; per-block partials are
 // combined with fp32 atomics into acc[NACC][N] (caller zeroes acc).
@@ -930,6 +968,20 @@ extern "C" int dtf_convert_input(const void* src, void* dst, long long pixels, i
   else
     convert_input_kernel<float><<<g, 256, 0, ST(stream)>>>((const float*)src, (__nv_bfloat16*)dst, pixels, C, Cpad,
                                                            scale, shift);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_subsample(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int s,
+                             void* stream) {
+  if (C % 8) return DTF_ERR_ALIGN;
+  subsample_kernel<<<grid_for((long long)n_img * OH * OW * (C / 8), 256), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, n_img, H, W, C, OH, OW, s);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_upsample_zero(const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW, int s,
+                                 void* stream) {
+  if (C % 8) return DTF_ERR_ALIGN;
+  upsample_zero_kernel<<<grid_for((long long)n_img * H * W * (C / 8), 256), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, n_img, H, W, C, OH, OW, s);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {

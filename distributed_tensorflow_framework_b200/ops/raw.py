@@ -60,9 +60,26 @@ def gemm_ag(a, ag, transposed_shadow, bias=None, relu=False, out_fp32=False):
     return out
 
 
+def subsample(x, s):
+    n, H, W, C = x.shape
+    OH, OW = -(-H // s), -(-W // s)
+    y = torch.empty((n, OH, OW, C), device=x.device, dtype=bf16)
+    _lib.call("dtf_subsample", x, y, n, H, W, C, OH, OW, s, _sp())
+    return y
+
+
+def upsample_zero(dy, in_hw, s):
+    n, OH, OW, C = dy.shape
+    dx = torch.empty((n, in_hw[0], in_hw[1], C), device=dy.device, dtype=bf16)
+    _lib.call("dtf_upsample_zero", dy, dx, n, in_hw[0], in_hw[1], C, OH, OW, s, _sp())
+    return dx
+
+
 def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False):
     n, H, W, C = x.shape
     n_out = w2d.shape[1]
+    if KH == 1 and KW == 1 and stride > 1:  # strided 1x1: select the sampled pixels, then a dense GEMM
+        return conv_fprop(subsample(x, stride), w2d, bias, 1, 1, 1, relu, out_fp32)
     if KH == 1 and KW == 1 and stride == 1:  # a 1x1 convolution is a dense GEMM: TMA-fed A operand, no gather
         return gemm(x.view(-1, C), w2d, bias, relu=relu, out_fp32=out_fp32).view(n, H, W, n_out)
     OH, pt = same_pad(H, KH, stride)
@@ -85,6 +102,9 @@ def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False):
     Ci = w2d_t.shape[1]
     if KH == 1 and KW == 1 and stride == 1:
         return gemm(dy.view(-1, Co), w2d_t, bias, relu=relu).view(n, H, W, Ci)
+    if KH == 1 and KW == 1 and stride > 1 and bias is None and not relu:
+        small = gemm(dy.view(-1, Co), w2d_t).view(n, OH, OW, Ci)
+        return upsample_zero(small, (H, W), stride)
     _, pt = same_pad(H, KH, stride)
     _, pl = same_pad(W, KW, stride)
     dx = torch.empty((n, H, W, Ci), device=dy.device, dtype=bf16)
@@ -104,8 +124,11 @@ def conv_wgrad(x, dy, KH, KW, stride=1, out=None):
     _, pl = same_pad(W, KW, stride)
     if out is None:
         out = torch.zeros((KH * KW * C, Co), device=x.device, dtype=torch.float32)
+    if KH == 1 and KW == 1 and stride > 1:
+        x = subsample(x, stride)
+        stride = 1
     if KH == 1 and KW == 1 and stride == 1:  # dW = x^T dy: dense MN-major A operand, split over pixels
-        return gemm(x.view(-1, C), dy.view(-1, Co), a_transposed=True, out=out, accumulate=True)
+        return gemm(x.reshape(-1, C), dy.view(-1, Co), a_transposed=True, out=out, accumulate=True)
     _lib.call("dtf_conv_wgrad_bf16", x, dy, out, n, H, W, C, OH, OW, KH, KW, Co, stride, pt, pl, _sp())
     return out
 

@@ -70,6 +70,10 @@ int dtf_conv_wgrad_bf16(const void* x, const void* dy, float* dw, int n_img, int
  * distribute_input.py:54-106). */
 int dtf_convert_input(const void* src, void* dst, long long pixels, int C, int Cpad, float scale, float shift,
                       int src_is_u8, void* stream);
+/* y[n,oh,ow,:] = x[n,oh*s,ow*s,:] and its adjoint (zero-filled scatter): a 1x1 stride-s convolution becomes
+ * "select pixels, then dense GEMM" instead of an im2col gather. */
+int dtf_subsample(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int s, void* stream);
+int dtf_upsample_zero(const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW, int s, void* stream);
 int dtf_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);
 int dtf_cast_bf16_to_f32(const void* src, float* dst, long long n, void* stream);
 
