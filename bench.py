@@ -189,6 +189,7 @@ def run_ours(args, cfg):
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
+    allreduce = measure_allreduce(trainer, world, device, barrier) if world > 1 else None
     gb = batch * world
     x0, y0 = pool[0]
     res = {
@@ -205,12 +206,58 @@ def run_ours(args, cfg):
                 "h2d_bytes_per_step": x0.numel() * x0.element_size() + y0.numel() * y0.element_size(),
                 "d2h_bytes_per_step": 4},
         "gpu_launches": int(launches), "final_loss": final_loss, "clocks": clocks,
+        "grad_allreduce": allreduce,
     }
     if rank == 0:
         print(json.dumps(res), flush=True)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
+
+
+def measure_allreduce(trainer, world, device, barrier, iters=10):
+    """Second half of the BASELINE.json metric: bus bandwidth of the gradient collective on this model's gradient
+    arena. K-AR (one-shot peer-load allreduce, fp32) and NCCL allreduce on the same buffer, CUDA events, max over
+    ranks; bus GB/s = 2 (N-1)/N * bytes / t (nccl-tests convention); fraction of the measured 770 GB/s per-direction
+    peer-copy bandwidth (B200_PROFILING.md)."""
+    import torch
+    import torch.distributed as dist
+    eng = trainer.engine
+    if eng is None or eng.comm is None:
+        return None
+    st = trainer.store
+    n = st.n_params // 4 * 4
+    nbytes = n * 4
+    out = torch.empty(n, device=device, dtype=torch.float32)
+    goff = eng.heap.offset_of("grad")
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1) / iters, world, device)
+
+    cur = torch.cuda.current_stream(device)
+    t_ar = timed(lambda: eng.comm.allreduce_mean(goff, 0, n, out, stream=cur))
+    buf = st.grad_arena[:n].clone()
+    t_nccl = timed(lambda: dist.all_reduce(buf))
+    import distributed_tensorflow_framework_b200 as dtf
+    frozen = dtf.GradientDescentOptimizer(0.0)  # lr 0: the owner update leaves the weights unchanged
+    t_rs = timed(lambda: eng.comm.rs_optim_ag(goff, st.owner_bounds, frozen, 1, st.master_arena, None, None,
+                                              eng.heap.offset_of("shadow"), stream=cur))
+    f = 2.0 * (world - 1) / world
+    return {"bytes": nbytes, "k_rs_opt_ms": t_rs,
+            "k_rs_opt_bus_gbs": (world - 1) / world * (nbytes + nbytes / 2) / t_rs / 1e6, "k_ar_ms": t_ar, "k_ar_bus_gbs": f * nbytes / t_ar / 1e6,
+            "nccl_ms": t_nccl, "nccl_bus_gbs": f * nbytes / t_nccl / 1e6,
+            "k_ar_frac_of_770": f * nbytes / t_ar / 1e6 / 770.0,
+            "note": "one-shot K-AR reads (N-1) remote copies per rank: its wire bytes per GPU are (N-1)*S, so the "
+                    "nccl-tests bus figure understates link utilisation for N > 2"}
 
 
 def run_reference(args, cfg):
