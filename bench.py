@@ -27,7 +27,7 @@ CONFIGS = {
     # name: (model, per-GPU batch, image shape, classes (0 = image target), loss, optimizer)
     "cifar10": dict(model="Cifar10CNN", batch=128, shape=(32, 32, 3), classes=10, loss="xent",
                     desc="CIFAR-10-tutorial CNN multi-tower sync gradient averaging"),
-    "resnet50": dict(model="ResNet50", batch=64, shape=(224, 224, 3), classes=1000, loss="xent",
+    "resnet50": dict(model="ResNet50", batch=256, shape=(224, 224, 3), classes=1000, loss="xent",
                      desc="ResNet-50 synthetic 224x224 sync data-parallel (ps/worker-equivalent) bf16"),
     "resnet18_async": dict(model="ResNet18", batch=64, shape=(224, 224, 3), classes=1000, loss="xent",
                            desc="ResNet-18 async parameter-server mode with sharded owner-side updates"),

@@ -277,6 +277,9 @@ class VariableStore(object):
                 v.shadow_t = self.shadow_t_arena[sl].view(v.store_shape[:-2] + (Co, Ci))
                 descs.append((v.offset, v.offset, T, Ci, Co, tile_start))
                 tile_start += T * ((Ci + 31) // 32) * ((Co + 31) // 32)
+        if not (placement == "round_robin" and world > 1):
+            for v in tv:  # owner = the shard that holds the variable's first element
+                v.owner = max(i for i in range(world) if self.owner_bounds[i] <= v.offset)
         self._build_tap_table(descs, tile_start)
         self.refresh_transposed_shadows()
         self.finalized = True

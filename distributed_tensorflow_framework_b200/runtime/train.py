@@ -21,6 +21,7 @@ from ..api import log as logger
 from ..engine.trainer import Trainer
 from ..io.events import EventFileWriter
 from ..plugins import input as Input
+from ..utils import fault, nvtx
 from . import hooks as H
 from .cluster import DoneQueue
 from .session import MonitoredTrainingSession, Saver, Scaffold
@@ -126,7 +127,7 @@ class Train(object):
             logger.info("Worker %d: Waiting for session to be initialized..." % self.task_index)
 
         writer = EventFileWriter(self.model_dir) if (is_chief and self.model_dir) else None
-        saver = Saver(store, base_opt, num_shards=1,
+        saver = Saver(store, base_opt, num_shards=num_workers if getattr(self, "sharded_checkpoint", False) else 1,
                       gather_fn=trainer.engine.gather_masters if trainer.engine is not None else None)
 
         def barrier():
@@ -137,7 +138,13 @@ class Train(object):
         session_hooks = [H.StopAtStepHook(last_step=total_step)]
         if sync_replicas_hook is not None:
             session_hooks.append(sync_replicas_hook)
+        if trainer.engine is not None and trainer.engine.comm is not None and num_workers > 1:
+            session_hooks.append(H.HeartbeatHook(trainer.engine.comm, every_n_steps=50, timeout_s=120.0))
         session_hooks += list(getattr(self, "extra_hooks", []))
+        if flags.FLAGS.log_device_placement:  # honoured here; the reference hard-codes False (distribute_train.py:176-178)
+            for v in store.all_variables():
+                logger.info("placement: %s -> owner rank %d (offset %d, %d elements)", v.name, v.owner, v.offset,
+                            v.numel)
         pending = {"batches": first}
         state = {"loss": None}
 
@@ -145,8 +152,10 @@ class Train(object):
             batches = pending.pop("batches", None)
             if batches is None:
                 batches = [self._next_host_batch(name_queue, placeholder_queue) for _ in range(num_devices)]
-            loss = trainer.step(batches)
+            with nvtx.range("train_step"):
+                loss = trainer.step(batches)
             state["loss"] = loss
+            fault.maybe_kill(self.task_index, store.global_step)
             return {"loss": loss, "summaries": trainer.last_summaries}
 
         with MonitoredTrainingSession(master=self.server.target, is_chief=is_chief, checkpoint_dir=self.model_dir,

@@ -221,3 +221,15 @@ def test_run_config_uid_is_stable():
     b = dtf.RunConfig(model_dir="/m", cluster_spec=dtf.ClusterSpec({"ps": "p:1", "worker": "b:1,a:2"}), foo=1,
                       save_summary_steps=99)
     assert a.uid() == b.uid() and "_foo=1" in a.uid()
+
+
+def test_fault_injection_spec_and_nvtx_noop():
+    from distributed_tensorflow_framework_b200.utils import fault, nvtx
+    assert fault.parse("") is None and fault.parse("1:20") == (1, 20)
+    with pytest.raises(ValueError):
+        fault.parse("oops")
+    died = []
+    assert not fault.maybe_kill(0, 20, "1:20", _exit=died.append)
+    assert fault.maybe_kill(1, 20, "1:20", _exit=died.append) and died == [17]
+    with nvtx.range("unit"):
+        nvtx.mark("m")

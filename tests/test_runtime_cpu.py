@@ -171,7 +171,21 @@ def test_multi_tower_cpu_equals_mean_of_tower_gradients():
         assert torch.allclose(v, t2.store.state_dict()[k], atol=1e-5), k
 
 
+def _free_ports(n):
+    import socket
+    socks, ports = [], []
+    for _ in range(n):
+        sk = socket.socket()
+        sk.bind(("127.0.0.1", 0))
+        socks.append(sk)
+        ports.append(sk.getsockname()[1])
+    for sk in socks:
+        sk.close()
+    return ports
+
+
 def test_ps_and_two_workers_over_loopback(tmp_path):
+    p_ps, p_w0, p_w1 = _free_ports(3)
     script = tmp_path / "job.py"
     script.write_text('''
 import os, sys
@@ -188,8 +202,8 @@ os.makedirs(md, exist_ok=True)
 @ann.current_mode(mode="Train")
 @ann.current_input(input="Cifar10SyntheticLoader")
 @ann.gpu_num(gpu_num=0)
-@ann.ps_hosts(ps_hosts="127.0.0.1:29655")
-@ann.worker_hosts(worker_hosts="127.0.0.1:29656, 127.0.0.1:29657")
+@ann.ps_hosts(ps_hosts="127.0.0.1:%d")
+@ann.worker_hosts(worker_hosts="127.0.0.1:%d, 127.0.0.1:%d")
 @ann.job_name(job_name=flags.FLAGS.job_name)
 @ann.task_index(task_index=flags.FLAGS.task_index)
 @ann.batch_size(batch_size=8)
@@ -204,12 +218,17 @@ if flags.FLAGS.job_name == "worker":
     print("RESULT", flags.FLAGS.task_index, op.trainer.store.global_step, "%%.8f" %% float(w.double().sum()), flush=True)
 else:
     print("PS_EXIT", flush=True)
-''' % (ROOT, str(tmp_path)))
+''' % (ROOT, str(tmp_path), p_ps, p_w0, p_w1))
     env = dict(os.environ, OMP_NUM_THREADS="2")
     procs = [subprocess.Popen([sys.executable, str(script), "--job_name=%s" % j, "--task_index=%d" % t],
                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
              for j, t in (("ps", 0), ("worker", 0), ("worker", 1))]
-    outs = [p.communicate(timeout=300)[0] for p in procs]
+    try:
+        outs = [p.communicate(timeout=240)[0] for p in procs]
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                p.kill()
     assert all(p.returncode == 0 for p in procs), "\\n".join(o[-1500:] for o in outs)
     assert "PS_EXIT" in outs[0]  # the ps left after both workers signalled the done queue
     r0 = [l for l in outs[1].splitlines() if l.startswith("RESULT")][0].split()
