@@ -198,6 +198,152 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   }
 }
 
+
+// --------------------------------------------------------------------------------------------------------------
+// Filter gradient on halo tiles: dW[tap, ci, co] = sum over pixels p of x[p + shift(tap), ci] * dy[p, co].
+// A CTA owns one (64 ci) x (64 co) block of ALL taps and walks a range of image tiles. Per tile one TMA load brings
+// the x halo (same box as fprop) and R row loads bring the dy tile into the padded-linear layout (gap positions stay
+// zero from the one-time clear). Both operands are MN-major: shared-memory rows are pixels (the reduction dim),
+// the 128 bytes of a row are 64 channels. A tap is again only a start-address shift of the x halo; two taps are
+// paired into one M=128 MMA by using the shift difference as the descriptor's leading-dimension byte offset, so the
+// KH*KW accumulators [128 x 64] live side by side in TMEM for the whole kernel and are reduced into dW with red.add
+// once at the end (split over tiles across CTAs).
+struct WgradParams {
+  int n_img, H, W, C, n_out;
+  int KH, KW, Wp, Wt, R, tiles_x, tiles_per_img;
+  int org_x, org_y;
+  int a_stage_bytes, a_tx_bytes, b_tx_bytes;
+  int total_tiles, tiles_per_split;
+  float* dw;
+};
+constexpr int WG_STAGES = 3;
+constexpr int WG_B_BYTES = 128 * 128;  // 128 pixel rows x 64 co
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+wgrad_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_dy,
+                  const WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t a_base = smem_base;
+  const uint32_t b_base = smem_base + WG_STAGES * p.a_stage_bytes;
+  const int data_bytes = WG_STAGES * (p.a_stage_bytes + WG_B_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + data_bytes);
+  uint64_t* empty = full + WG_STAGES;
+  uint64_t* tmem_full = empty + WG_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int co0 = blockIdx.x * 64, ci0 = blockIdx.y * 64;
+  const int t_begin = blockIdx.z * p.tiles_per_split;
+  const int t_end = min(p.total_tiles, t_begin + p.tiles_per_split);
+  const int ntaps = p.KH * p.KW;
+  const int npairs = (ntaps + 1) >> 1;
+
+  // one-time clear: positions that TMA never writes (row gaps, tails) must read as finite zeros
+  for (int i = threadIdx.x * 16; i < data_bytes; i += NUM_THREADS * 16)
+    *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < WG_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 4) tmem_alloc<512>(tmem_slot);
+  if (warp == 5 && lane == 0) {
+    tma_prefetch_desc(&tma_x);
+    tma_prefetch_desc(&tma_dy);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 5) {
+    if (lane == 0) {
+      int it = 0;
+      for (int t = t_begin; t < t_end; ++t, ++it) {
+        const int s = it % WG_STAGES;
+        mbar_wait(&empty[s], ((it / WG_STAGES) & 1) ^ 1);
+        const int img = t / p.tiles_per_img;
+        const int tin = t - img * p.tiles_per_img;
+        const int y0 = (tin / p.tiles_x) * p.R, x0 = (tin % p.tiles_x) * p.Wt;
+        mbar_arrive_expect_tx(&full[s], p.a_tx_bytes + p.b_tx_bytes);
+        tma_load_4d(a_base + s * p.a_stage_bytes, &tma_x, &full[s], ci0, x0 + p.org_x, y0 + p.org_y, img);
+        for (int ry = 0; ry < p.R; ++ry)
+          tma_load_4d(b_base + s * WG_B_BYTES + ry * p.Wp * 128, &tma_dy, &full[s], co0, x0, y0 + ry, img);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 4) {
+    constexpr uint32_t idesc = make_idesc_bf16(128, 64, /*a_mn=*/true, /*b_mn=*/true);
+    int it = 0;
+    for (int t = t_begin; t < t_end; ++t, ++it) {
+      const int s = it % WG_STAGES;
+      mbar_wait(&full[s], (it / WG_STAGES) & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        for (int j = 0; j < npairs; ++j) {
+          const int t0 = 2 * j, t1 = min(2 * j + 1, ntaps - 1);
+          const int sh0 = (t0 / p.KW) * p.Wp + (t0 % p.KW);
+          const int sh1 = (t1 / p.KW) * p.Wp + (t1 % p.KW);
+          const uint32_t a_tap = a_base + s * p.a_stage_bytes + (uint32_t)sh0 * 128u;
+          const uint32_t lbo = (t1 == t0) ? 128u : (uint32_t)(sh1 - sh0) * 128u;  // odd tail: second half is a dummy
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const uint64_t adesc = make_smem_desc(a_tap + k * 2048, lbo, 1024);
+            const uint64_t bdesc = make_smem_desc(b_base + s * WG_B_BYTES + k * 2048, 8192, 1024);
+            umma_bf16(tmem_base + j * 64, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty[s]);
+      }
+      __syncwarp();
+    }
+    if (lane == 0) umma_commit(tmem_full);
+    __syncwarp();
+  } else {
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const int r = threadIdx.x;  // TMEM lane: rows 0-63 = first tap of the pair, 64-127 = second tap
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const bool have = t_end > t_begin;
+    for (int j = 0; j < npairs; ++j) {
+      const int tap = 2 * j + (r >> 6);
+      const int ci = ci0 + (r & 63);
+#pragma unroll 1
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t v[32];
+        tmem_ld32(lane_addr + j * 64 + cc * 32, v);
+        tmem_ld_wait();
+        if (have && tap < ntaps && ci < p.C) {
+          float* o = p.dw + ((size_t)tap * p.C + ci) * p.n_out + co0 + cc * 32;
+          if (co0 + cc * 32 + 32 <= p.n_out && (p.n_out & 3) == 0) {
+#pragma unroll
+            for (int q = 0; q < 32; q += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(o + q), "f"(__uint_as_float(v[q])),
+                           "f"(__uint_as_float(v[q + 1])), "f"(__uint_as_float(v[q + 2])),
+                           "f"(__uint_as_float(v[q + 3]))
+                           : "memory");
+          } else {
+            for (int q = 0; q < 32; ++q)
+              if (co0 + cc * 32 + q < p.n_out) red_add_f32(o + q, __uint_as_float(v[q]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -313,4 +459,75 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   if (n_out <= 64) return launch<64, 4>(tx, tw, p, stream);
   return launch<128, 4>(tx, tw, p, stream);
+}
+
+// 1 if dtf_conv_wgrad_halo_bf16 supports the geometry (stride 1, C % 64 == 0, n_out % 64 == 0, <= 16 taps).
+extern "C" int dtf_conv_wgrad_halo_supported(int H, int W, int C, int KH, int KW, int n_out) {
+  if ((C & 63) || (n_out & 63) || KH * KW < 2 || KH * KW > 16) return 0;
+  int Wt, R;
+  return halo_plan(H, W, KH, KW, &Wt, &R) >= 0.60 ? 1 : 0;
+}
+
+// dW[KH*KW*C, n_out] (fp32, += with red.add) from x[n_img,H,W,C] and dy[n_img,H,W,n_out]; SAME padding, stride 1.
+extern "C" int dtf_conv_wgrad_halo_bf16(const void* x, const void* dy, float* dw, int n_img, int H, int W, int C,
+                                        int KH, int KW, int n_out, int pad_h, int pad_w, void* stream_) {
+  using namespace dtf::halo;
+  if (!dtf_conv_wgrad_halo_supported(H, W, C, KH, KW, n_out)) return DTF_ERR_UNSUPPORTED;
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return DTF_ERR_DRIVER;
+  WgradParams p{};
+  p.n_img = n_img; p.H = H; p.W = W; p.C = C; p.n_out = n_out; p.KH = KH; p.KW = KW;
+  halo_plan(H, W, KH, KW, &p.Wt, &p.R);
+  p.Wp = p.Wt + KW - 1;
+  p.tiles_x = (W + p.Wt - 1) / p.Wt;
+  p.tiles_per_img = p.tiles_x * ((H + p.R - 1) / p.R);
+  p.org_x = -pad_w;
+  p.org_y = -pad_h;
+  const int halo_rows = p.R + KH - 1;
+  p.a_tx_bytes = halo_rows * p.Wp * 128;
+  const int span = (128 + (KH - 1) * p.Wp + (KW - 1) + 1) * 128;
+  p.a_stage_bytes = ((span > p.a_tx_bytes ? span : p.a_tx_bytes) + 1023) & ~1023;
+  p.b_tx_bytes = p.R * p.Wt * 128;
+  p.total_tiles = n_img * p.tiles_per_img;
+  const int blocks_xy = (n_out / 64) * (C / 64);
+  int splits = (148 + blocks_xy - 1) / blocks_xy;
+  if (splits > p.total_tiles) splits = p.total_tiles;
+  if (splits < 1) splits = 1;
+  p.tiles_per_split = (p.total_tiles + splits - 1) / splits;
+  splits = (p.total_tiles + p.tiles_per_split - 1) / p.tiles_per_split;
+  p.dw = dw;
+  CUtensorMap tx, tdy;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n_img};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.Wp, (cuuint32_t)halo_rows, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    if (fn(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), dims, strides, box, es,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return DTF_ERR_TENSORMAP;
+  }
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)n_out, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n_img};
+    cuuint64_t strides[3] = {(cuuint64_t)n_out * 2, (cuuint64_t)W * n_out * 2, (cuuint64_t)H * W * n_out * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)p.Wt, 1, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    if (fn(&tdy, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(dy), dims, strides, box, es,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return DTF_ERR_TENSORMAP;
+  }
+  const int smem = WG_STAGES * (p.a_stage_bytes + WG_B_BYTES) + 256 + 1024;
+  if (smem > 227 * 1024) return DTF_ERR_TOO_LARGE;
+  static int attr[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr[dev & 63] < smem) {
+    if (cudaFuncSetAttribute(wgrad_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+      return DTF_ERR_CUDA;
+    attr[dev & 63] = smem;
+  }
+  dim3 grid(n_out / 64, C / 64, splits);
+  wgrad_halo_kernel<<<grid, NUM_THREADS, smem, reinterpret_cast<cudaStream_t>(stream_)>>>(tx, tdy, p);
+  return DTF_CHECK_LAUNCH();
 }

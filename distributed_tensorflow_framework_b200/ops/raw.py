@@ -129,6 +129,9 @@ def conv_wgrad(x, dy, KH, KW, stride=1, out=None):
         stride = 1
     if KH == 1 and KW == 1 and stride == 1:  # dW = x^T dy: dense MN-major A operand, split over pixels
         return gemm(x.reshape(-1, C), dy.view(-1, Co), a_transposed=True, out=out, accumulate=True)
+    if stride == 1 and USE_HALO and _lib.lib().dtf_conv_wgrad_halo_supported(H, W, C, KH, KW, Co):
+        _lib.call("dtf_conv_wgrad_halo_bf16", x, dy, out, n, H, W, C, KH, KW, Co, pt, pl, _sp())
+        return out
     _lib.call("dtf_conv_wgrad_bf16", x, dy, out, n, H, W, C, OH, OW, KH, KW, Co, stride, pt, pl, _sp())
     return out
 

@@ -59,6 +59,13 @@ int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int n_out);
 int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H, int W, int C,
                        int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags, void* stream);
 
+/* Halo-tile filter gradient (stride 1, C % 64 == 0, n_out % 64 == 0, <= 16 taps): x halo + dy tile per image tile,
+ * all taps accumulate in TMEM (tap pairs share one M=128 MMA through the descriptor's leading-dimension offset),
+ * one red.add pass into dW at the end. dW is fp32 and accumulated: zero it first. */
+int dtf_conv_wgrad_halo_supported(int H, int W, int C, int KH, int KW, int n_out);
+int dtf_conv_wgrad_halo_bf16(const void* x, const void* dy, float* dw, int n_img, int H, int W, int C, int KH, int KW,
+                             int n_out, int pad_h, int pad_w, void* stream);
+
 /* Filter gradient dW[KH*KW*C, n_out] (fp32, red.add accumulated; zero it first) from x[n_img,H,W,C] and
  * dy[n_img,PH,PW,n_out]. Backward of the conv layers above (TF autodiff, distribute_tower.py:26-27). */
 int dtf_conv_wgrad_bf16(const void* x, const void* dy, float* dw, int n_img, int H, int W, int C, int PH, int PW,
