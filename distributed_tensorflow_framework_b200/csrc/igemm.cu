@@ -65,6 +65,77 @@ struct PixelCoord {
   int n, y, x;
 };
 
+// Fused epilogue of one 128 x BN accumulator tile: TMEM -> registers -> (bias, ReLU) -> bf16 / fp32 store or
+// split-K red.add. Called by the four epilogue warps (warp index == TMEM lane quarter).
+template <int BN>
+__device__ __forceinline__ void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, int tile_m, int tile_n,
+                                               int warp) {
+  const int r = threadIdx.x;  // accumulator row == TMEM lane
+  const int m = tile_m * BLOCK_M + r;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+  for (int cc = 0; cc < BN / 32; ++cc) {
+    uint32_t v[32];
+    tmem_ld32(lane_addr + cc * 32, v);
+    tmem_ld_wait();
+    const int n0 = tile_n * BN + cc * 32;
+    if (m < p.M && n0 < p.N) {
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (n0 + j < p.N) f[j] += __ldg(p.bias + n0 + j);
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
+      const bool full = (n0 + 32 <= p.N);
+      if (p.atomic) {
+        float* o = reinterpret_cast<float*>(p.out) + (size_t)m * p.ldc + n0;
+        if (full && ((p.ldc & 3) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(o + j), "f"(f[j]), "f"(f[j + 1]),
+                         "f"(f[j + 2]), "f"(f[j + 3])
+                         : "memory");
+        } else {
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.N) red_add_f32(o + j, f[j]);
+        }
+      } else if (p.out_fp32) {
+        float* o = reinterpret_cast<float*>(p.out) + (size_t)m * p.ldc + n0;
+        if (full && ((p.ldc & 3) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
+        } else {
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.N) o[j] = f[j];
+        }
+      } else {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.ldc + n0;
+        if (full && ((p.ldc & 7) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 q;
+            q.x = pack_bf16x2(f[j], f[j + 1]);
+            q.y = pack_bf16x2(f[j + 2], f[j + 3]);
+            q.z = pack_bf16x2(f[j + 4], f[j + 5]);
+            q.w = pack_bf16x2(f[j + 6], f[j + 7]);
+            *reinterpret_cast<uint4*>(o + j) = q;
+          }
+        } else {
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.N) o[j] = __float2bfloat16(f[j]);
+        }
+      }
+    }
+  }
+}
+
 // K-AG-GEMM support: the B operand (weights) is sharded over the ranks of a parameter-server group and is NOT
 // gathered beforehand: the TMA producer picks, per k-block (mode 1: B sharded by rows / K) or per n-tile (mode 2:
 // B sharded by columns / N), the tensor map that points into the OWNER's symmetric heap, so weight tiles cross
@@ -308,70 +379,7 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
     // ----------------------------------------------------- epilogue: TMEM -> registers -> global
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    const int r = threadIdx.x;  // accumulator row == TMEM lane
-    const int m = tile_m * BLOCK_M + r;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
-#pragma unroll 1
-    for (int cc = 0; cc < BN / 32; ++cc) {
-      uint32_t v[32];
-      tmem_ld32(lane_addr + cc * 32, v);
-      tmem_ld_wait();
-      const int n0 = tile_n * BN + cc * 32;
-      if (m < p.M && n0 < p.N) {
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (p.bias != nullptr) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (n0 + j < p.N) f[j] += __ldg(p.bias + n0 + j);
-        }
-        if (p.relu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-        }
-        const bool full = (n0 + 32 <= p.N);
-        if (p.atomic) {
-          float* o = reinterpret_cast<float*>(p.out) + (size_t)m * p.ldc + n0;
-          if (full && ((p.ldc & 3) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(o + j), "f"(f[j]), "f"(f[j + 1]),
-                           "f"(f[j + 2]), "f"(f[j + 3])
-                           : "memory");
-          } else {
-            for (int j = 0; j < 32; ++j)
-              if (n0 + j < p.N) red_add_f32(o + j, f[j]);
-          }
-        } else if (p.out_fp32) {
-          float* o = reinterpret_cast<float*>(p.out) + (size_t)m * p.ldc + n0;
-          if (full && ((p.ldc & 3) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-              *reinterpret_cast<float4*>(o + j) = make_float4(f[j], f[j + 1], f[j + 2], f[j + 3]);
-          } else {
-            for (int j = 0; j < 32; ++j)
-              if (n0 + j < p.N) o[j] = f[j];
-          }
-        } else {
-          __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.ldc + n0;
-          if (full && ((p.ldc & 7) == 0)) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 q;
-              q.x = pack_bf16x2(f[j], f[j + 1]);
-              q.y = pack_bf16x2(f[j + 2], f[j + 3]);
-              q.z = pack_bf16x2(f[j + 4], f[j + 5]);
-              q.w = pack_bf16x2(f[j + 6], f[j + 7]);
-              *reinterpret_cast<uint4*>(o + j) = q;
-            }
-          } else {
-            for (int j = 0; j < 32; ++j)
-              if (n0 + j < p.N) o[j] = __float2bfloat16(f[j]);
-          }
-        }
-      }
-    }
+    igemm_epilogue<BN>(p, tmem_base, tile_m, tile_n, warp);
   } else if (warp == 4) {
     // ===================================================== MMA issuer
     constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, /*b_mn=*/true);
@@ -431,6 +439,155 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
     tc_fence_after();
     tmem_dealloc<BN>(tmem_base);
   }
+}
+
+
+// Persistent variant for the TMA-fed (dense) modes: one CTA per SM slot walks tiles t = blockIdx.x, +gridDim.x, ...
+// The TMA producer keeps the smem ring full ACROSS tiles, the accumulator is double buffered in TMEM (2 x BN
+// columns), so the epilogue of tile i (tcgen05.ld + stores) overlaps the loads and MMAs of tile i+1, and the
+// per-tile costs of the one-shot kernel (launch, TMEM alloc, barrier init, exposed first-load latency) are paid once.
+template <int BN, int STAGES, int AMODE>
+__global__ void __launch_bounds__(NUM_THREADS)
+igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                        const IgemmParams p, int tiles_m, int tiles_n, int splits) {
+  static_assert(AMODE == A_TMA_K || AMODE == A_TMA_MN, "persistent kernel is for the TMA-fed modes");
+  using L = SmemLayout<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFFSET);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* acc_full = empty_bar + STAGES;   // [2]
+  uint64_t* acc_empty = acc_full + 2;        // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr bool kAMn = (AMODE == A_TMA_MN);
+  const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
+  const int total_tiles = tiles_m * tiles_n * splits;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], 4);  // one arrival per epilogue warp
+    }
+    mbar_fence_init();
+  }
+  if (warp == 4) tmem_alloc<2 * BN>(tmem_slot);
+  if (warp == 5 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t smem_base = smem_u32(smem);
+  auto a_stage = [&](int s) { return smem_base + s * L::STAGE_BYTES; };
+  auto b_stage = [&](int s) { return smem_base + s * L::STAGE_BYTES + L::A_BYTES; };
+  auto decode = [&](int t, int& tile_m, int& tile_n, int& kb0, int& kb1) {
+    tile_n = t % tiles_n;
+    const int r = t / tiles_n;
+    tile_m = r % tiles_m;
+    const int z = r / tiles_m;
+    kb0 = z * p.kb_per_split;
+    kb1 = min(total_kb, kb0 + p.kb_per_split);
+  };
+
+  if (warp == 5) {
+    if (lane == 0) {
+      int it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        int tile_m, tile_n, kb0, kb1;
+        decode(t, tile_m, tile_n, kb0, kb1);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % STAGES;
+          mbar_wait(&empty_bar[s], ((it / STAGES) & 1) ^ 1);
+          mbar_arrive_expect_tx(&full_bar[s], L::STAGE_BYTES);
+          if constexpr (AMODE == A_TMA_K) {
+            tma_load_2d(a_stage(s), &tma_a, &full_bar[s], kb * BLOCK_K, tile_m * BLOCK_M);
+          } else {
+            tma_load_2d(a_stage(s), &tma_a, &full_bar[s], tile_m * BLOCK_M, kb * BLOCK_K);
+            tma_load_2d(a_stage(s) + 8192, &tma_a, &full_bar[s], tile_m * BLOCK_M + 64, kb * BLOCK_K);
+          }
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j)
+            tma_load_2d(b_stage(s) + j * 8192, &tma_b, &full_bar[s], tile_n * BN + j * 64, kb * BLOCK_K);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 4) {
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, true);
+    int it = 0, lt = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
+      int tile_m, tile_n, kb0, kb1;
+      decode(t, tile_m, tile_n, kb0, kb1);
+      const int buf = lt & 1;
+      mbar_wait(&acc_empty[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+      tc_fence_after();
+      for (int kb = kb0; kb < kb1; ++kb, ++it) {
+        const int s = it % STAGES;
+        mbar_wait(&full_bar[s], (it / STAGES) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            uint64_t adesc;
+            if constexpr (kAMn) adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 128), 8192, 1024);
+            else adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 2), 16, 1024);
+            const uint64_t bdesc = make_smem_desc(b_stage(s) + k * (UMMA_K * 128), 8192, 1024);
+            umma_bf16(tmem_base + buf * BN, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
+          if (kb == kb1 - 1) umma_commit(&acc_full[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    int lt = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
+      int tile_m, tile_n, kb0, kb1;
+      decode(t, tile_m, tile_n, kb0, kb1);
+      const int buf = lt & 1;
+      mbar_wait(&acc_full[buf], (lt >> 1) & 1);
+      tc_fence_after();
+      igemm_epilogue<BN>(p, tmem_base + buf * BN, tile_m, tile_n, warp);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<2 * BN>(tmem_base);
+  }
+}
+
+template <int BN, int STAGES, int AMODE>
+static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
+                             cudaStream_t stream) {
+  using L = SmemLayout<BN, STAGES>;
+  static bool attr_set[64] = {};
+  auto kern = igemm_persistent_kernel<BN, STAGES, AMODE>;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) != cudaSuccess)
+      return DTF_ERR_CUDA;
+    attr_set[dev & 63] = true;
+  }
+  const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M;
+  const int total = tiles_n * tiles_m * splits;
+  const int per_sm = (L::TOTAL <= 110 * 1024) ? 2 : 1;
+  const int grid = total < 148 * per_sm ? total : 148 * per_sm;
+  kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(ta, tb, p, tiles_m, tiles_n, splits);
+  return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
 template <int BN, int STAGES, int AMODE>
@@ -522,12 +679,25 @@ static int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, const Igem
   return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
+static int g_use_persistent = 1;
+static int g_wide_tiles = 1;
+
 template <int AMODE>
 static int dispatch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
                        cudaStream_t stream) {
   // few k-blocks per tile: a deep ring is useless, so use 2 stages and let more CTAs share an SM (their
   // prologues / epilogues overlap with each other's main loops)
   const bool shallow = p.kb_per_split <= 2;
+  if constexpr (AMODE == A_TMA_K || AMODE == A_TMA_MN) {
+    if (g_use_persistent) {
+      if (p.N <= 64) return launch_persistent<64, 4, AMODE>(ta, tb, p, splits, stream);
+      // 128 x 256 tiles halve the A re-reads and make the tile MMA-bound instead of smem-bound; use them when
+      // there are still enough tiles to fill the machine
+      const long long tiles256 = (long long)((p.M + BLOCK_M - 1) / BLOCK_M) * ((p.N + 255) / 256) * splits;
+      if (g_wide_tiles && p.N >= 256 && tiles256 >= 148) return launch_persistent<256, 3, AMODE>(ta, tb, p, splits, stream);
+      return launch_persistent<128, 3, AMODE>(ta, tb, p, splits, stream);
+    }
+  }
   if (p.N <= 64) {
     if (shallow) return launch_igemm<64, 2, AMODE>(ta, tb, p, splits, stream);
     return launch_igemm<64, 4, AMODE>(ta, tb, p, splits, stream);
@@ -549,6 +719,14 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 }  // namespace dtf
 
 using namespace dtf;
+
+// 1 (default): dense TMA-fed GEMMs use the persistent, TMEM-double-buffered kernel; 0: one tile per CTA.
+extern "C" int dtf_set_persistent_gemm(int on) {
+  const int prev = g_use_persistent | (g_wide_tiles << 1);
+  g_use_persistent = on & 1;
+  g_wide_tiles = (on >> 1) & 1;
+  return prev;
+}
 
 // flags
 //   bit0 relu, bit1 out_fp32, bit2 atomic accumulate into fp32 out (split-K allowed), bit3 A is stored [K,M]

@@ -34,6 +34,11 @@ extern "C" {
 int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
                   int ldc, int flags, void* stream);
 
+/* Dense GEMMs run a persistent kernel (tile loop per CTA, smem ring kept full across tiles, accumulator double
+ * buffered in TMEM so the epilogue overlaps the next tile). bit0 of `on`: persistent kernel (0 = one tile per CTA);
+ * bit1: allow 128x256 tiles for N >= 256. Default 3. Returns the previous setting. */
+int dtf_set_persistent_gemm(int on);
+
 /* K-AG-GEMM: the all-gather of parameter-server weights fused into the consuming GEMM. B is sharded over the heaps
  * of `world` ranks (peer_b[r] = rank r's mapping of the matrix, `bounds` = owned arena ranges, b_arena_off = arena
  * offset of the matrix); the TMA producer reads every tile from its OWNER over NVLink, no gather pass and no local
