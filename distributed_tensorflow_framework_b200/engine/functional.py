@@ -14,10 +14,6 @@ from . import variables as V
 bf16 = torch.bfloat16
 
 
-def _store_of(var):
-    return getattr(var, "_store", None) or V.default_store()
-
-
 def _ready(var):
     st = getattr(var, "_store", None)
     if st is not None:

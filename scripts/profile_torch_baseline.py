@@ -4,9 +4,10 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(
 import torch, torch.nn.functional as F
 import torch_baseline as tb
 torch.backends.cudnn.benchmark = True
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
 model = tb.build("ResNet50").cuda().to(memory_format=torch.channels_last)
 opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9)
-x = torch.rand(64, 3, 224, 224, device="cuda").contiguous(memory_format=torch.channels_last); y = torch.randint(0, 1000, (64,), device="cuda")
+x = torch.rand(B, 3, 224, 224, device="cuda").contiguous(memory_format=torch.channels_last); y = torch.randint(0, 1000, (B,), device="cuda")
 def step():
     with torch.autocast("cuda", dtype=torch.bfloat16):
         loss = F.cross_entropy(model(x).float(), y)

@@ -62,3 +62,45 @@ def test_conv_family(raw, n, H, W, Ci, Co, KH, KW, s):
     w_t = w.permute(0, 1, 3, 2).contiguous().reshape(KH * KW * Co, Ci)
     close(raw.conv_dgrad(dy, w_t, (H, W), KH, KW, s), xf.grad.permute(0, 2, 3, 1))
     close(raw.conv_wgrad(x, dy, KH, KW, s).view(KH, KW, Ci, Co), wf.grad.permute(2, 3, 1, 0), 3e-2)
+
+
+def test_halo_kernels_match_the_gather_kernels(raw):
+    """The halo-tile fprop / dgrad / wgrad kernels against the im2col-gather kernels on the same problem."""
+    n, H, W, Ci, Co, k = 3, 28, 28, 128, 64, 3
+    x, dy = rnd(n, H, W, Ci), rnd(n, H, W, Co)
+    w = (torch.randn(k, k, Ci, Co, device="cuda") * 0.05).to(torch.bfloat16)
+    w2 = w.reshape(k * k * Ci, Co)
+    wt = w.permute(0, 1, 3, 2).contiguous().reshape(k * k * Co, Ci)
+    assert raw._lib.lib().dtf_conv_halo_supported(H, W, Ci, k, k, Co) == 1
+    assert raw._lib.lib().dtf_conv_wgrad_halo_supported(H, W, Ci, k, k, Co) == 1
+    got = (raw.conv_fprop(x, w2, None, k, k, 1), raw.conv_dgrad(dy, wt, (H, W), k, k, 1), raw.conv_wgrad(x, dy, k, k, 1))
+    raw.USE_HALO = False
+    try:
+        ref = (raw.conv_fprop(x, w2, None, k, k, 1), raw.conv_dgrad(dy, wt, (H, W), k, k, 1),
+               raw.conv_wgrad(x, dy, k, k, 1))
+    finally:
+        raw.USE_HALO = True
+    for g, r in zip(got, ref):
+        close(g, r, 1e-2)
+
+
+def test_persistent_gemm_matches_one_tile_per_cta(raw):
+    a, b = rnd(1000, 320), rnd(320, 512)
+    bias = torch.randn(512, device="cuda")
+    y_p = raw.gemm(a, b, bias, relu=True)
+    prev = raw._lib.lib().dtf_set_persistent_gemm(0)
+    try:
+        y_1 = raw.gemm(a, b, bias, relu=True)
+    finally:
+        raw._lib.lib().dtf_set_persistent_gemm(prev)
+    assert torch.equal(y_p, y_1)
+
+
+def test_strided_pixel_select_and_scatter(raw):
+    x = rnd(2, 9, 10, 16)
+    y = raw.subsample(x, 2)
+    assert torch.equal(y, x[:, ::2, ::2, :])
+    back = raw.upsample_zero(y, (9, 10), 2)
+    ref = torch.zeros_like(x)
+    ref[:, ::2, ::2, :] = y
+    assert torch.equal(back, ref)
