@@ -47,6 +47,7 @@ static_assert((HEARTBEAT_OFF + MAX_RANKS) * 4 <= FLAG_PAGE_BYTES, "flag page too
 struct CommCtx {
   int rank, world;
   uint8_t* peer[MAX_RANKS];  // heap base of every rank as mapped in this process (peer[rank] is local)
+  uint8_t* mc;               // NVLS multicast mapping of the heap (nullptr when not available)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -229,6 +230,54 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float
   block_barrier(c);  // all shards have landed everywhere; gradients may be overwritten
 }
 
+// ---- K-RS-OPT over NVLS: the owner reduces its slice with ONE multimem.ld_reduce per 16 bytes (the NVSwitch pulls the
+// eight copies and adds them in the switch), applies the optimizer, and publishes the new bf16 weights with ONE
+// multimem.st (the switch replicates the store into every GPU's shadow arena). Wire bytes per GPU drop from
+// 2 (N-1)/N S to about S/N in each direction.
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const void* mc_addr) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];\n"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc_addr)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_b64(void* mc_addr, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};\n" ::"l"(mc_addr), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y))
+               : "memory");
+}
+__global__ void __launch_bounds__(512)
+rs_optim_ag_nvls_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float* master, float* m, float* v,
+                        size_t shadow_off, NoPush np) {
+  block_barrier(c);
+  const long long start = bounds.b[c.rank];
+  const long long n4 = (bounds.b[c.rank + 1] - start) >> 2;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const float4* gmc = reinterpret_cast<const float4*>(c.mc + grad_off) + (start >> 2);
+  for (long long q0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * COMM_U) {
+    float4 gs[COMM_U];
+#pragma unroll
+    for (int u = 0; u < COMM_U; ++u) {
+      const long long q = q0 + u * stride;
+      gs[u] = (q < n4) ? multimem_ld_reduce_f4(gmc + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < COMM_U; ++u) {
+      const long long q = q0 + u * stride;
+      if (q >= n4) continue;
+      const long long i = start + (q << 2);
+      const float4 p = optim4(o, master, m, v, i, gs[u]);
+      const uint2 pb = pack4_bf16(p);
+      if (in_nopush(np, i))
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[c.rank] + shadow_off) + i) = pb;
+      else
+        multimem_st_b64(reinterpret_cast<__nv_bfloat16*>(c.mc + shadow_off) + i, pb);
+    }
+  }
+  block_barrier(c);
+}
+
 // ---- all-gather of owned slices by peer stores (16-byte units): used for checkpoint gathers and weight pulls.
 __global__ void __launch_bounds__(512)
 allgather_slices_kernel(CommCtx c, size_t buf_off, Bounds bounds16) {
@@ -400,6 +449,11 @@ extern "C" int dtf_comm_destroy(void* comm) {
   delete c;
   return DTF_OK;
 }
+// Attach the NVLS multicast mapping of the heap (from cuMulticast* / torch symmetric memory); 0 detaches it.
+extern "C" int dtf_comm_set_multicast(void* comm, void* mc_base) {
+  reinterpret_cast<DtfComm*>(comm)->ctx.mc = reinterpret_cast<uint8_t*>(mc_base);
+  return DTF_OK;
+}
 extern "C" void* dtf_comm_peer_ptr(void* comm, int r) { return reinterpret_cast<DtfComm*>(comm)->ctx.peer[r]; }
 
 static OptimArgs make_optim(int kind, float lr, float b1, float b2, float eps, float wd, float gscale,
@@ -455,8 +509,12 @@ extern "C" int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long
     np.hi[k] = nopush_ranges[2 * k + 1];
     np.n = k + 1;
   }
-  rs_optim_ag_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
-                                                           master_off, np);
+  if (c->ctx.mc != nullptr && master_off == (size_t)-1)
+    rs_optim_ag_nvls_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
+                                                                  np);
+  else
+    rs_optim_ag_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
+                                                             master_off, np);
   return DTF_CHECK_LAUNCH();
 }
 // bounds16 in units of 16 bytes relative to buf_off

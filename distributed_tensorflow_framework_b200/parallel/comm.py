@@ -29,16 +29,38 @@ class _RawCuda(object):
 
 
 class SymmetricHeap(object):
-    def __init__(self, nbytes, device):
+    """backend 'ipc': cudaMalloc + CUDA IPC handles (default). backend 'nvls': torch symmetric memory (VMM
+    allocation bound to an NVLS multicast object); gives the same peer pointers plus `multicast_ptr`, which lets
+    K-RS-OPT reduce and broadcast inside the NVSwitch (multimem.ld_reduce / multimem.st)."""
+
+    def __init__(self, nbytes, device, backend="ipc", group=None):
         self.device = torch.device(device)
         self.nbytes = int(nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
-        ptr = ctypes.c_void_p()
-        self.handle = ctypes.create_string_buffer(64)
-        with torch.cuda.device(self.device):
-            _lib.call("dtf_comm_heap_alloc", self.nbytes, ctypes.byref(ptr), self.handle)
-        self.ptr = ptr.value
-        self._raw = _RawCuda(self.ptr, self.nbytes)
-        self.bytes = torch.as_tensor(self._raw, device=self.device)
+        self.backend = backend
+        self.peer_ptrs = None
+        self.multicast_ptr = 0
+        if backend == "nvls":
+            import torch.distributed as dist
+            import torch.distributed._symmetric_memory as symm
+            group = group or dist.group.WORLD
+            self.nbytes = (self.nbytes + (2 << 20) - 1) // (2 << 20) * (2 << 20)
+            self.bytes = symm.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+            self._hdl = symm.rendezvous(self.bytes, group.group_name)
+            self.bytes.zero_()
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=group)
+            self.ptr = self.bytes.data_ptr()
+            self.peer_ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+            self.multicast_ptr = int(self._hdl.multicast_ptr or 0)
+            self.handle = None
+        else:
+            ptr = ctypes.c_void_p()
+            self.handle = ctypes.create_string_buffer(64)
+            with torch.cuda.device(self.device):
+                _lib.call("dtf_comm_heap_alloc", self.nbytes, ctypes.byref(ptr), self.handle)
+            self.ptr = ptr.value
+            self._raw = _RawCuda(self.ptr, self.nbytes)
+            self.bytes = torch.as_tensor(self._raw, device=self.device)
         self._top = _lib.lib().dtf_comm_flag_page_bytes()  # the flag page sits at offset 0
         self.allocs = {}
 
@@ -57,7 +79,7 @@ class SymmetricHeap(object):
         return self.allocs[tag][0]
 
     def free(self):
-        if self.ptr:
+        if self.ptr and self.backend == "ipc":
             _lib.call("dtf_comm_heap_free", ctypes.c_void_p(self.ptr))
             self.ptr = None
 
@@ -69,7 +91,12 @@ class Communicator(object):
         self.stream = torch.cuda.Stream(device=heap.device)
         self.blocks = 64
         self._version = 0
-        if local_heaps is not None:  # single process driving several peer-enabled GPUs (tests)
+        if heap.peer_ptrs is not None:  # peers already mapped (torch symmetric memory / NVLS backend)
+            arr = (ctypes.c_void_p * world)(*heap.peer_ptrs)
+            _lib.call("dtf_comm_create_local", rank, world, arr, heap.nbytes, ctypes.byref(self.handle))
+            if heap.multicast_ptr:
+                _lib.call("dtf_comm_set_multicast", self.handle, ctypes.c_void_p(heap.multicast_ptr))
+        elif local_heaps is not None:  # single process driving several peer-enabled GPUs (tests)
             arr = (ctypes.c_void_p * world)(*[h.ptr for h in local_heaps])
             _lib.call("dtf_comm_create_local", rank, world, arr, heap.nbytes, ctypes.byref(self.handle))
         else:
@@ -172,6 +199,9 @@ class GradientEngine(object):
         self.overlap = overlap and algo in ("oneshot", "nccl", "twoshot", "twoshot_pull")
         self.comm = None
         self.heap = None
+        self.nvls = algo == "twoshot_nvls"
+        if self.nvls:
+            algo = self.algo = "twoshot"
         self.pull = algo == "twoshot_pull"
         if self.pull:
             algo = self.algo = "twoshot"
@@ -179,7 +209,7 @@ class GradientEngine(object):
         if use_heap:
             mailbox = n_est * 4 * 1 if algo == "async" else 0
             need = n_est * (4 + 4 + 2 + 2 + 4 + 4) + mailbox * max(world, 1) + (1 << 20) + heap_extra_bytes
-            self.heap = SymmetricHeap(need, dev)
+            self.heap = SymmetricHeap(need, dev, backend="nvls" if (self.nvls and world > 1) else "ipc", group=group)
             store.finalize(allocator=self.heap.alloc, placement=placement, world=world, slots=optimizer.num_slots())
             if algo == "async":
                 per = max(store.owner_bounds[i + 1] - store.owner_bounds[i] for i in range(world))

@@ -181,6 +181,9 @@ int dtf_comm_create(int rank, int world, void* local_heap, size_t heap_bytes, co
 int dtf_comm_create_local(int rank, int world, void* const* heaps, size_t heap_bytes, void** comm_out);
 int dtf_comm_destroy(void* comm);
 void* dtf_comm_peer_ptr(void* comm, int r);
+/* NVLS: attach the multicast mapping of the heap; K-RS-OPT then reduces with multimem.ld_reduce (in-switch add) and
+ * publishes weights with multimem.st (in-switch replication). */
+int dtf_comm_set_multicast(void* comm, void* mc_base);
 
 /* K-AR: one-shot allreduce of grad[start, start+count) (heap offset grad_off) fused with x gscale and the optimizer
  * update of the local replica. Replaces Tower.average_gradients + apply (distribute_tower.py:78-114). With

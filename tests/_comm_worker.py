@@ -114,7 +114,7 @@ def main():
 
     # ---- Trainer level: data-parallel CIFAR CNN, every algorithm
     curves = {}
-    for algo in ("oneshot", "twoshot", "twoshot_pull", "nccl", "async"):
+    for algo in ("oneshot", "twoshot", "twoshot_pull", "twoshot_nvls", "nccl", "async"):
         torch.manual_seed(100 + rank)
         x = torch.rand(32, 32, 32, 3)
         y = torch.randint(0, 10, (32,))
@@ -125,6 +125,10 @@ def main():
         check(all(l == l for l in losses), "%s: NaN loss" % algo)
         check(losses[-1] < losses[0], "%s: loss did not decrease %s" % (algo, losses))
         curves[algo] = losses
+        if algo == "twoshot_nvls":
+            check(tr.engine.heap.multicast_ptr != 0, "no NVLS multicast mapping")
+            diff = max(abs(a - b) for a, b in zip(losses, curves["twoshot"]))
+            check(diff < 2e-2, "NVLS path deviates from the P2P path: %s vs %s" % (losses, curves["twoshot"]))
         if algo == "twoshot_pull":
             check(len(tr.engine.nopush) == 2, "pull mode should cover local3 and local4 weights")
             diff = max(abs(a - b) for a, b in zip(losses, curves["twoshot"]))
