@@ -199,7 +199,8 @@ def run_ours(args, cfg):
         "dtype": "bf16", "data": "synthetic (uint8 images of the named shape, random labels; random-init weights)",
         "impl": "ours",
         "config": {"model": cfg["model"], "desc": cfg["desc"], "global_batch": gb, "per_gpu_batch": batch,
-                   "image": list(cfg["shape"]), "parallelism": "dp%d" % world, "collective": trainer.algo,
+                   "image": list(cfg["shape"]), "parallelism": "dp%d" % world,
+                   "collective": trainer.algo + ("_nvls" if getattr(trainer.engine, "nvls", False) else ""),
                    "optimizer": "momentum", "cuda_graph": bool(trainer._graph is not None),
                    "l2": "256 MiB write between timed steps (outside the event pairs)"},
         "e2e": {"value": gb * args.steps / e2e_s, "unit": "images/s",

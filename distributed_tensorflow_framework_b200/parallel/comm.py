@@ -194,9 +194,17 @@ class GradientEngine(object):
         dev = store.device
         n_est = sum((v.numel + 7) // 8 * 8 for v in store.trainable_variables())
         if algo == "auto":
-            algo = "local" if world == 1 else ("oneshot" if n_est * 4 <= (16 << 20) else "twoshot")
+            # small model on a pair of GPUs: one-shot K-AR (one kernel, replicated masters). Otherwise the two-shot
+            # K-RS-OPT, over NVLS (in-switch reduce / broadcast) when a multicast mapping can be had.
+            if world == 1:
+                algo = "local"
+            elif world <= 2 and n_est * 4 <= (16 << 20):
+                algo = "oneshot"
+            else:
+                import os
+                algo = "twoshot_nvls" if os.environ.get("DTF_NVLS", "1") != "0" else "twoshot"
         self.algo = algo
-        self.overlap = overlap and algo in ("oneshot", "nccl", "twoshot", "twoshot_pull")
+        self.overlap = overlap and algo in ("oneshot", "nccl", "twoshot", "twoshot_pull", "twoshot_nvls")
         self.comm = None
         self.heap = None
         self.nvls = algo == "twoshot_nvls"
@@ -209,7 +217,12 @@ class GradientEngine(object):
         if use_heap:
             mailbox = n_est * 4 * 1 if algo == "async" else 0
             need = n_est * (4 + 4 + 2 + 2 + 4 + 4) + mailbox * max(world, 1) + (1 << 20) + heap_extra_bytes
-            self.heap = SymmetricHeap(need, dev, backend="nvls" if (self.nvls and world > 1) else "ipc", group=group)
+            self.heap = None
+            if self.nvls and world > 1:
+                self.heap = self._try_nvls_heap(need, dev, group)
+            if self.heap is None:
+                self.nvls = False
+                self.heap = SymmetricHeap(need, dev, backend="ipc")
             store.finalize(allocator=self.heap.alloc, placement=placement, world=world, slots=optimizer.num_slots())
             if algo == "async":
                 per = max(store.owner_bounds[i + 1] - store.owner_bounds[i] for i in range(world))
@@ -246,6 +259,22 @@ class GradientEngine(object):
         if self.overlap:
             store.grad_ready_hook = self._on_grad_ready
         self.kernel_launches = 0
+
+    def _try_nvls_heap(self, need, dev, group):
+        """NVLS heap through torch symmetric memory; every rank must succeed, otherwise all fall back to CUDA IPC."""
+        import torch.distributed as dist
+        heap, ok = None, 1
+        try:
+            heap = SymmetricHeap(need, dev, backend="nvls", group=group)
+            if not heap.multicast_ptr:
+                ok = 0
+        except Exception as e:  # no multicast support, old driver, fabric not configured ...
+            from ..api import log as logger
+            logger.warn("NVLS heap unavailable (%s); using CUDA IPC peer mappings", str(e)[:120])
+            ok = 0
+        flag = torch.tensor([ok], device=dev, dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        return heap if int(flag.item()) == 1 else None
 
     def _setup_pull(self):
         """Parameter-server PULL fused into the consumer (K-AG-GEMM): large FC weights are not broadcast after the
