@@ -159,8 +159,10 @@ __global__ void __launch_bounds__(256)
 colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __restrict__ in1,
                  const __nv_bfloat16* __restrict__ in2, __nv_bfloat16* __restrict__ out, float* __restrict__ acc,
                  const float* __restrict__ mean, const float* __restrict__ rstd, long long R, int N, int relu,
-                 int rows_per_block, float* __restrict__ part) {
+                 int rows_per_block, float* __restrict__ part, const float* __restrict__ msc = nullptr,
+                 const float* __restrict__ msh = nullptr) {
   constexpr int NACC = (MODE >= 2) ? 2 : 1;
+  constexpr bool kBnBwd = (MODE == 3 || MODE == 4);  // MODE 4: batch-norm backward with the mask recomputed from x
   const int cpr = N / 8;
   const int cg0 = blockIdx.x * 256;
   const int cprg = min(256, cpr - cg0);
@@ -172,18 +174,23 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
   float a0[8], a1[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) a0[j] = a1[j] = 0.f;
-  float mu[8], rs[8];
-  if (MODE == 3 && active) {
+  float mu[8], rs[8], ksc[8], ksh[8];
+  // relu == 2 (MODE 3): the ReLU mask is recomputed from x (y > 0 <=> x*scale + shift > 0), so neither y is read
+  // nor dz written -- two of the seven passes of the batch-norm backward disappear
+  constexpr bool mask_from_x = (MODE == 4);
+  if (kBnBwd && active) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       mu[j] = mean[col_chunk * 8 + j];
       rs[j] = rstd[col_chunk * 8 + j];
+      ksc[j] = mask_from_x ? msc[col_chunk * 8 + j] : 0.f;
+      ksh[j] = mask_from_x ? msh[col_chunk * 8 + j] : 0.f;
     }
   }
   const long long r0 = (long long)blockIdx.y * rows_per_block;
   const long long r1 = min(R, r0 + rows_per_block);
   if (active) {
-    constexpr int U = (MODE == 3) ? 4 : 8;  // rows in flight per thread (memory-level parallelism)
+    constexpr int U = kBnBwd ? 4 : 8;  // rows in flight per thread (memory-level parallelism)
     for (long long rb = r0 + row_lane; rb < r1; rb += (long long)rpp * U) {
       BF8 b0[U], b1[U], b2[U];
       bool ok[U];
@@ -194,8 +201,8 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
         if (ok[u]) {
           const long long off = r * N + (long long)col_chunk * 8;
           b0[u] = ld8(in0 + off);
-          if (MODE == 1 || (MODE == 3 && relu)) b1[u] = ld8(in1 + off);
-          if (MODE == 3) b2[u] = ld8(in2 + off);
+          if (MODE == 1 || (MODE == 3 && relu == 1)) b1[u] = ld8(in1 + off);
+          if (kBnBwd) b2[u] = ld8(in2 + off);
         }
       }
 #pragma unroll
@@ -204,11 +211,17 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
         const long long off = (rb + (long long)u * rpp) * N + (long long)col_chunk * 8;
         float g[8];
         unpack8(b0[u], g);
-        if (MODE == 1 || (MODE == 3 && relu)) {
+        if (MODE == 1 || (MODE == 3 && relu == 1)) {
           float y[8];
           unpack8(b1[u], y);
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] = y[j] > 0.f ? g[j] : 0.f;
+        }
+        if (mask_from_x) {
+          float xm[8];
+          unpack8(b2[u], xm);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = fmaf(xm[j], ksc[j], ksh[j]) > 0.f ? g[j] : 0.f;
         }
         if ((MODE == 1 || MODE == 3) && out != nullptr) st8(out + off, pack8(g));
         if (MODE == 2) {
@@ -217,7 +230,7 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
             a0[j] += g[j];
             a1[j] = fmaf(g[j], g[j], a1[j]);
           }
-        } else if (MODE == 3) {
+        } else if (kBnBwd) {
           float x[8];
           unpack8(b2[u], x);
 #pragma unroll
@@ -294,13 +307,14 @@ static void elementwise_geometry(long long R, int N, int* gx_out, int* gy_out, i
 
 template <int MODE>
 static int launch_colreduce(const void* in0, const void* in1, const void* in2, void* out, float* acc, float* part,
-                            const float* mean, const float* rstd, long long R, int N, int relu, cudaStream_t st) {
+                            const float* mean, const float* rstd, long long R, int N, int relu, cudaStream_t st,
+                            const float* msc = nullptr, const float* msh = nullptr) {
   if (N % 8) return DTF_ERR_ALIGN;
   int gx, gy, rows_per_block;
   colreduce_geometry(R, N, &gx, &gy, &rows_per_block);
   colreduce_kernel<MODE><<<dim3(gx, gy), 256, 0, st>>>(
       (const __nv_bfloat16*)in0, (const __nv_bfloat16*)in1, (const __nv_bfloat16*)in2, (__nv_bfloat16*)out, acc, mean,
-      rstd, R, N, relu, rows_per_block, part);
+      rstd, R, N, relu, rows_per_block, part, msc, msh);
   return DTF_CHECK_LAUNCH();
 }
 
@@ -454,7 +468,7 @@ bn_bwd_coef_kernel(const float* __restrict__ part, int nblk, const float* __rest
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x,
                     __nv_bfloat16* __restrict__ dx, const float* __restrict__ coef, long long R, int N,
-                    int rows_per_block) {
+                    int rows_per_block, const float* __restrict__ msc, const float* __restrict__ msh) {
   const int cpr = N / 8;
   const int cg0 = blockIdx.x * 256;
   const int cprg = min(256, cpr - cg0);
@@ -469,6 +483,13 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* _
     A[j] = coef[col_chunk * 8 + j];
     B[j] = coef[N + col_chunk * 8 + j];
     C[j] = coef[2 * N + col_chunk * 8 + j];
+  }
+  const bool mask_from_x = msc != nullptr;  // dz is the raw upstream gradient: apply the recomputed ReLU mask here
+  float ksc[8], ksh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    ksc[j] = mask_from_x ? msc[col_chunk * 8 + j] : 0.f;
+    ksh[j] = mask_from_x ? msh[col_chunk * 8 + j] : 0.f;
   }
   const long long r0 = (long long)blockIdx.y * rows_per_block;
   const long long r1 = min(R, r0 + rows_per_block);
@@ -491,6 +512,10 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* _
       float g[8], xv[8];
       unpack8(gb[u], g);
       unpack8(xb[u], xv);
+      if (mask_from_x) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = fmaf(xv[j], ksc[j], ksh[j]) > 0.f ? g[j] : 0.f;
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) g[j] = fmaf(A[j], g[j], fmaf(B[j], xv[j], C[j]));
       st8(dx + r * N + (long long)col_chunk * 8, pack8(g));
@@ -1053,21 +1078,30 @@ extern "C" int dtf_bn_apply(const void* x, const void* res, void* y, const float
   return DTF_CHECK_LAUNCH();
 }
 // part[blocks][2][N] = per-row-block {sum dz, sum dz*xhat}; dz (optional output) = relu ? dy*(y>0) : dy
+// relu: 0 none; 1 mask from y (y > 0); 2 mask recomputed from x with the forward's folded scale / shift
+// (mask_scale / mask_shift, no y read, dz may be NULL and is then never materialised).
 extern "C" int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* part,
-                                 const float* mean, const float* rstd, long long R, int N, int relu, void* stream) {
+                                 const float* mean, const float* rstd, const float* mask_scale,
+                                 const float* mask_shift, long long R, int N, int relu, void* stream) {
+  if (relu == 2 && (mask_scale == nullptr || mask_shift == nullptr)) return DTF_ERR_ARG;
+  if (relu == 2)
+    return launch_colreduce<4>(dy, nullptr, x, nullptr, nullptr, part, mean, rstd, R, N, 0, ST(stream), mask_scale,
+                               mask_shift);
   return launch_colreduce<3>(dy, y, x, dz, nullptr, part, mean, rstd, R, N, relu, ST(stream));
 }
 // dx from dz, x and the partial sums; dgamma_acc / dbeta_acc (optional) receive += the parameter gradients.
 extern "C" int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* part, const float* mean,
                                 const float* rstd, const float* gamma, float* coef, float* dgamma_acc,
-                                float* dbeta_acc, long long R, int N, void* stream) {
+                                float* dbeta_acc, const float* mask_scale, const float* mask_shift, long long R,
+                                int N, void* stream) {
   if (N % 8) return DTF_ERR_ALIGN;
   bn_bwd_coef_kernel<<<(N + 31) / 32, 1024, 0, ST(stream)>>>(part, dtf_colreduce_blocks(R, N), mean, rstd, gamma, coef,
                                                             dgamma_acc, dbeta_acc, N, 1.f / (float)R);
   int gx, gy, rpb;
   elementwise_geometry(R, N, &gx, &gy, &rpb);
   bn_bwd_apply_kernel<<<dim3(gx, gy), 256, 0, ST(stream)>>>((const __nv_bfloat16*)dz, (const __nv_bfloat16*)x,
-                                                            (__nv_bfloat16*)dx, coef, R, N, rpb);
+                                                            (__nv_bfloat16*)dx, coef, R, N, rpb, mask_scale,
+                                                            mask_shift);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_pool_fwd(const void* x, void* y, void* idx, int n_img, int H, int W, int C, int OH, int OW, int kh,

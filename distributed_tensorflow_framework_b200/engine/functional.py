@@ -251,21 +251,26 @@ class BatchNormFn(torch.autograd.Function):
         res2 = res.reshape(rows, -1) if res is not None else None
         gamma = gvar.master if gvar is not None else None
         beta = bvar.master if bvar is not None else None
-        y2, mean, rstd = raw.bn_train_fwd(x2, gamma, beta, run_mean, run_var, eps, momentum, res2, relu)
+        y2, mean, rstd, scale, shift = raw.bn_train_fwd(x2, gamma, beta, run_mean, run_var, eps, momentum, res2, relu)
         ctx.gvar, ctx.bvar, ctx.relu, ctx.rows, ctx.has_res = gvar, bvar, relu, rows, res is not None
-        ctx.save_for_backward(x2, y2 if relu else None, mean, rstd)
+        # without a residual the ReLU mask is a function of x alone: keep the folded coefficients instead of y
+        ctx.mask_from_x = relu and res is None
+        if ctx.mask_from_x:
+            ctx.save_for_backward(x2, None, mean, rstd, scale, shift)
+        else:
+            ctx.save_for_backward(x2, y2 if relu else None, mean, rstd, None, None)
         return y2.view(shape)
 
     @staticmethod
     def backward(ctx, dy):
-        x2, y2, mean, rstd = ctx.saved_tensors
+        x2, y2, mean, rstd, msc, msh = ctx.saved_tensors
         gvar, bvar = ctx.gvar, ctx.bvar
         shape = dy.shape
         dy2 = dy.contiguous().view(ctx.rows, -1)
         # the coefficient kernel adds d gamma / d beta straight into the gradient arena
         dx2, dz2, _, _ = raw.bn_bwd(dy2, y2, x2, mean, rstd, gvar.master if gvar is not None else None, ctx.relu,
                                     dgamma_acc=gvar.grad if gvar is not None else None,
-                                    dbeta_acc=bvar.grad if bvar is not None else None)
+                                    dbeta_acc=bvar.grad if bvar is not None else None, mask_scale=msc, mask_shift=msh)
         if gvar is not None:
             _ready(gvar)
         if bvar is not None:

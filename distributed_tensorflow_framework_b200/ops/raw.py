@@ -239,7 +239,7 @@ def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, re
               _sp())
     y = torch.empty_like(x2d)
     _lib.call("dtf_bn_apply", x2d, res, y, scale, shift, R, N, 1 if relu else 0, _sp())
-    return y, mean, rstd
+    return y, mean, rstd, scale, shift
 
 
 def bn_eval_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, res=None, relu=False):
@@ -252,22 +252,27 @@ def bn_eval_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, res=None, relu=Fa
     return y
 
 
-def bn_bwd(dy2d, y2d, x2d, mean, rstd, gamma, relu=False, dgamma_acc=None, dbeta_acc=None):
+def bn_bwd(dy2d, y2d, x2d, mean, rstd, gamma, relu=False, dgamma_acc=None, dbeta_acc=None, mask_scale=None,
+           mask_shift=None):
     """Returns (dx, dz, dgamma, dbeta); dz = masked upstream gradient (also the residual-branch gradient).
-    The parameter gradients are ADDED into dgamma_acc / dbeta_acc (pass gradient-arena views to avoid extra passes);
-    fresh zero buffers are used when they are not given."""
+    The parameter gradients are ADDED into dgamma_acc / dbeta_acc (pass gradient-arena views to avoid extra passes).
+    With relu and mask_scale / mask_shift (the forward's folded coefficients, no residual) the ReLU mask is
+    recomputed from x: y is not read and dz is not materialised (returned as None)."""
     R, N = x2d.shape
     dev = x2d.device
     if dgamma_acc is None:
         acc = torch.zeros(2, N, device=dev, dtype=torch.float32)
         dgamma_acc, dbeta_acc = acc[0], acc[1]
     part = _part(R, N, dev)
-    dz = torch.empty_like(dy2d) if relu else dy2d
-    _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if relu else None, x2d, dz if relu else None, part, mean, rstd, R, N,
-              1 if relu else 0, _sp())
+    from_x = relu and mask_scale is not None
+    mode = 2 if from_x else (1 if relu else 0)
+    dz = None if from_x else (torch.empty_like(dy2d) if relu else dy2d)
+    _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if mode == 1 else None, x2d, dz if mode == 1 else None, part, mean, rstd,
+              mask_scale if from_x else None, mask_shift if from_x else None, R, N, mode, _sp())
     dx = torch.empty_like(x2d)
     coef = torch.empty(3, N, device=dev, dtype=torch.float32)
-    _lib.call("dtf_bn_bwd_apply", dz, x2d, dx, part, mean, rstd, gamma, coef, dgamma_acc, dbeta_acc, R, N, _sp())
+    _lib.call("dtf_bn_bwd_apply", dy2d if from_x else dz, x2d, dx, part, mean, rstd, gamma, coef, dgamma_acc, dbeta_acc,
+              mask_scale if from_x else None, mask_shift if from_x else None, R, N, _sp())
     return dx, dz, dgamma_acc, dbeta_acc
 
 

@@ -111,12 +111,14 @@ int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma,
                 float* shift, int N, float eps, void* stream);
 int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift, long long R, int N,
                  int relu, void* stream);
+/* relu: 0 none, 1 mask from y, 2 mask recomputed from x with the forward's folded scale/shift (no y read, no dz). */
 int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* part, const float* mean,
-                      const float* rstd, long long R, int N, int relu, void* stream);
+                      const float* rstd, const float* mask_scale, const float* mask_shift, long long R, int N,
+                      int relu, void* stream);
 /* coef: [3][N] float workspace. dgamma_acc / dbeta_acc (may be NULL) receive += sum dz*xhat / sum dz. */
 int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* part, const float* mean, const float* rstd,
-                     const float* gamma, float* coef, float* dgamma_acc, float* dbeta_acc, long long R, int N,
-                     void* stream);
+                     const float* gamma, float* coef, float* dgamma_acc, float* dbeta_acc, const float* mask_scale,
+                     const float* mask_shift, long long R, int N, void* stream);
 
 /* pool (distribute_tools.py:160-165): max / avg, TF SAME semantics via explicit top/left padding. Max pooling
  * records the in-window position of the first maximum (one byte per output element, `idx`) for the backward. */

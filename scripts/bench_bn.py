@@ -18,8 +18,8 @@ for (R, N) in [(200704, 256), (200704, 64), (50176, 512), (12544, 1024), (3136, 
     sp = _lib.stream_ptr
     t1 = timeit(lambda: _lib.call("dtf_bn_stats", x, stats, R, N, sp()))
     t2 = timeit(lambda: _lib.call("dtf_bn_apply", x, res, out, scale, shift, R, N, 1, sp()))
-    t3 = timeit(lambda: _lib.call("dtf_bn_bwd_reduce", dy, y, x, out, stats, mean, rstd, R, N, 1, sp()))
-    t4 = timeit(lambda: _lib.call("dtf_bn_bwd_apply", dy, x, out, stats, mean, rstd, None, coef, None, None, R, N, sp()))
+    t3 = timeit(lambda: _lib.call("dtf_bn_bwd_reduce", dy, None, x, None, stats, mean, rstd, scale, shift, R, N, 2, sp()))
+    t4 = timeit(lambda: _lib.call("dtf_bn_bwd_apply", dy, x, out, stats, mean, rstd, None, coef, None, None, scale, shift, R, N, sp()))
     t5 = timeit(lambda: out.copy_(x))
     print("R=%7d N=%5d (%6.1f MB)  stats %.3f ms %5.0f GB/s | apply %.3f %5.0f | bwd_reduce %.3f %5.0f | bwd_apply %.3f %5.0f | torch copy %.3f %5.0f" % (
         R, N, nb, t1, nb / t1, t2, 3 * nb / t2, t3, 4 * nb / t3, t4, 3 * nb / t4, t5, 2 * nb / t5))

@@ -88,7 +88,7 @@ def test_lrn(raw):
     close(raw.lrn_bwd(x, dy, r, bias, alpha, beta), xf.grad.permute(0, 2, 3, 1), 3e-2)
 
 
-@pytest.mark.parametrize("R,N,relu,with_res", [(2048, 64, True, True), (512, 256, False, False),
+@pytest.mark.parametrize("R,N,relu,with_res", [(2048, 64, True, True), (1024, 128, True, False), (512, 256, False, False),
                                                (64, 8 * 8 * 16, False, False)])
 def test_batch_norm(raw, R, N, relu, with_res):
     x = rnd(R, N) * 2 + 0.5
@@ -105,7 +105,7 @@ def test_batch_norm(raw, R, N, relu, with_res):
         ref = ref + resf
     if relu:
         ref = torch.relu(ref)
-    y, mean, rstd = raw.bn_train_fwd(x, gamma, beta, rm, rv, 1e-3, 0.1, res, relu)
+    y, mean, rstd, scale, shift = raw.bn_train_fwd(x, gamma, beta, rm, rv, 1e-3, 0.1, res, relu)
     close(y, ref)
     close(rm, rm_ref, 1e-2)
     close(rv, rv_ref, 1e-2)
@@ -117,6 +117,11 @@ def test_batch_norm(raw, R, N, relu, with_res):
     close(dbeta, b2.grad, 2e-2)
     if with_res:
         close(dz, resf.grad)
+    if relu and not with_res:  # mask recomputed from x: same result without reading y / writing dz
+        dx2, dz2, dg2, db2 = raw.bn_bwd(dy, None, x, mean, rstd, gamma, relu, mask_scale=scale, mask_shift=shift)
+        assert dz2 is None
+        close(dx2, xf.grad, 3e-2)
+        close(dg2, g2.grad, 2e-2)
     close(raw.bn_eval_fwd(x, gamma, beta, rm, rv, 1e-3),
           F.batch_norm(x.float(), rm, rv, gamma, beta, False, 0.0, 1e-3))
 
