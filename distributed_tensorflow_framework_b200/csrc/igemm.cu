@@ -136,6 +136,66 @@ __device__ __forceinline__ void igemm_epilogue(const IgemmParams& p, uint32_t tm
   }
 }
 
+
+// Coalescing epilogue for bf16 outputs: a warp's 32 rows x COLS columns go through a shared-memory staging tile
+// (16-byte chunks XOR-swizzled by the row) so that every global store instruction writes complete 32-byte sectors of
+// few rows (COLS = 64: four full 128-byte lines per instruction; COLS = 32: eight 64-byte row segments) instead of
+// 32 scattered 16-byte pieces. `stage` is this warp's private 32 * COLS * 2 bytes.
+template <int BN, int COLS>
+__device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint32_t tmem_base, int tile_m,
+                                                      int tile_n, int warp, uint8_t* stage) {
+  constexpr int ROWB = COLS * 2;        // bytes per staged row
+  constexpr int CPR = ROWB / 16;        // 16-byte chunks per row (8 or 4)
+  constexpr int RPI = 32 / CPR;         // rows written per store instruction
+  const int lane = threadIdx.x & 31;
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
+  const int row0 = tile_m * BLOCK_M + warp * 32;
+  __nv_bfloat16* outp = reinterpret_cast<__nv_bfloat16*>(p.out);
+#pragma unroll 1
+  for (int cg = 0; cg < BN / COLS; ++cg) {
+    const int n0 = tile_n * BN + cg * COLS;
+#pragma unroll
+    for (int h = 0; h < COLS / 32; ++h) {
+      uint32_t v[32];
+      tmem_ld32(lane_addr + cg * COLS + h * 32, v);
+      tmem_ld_wait();
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (n0 + h * 32 + j < p.N) f[j] += __ldg(p.bias + n0 + h * 32 + j);
+      }
+      if (p.relu) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {  // four 16-byte chunks of this 32-column half
+        uint4 q;
+        q.x = pack_bf16x2(f[c * 8 + 0], f[c * 8 + 1]);
+        q.y = pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]);
+        q.z = pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]);
+        q.w = pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]);
+        const int chunk = h * 4 + c;
+        *reinterpret_cast<uint4*>(stage + lane * ROWB + ((chunk ^ (lane & (CPR - 1))) << 4)) = q;
+      }
+    }
+    __syncwarp();
+    const int chunk = lane & (CPR - 1);
+#pragma unroll
+    for (int i = 0; i < 32 / RPI; ++i) {
+      const int r = i * RPI + lane / CPR;
+      const uint4 q = *reinterpret_cast<const uint4*>(stage + r * ROWB + ((chunk ^ (r & (CPR - 1))) << 4));
+      const int m = row0 + r;
+      const int n = n0 + chunk * 8;
+      if (m < p.M && n + 8 <= p.N) *reinterpret_cast<uint4*>(outp + (size_t)m * p.ldc + n) = q;
+    }
+    __syncwarp();
+  }
+}
+
 // K-AG-GEMM support: the B operand (weights) is sharded over the ranks of a parameter-server group and is NOT
 // gathered beforehand: the TMA producer picks, per k-block (mode 1: B sharded by rows / K) or per n-tile (mode 2:
 // B sharded by columns / N), the tensor map that points into the OWNER's symmetric heap, so weight tiles cross
@@ -459,8 +519,13 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
   uint64_t* acc_full = empty_bar + STAGES;   // [2]
   uint64_t* acc_empty = acc_full + 2;        // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  constexpr int kStageCols = (BN >= 256) ? 64 : 32;  // wide tiles run one CTA per SM and can afford 4 KB per warp
+  uint8_t* stage_base = smem + L::BAR_OFFSET + 256;  // 4 warps x (32 rows x kStageCols x 2 B) epilogue staging
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr bool kAMn = (AMODE == A_TMA_MN);
+  // bf16 output with 16-byte aligned rows and whole 8-column groups: use the coalescing epilogue
+  const bool staged = !p.atomic && !p.out_fp32 && (p.ldc % 8 == 0) && (p.N % 8 == 0) &&
+                      ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
   const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
   const int total_tiles = tiles_m * tiles_n * splits;
 
@@ -555,7 +620,10 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
       const int buf = lt & 1;
       mbar_wait(&acc_full[buf], (lt >> 1) & 1);
       tc_fence_after();
-      igemm_epilogue<BN>(p, tmem_base + buf * BN, tile_m, tile_n, warp);
+      if (staged)
+        igemm_epilogue_staged<BN, kStageCols>(p, tmem_base + buf * BN, tile_m, tile_n, warp,
+                                              stage_base + warp * (32 * kStageCols * 2));
+      else igemm_epilogue<BN>(p, tmem_base + buf * BN, tile_m, tile_n, warp);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
@@ -573,20 +641,21 @@ template <int BN, int STAGES, int AMODE>
 static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
                              cudaStream_t stream) {
   using L = SmemLayout<BN, STAGES>;
+  constexpr int kStage = 4 * 32 * ((BN >= 256) ? 64 : 32) * 2;  // epilogue staging: 16 KB (wide tiles) or 8 KB
   static bool attr_set[64] = {};
   auto kern = igemm_persistent_kernel<BN, STAGES, AMODE>;
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) != cudaSuccess)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL + kStage) != cudaSuccess)
       return DTF_ERR_CUDA;
     attr_set[dev & 63] = true;
   }
   const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M;
   const int total = tiles_n * tiles_m * splits;
-  const int per_sm = (L::TOTAL <= 110 * 1024) ? 2 : 1;
+  const int per_sm = (L::TOTAL + kStage <= 112 * 1024) ? 2 : 1;
   const int grid = total < 148 * per_sm ? total : 148 * per_sm;
-  kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(ta, tb, p, tiles_m, tiles_n, splits);
+  kern<<<grid, NUM_THREADS, L::TOTAL + kStage, stream>>>(ta, tb, p, tiles_m, tiles_n, splits);
   return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
