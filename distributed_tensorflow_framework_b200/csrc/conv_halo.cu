@@ -126,7 +126,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
             kw = p.KW - 1 - kw;
           }
           const uint32_t a_tap = a_base + as * p.a_stage_bytes + (uint32_t)(kh * p.Wp + kw) * 128u;
-          const uint32_t boff = p.base_off_mode ? ((a_tap >> 7) & 7u) : 0u;
+          const uint32_t boff = (p.base_off_mode & 1) ? ((a_tap >> 7) & 7u) : 0u;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
             const uint64_t adesc = make_smem_desc_off(a_tap + k * 32, 16, 1024, boff);
@@ -199,6 +199,242 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
 }
 
 
+// Persistent variant: one CTA per SM walks a strided list of (pixel tile, channel tile) items. The accumulator is
+// double-buffered in TMEM (2 x BN columns) so the epilogue of item i overlaps the MMAs of item i+1, the halo tile of
+// the next item is prefetched into the second A stage while the current one is consumed, and -- when all KH*KW*C/64
+// weight tiles of the layer fit in shared memory next to the halo stages (64- and 128-channel layers) -- the weights
+// are loaded ONCE per CTA and stay resident, so the steady state streams only activations. Otherwise the weight ring
+// keeps running across items. The epilogue goes through a swizzled per-warp staging tile so that every global store
+// instruction writes whole 64-byte row segments.
+constexpr int MAX_B_STAGES = 40;
+constexpr int PERSIST_STAGE_BYTES = 4 * 32 * 64;  // 4 epilogue warps x 32 rows x 32 bf16 columns
+
+struct PersistParams {
+  int tiles_n;      // channel tiles
+  int total_items;  // pixel tiles x channel tiles
+  int nb;           // weight stages in shared memory
+  int resident;     // 1: nb == KH*KW*C/64 and every weight tile is loaded once
+};
+
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_halo_persistent_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w,
+                            const Params p, const PersistParams pp) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int B_BYTES = BN * 64 * 2;
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t a_base = smem_base;
+  const uint32_t b_base = smem_base + A_STAGES * p.a_stage_bytes;
+  const int bar_off = A_STAGES * p.a_stage_bytes + pp.nb * B_BYTES;
+  uint64_t* a_full = reinterpret_cast<uint64_t*>(smem + bar_off);
+  uint64_t* a_empty = a_full + A_STAGES;
+  uint64_t* acc_full = a_empty + A_STAGES;  // [2]
+  uint64_t* acc_empty = acc_full + 2;       // [2]
+  uint64_t* b_full = acc_empty + 2;         // [MAX_B_STAGES]
+  uint64_t* b_empty = b_full + MAX_B_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(b_empty + MAX_B_STAGES);
+  uint32_t* tap_off = reinterpret_cast<uint32_t*>(smem + bar_off + 768);  // [KH*KW] <= 49 entries
+  uint8_t* stage_base = smem + bar_off + 1024;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntaps = p.KH * p.KW;
+  const int ncblk = p.C >> 6;
+  const int nb = pp.nb;
+  const bool resident = pp.resident != 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < A_STAGES; ++s) {
+      mbar_init(&a_full[s], 1);
+      mbar_init(&a_empty[s], 1);
+    }
+    for (int s = 0; s < nb; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], 4);  // one arrival per epilogue warp
+    }
+    mbar_fence_init();
+  }
+  if (warp == 4) tmem_alloc<2 * BN>(tmem_slot);
+  if (warp == 5 && lane == 0) {
+    tma_prefetch_desc(&tma_x);
+    tma_prefetch_desc(&tma_w);
+  }
+  if (threadIdx.x < ntaps) {  // byte shift of every tap's view of the halo tile (mirrored for the data gradient)
+    int kh = threadIdx.x / p.KW, kw = threadIdx.x - kh * p.KW;
+    if (p.mirror) {
+      kh = p.KH - 1 - kh;
+      kw = p.KW - 1 - kw;
+    }
+    tap_off[threadIdx.x] = (uint32_t)(kh * p.Wp + kw) * 128u;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  auto decode = [&](int item, int& tile_n, int& img, int& y0, int& x0) {
+    tile_n = item % pp.tiles_n;
+    const int mt = item / pp.tiles_n;
+    img = mt / p.tiles_per_img;
+    const int tin = mt - img * p.tiles_per_img;
+    y0 = (tin / p.tiles_x) * p.R;
+    x0 = (tin % p.tiles_x) * p.Wt;
+  };
+
+  // The issuing threads run lean loops: ring indices and phases are carried as counters (no div / mod), tap shifts
+  // come from a table, and descriptors are a precomputed constant plus the 16-byte-granular address.
+  if (warp == 5) {
+    if (lane == 0) {
+      int as = 0, bs = 0;
+      uint32_t a_par = 1, b_par = 1;  // "empty" barriers: the first pass over a ring must not block
+      bool first = true;
+      for (int item = blockIdx.x; item < pp.total_items; item += gridDim.x) {
+        int tile_n, img, y0, x0;
+        decode(item, tile_n, img, y0, x0);
+        for (int cb = 0; cb < ncblk; ++cb) {
+          mbar_wait(&a_empty[as], a_par);
+          mbar_arrive_expect_tx(&a_full[as], p.a_tx_bytes);
+          tma_load_4d(a_base + as * p.a_stage_bytes, &tma_x, &a_full[as], cb * 64, x0 + p.org_x, y0 + p.org_y, img);
+          if (++as == A_STAGES) {
+            as = 0;
+            a_par ^= 1;
+          }
+          if (resident && !first) continue;
+          int krow = cb * 64;
+          for (int t = 0; t < ntaps; ++t, krow += p.C) {
+            if (!resident) mbar_wait(&b_empty[bs], b_par);
+            mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_base + bs * B_BYTES + j * 8192, &tma_w, &b_full[bs], tile_n * BN + j * 64, krow);
+            if (++bs == nb) {
+              bs = 0;
+              b_par ^= 1;
+            }
+          }
+        }
+        first = false;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 4) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, /*a_mn=*/false, /*b_mn=*/true);
+      const uint64_t adesc0 = make_smem_desc(0, 16, 1024);
+      const uint64_t bdesc0 = make_smem_desc(0, 8192, 1024);
+      int as = 0, bs = 0, buf = 0;
+      uint32_t a_par = 0, b_par = 0, acc_par = 1;
+      for (int item = blockIdx.x; item < pp.total_items; item += gridDim.x) {
+        mbar_wait(&acc_empty[buf], acc_par);  // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        uint32_t accum = 0;
+        for (int cb = 0; cb < ncblk; ++cb) {
+          mbar_wait(&a_full[as], a_par);
+          const uint32_t a_stage = a_base + as * p.a_stage_bytes;
+          for (int t = 0; t < ntaps; ++t) {
+            mbar_wait(&b_full[bs], b_par);  // resident: phase 0 completes once, b_par stays 0
+            tc_fence_after();
+            const uint64_t adesc = adesc0 + ((a_stage + tap_off[t]) >> 4);
+            const uint64_t bdesc = bdesc0 + ((b_base + bs * B_BYTES) >> 4);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              umma_bf16(d_tmem, adesc + 2 * k, bdesc + 128 * k, idesc, accum);
+              accum = 1;
+            }
+            if (!resident) umma_commit(&b_empty[bs]);
+            if (++bs == nb) {
+              bs = 0;
+              if (!resident) b_par ^= 1;
+            }
+          }
+          umma_commit(&a_empty[as]);
+          if (++as == A_STAGES) {
+            as = 0;
+            a_par ^= 1;
+          }
+        }
+        umma_commit(&acc_full[buf]);
+        if ((buf ^= 1) == 0) acc_par ^= 1;
+      }
+    }
+    __syncwarp();
+  } else {
+    // epilogue: GEMM row m -> (y, x) in the padded-linear space of the tile; TMEM -> registers -> bias / ReLU ->
+    // bf16 -> per-warp staging tile -> 64-byte row segments (8 rows per store instruction)
+    uint8_t* stage = stage_base + warp * (32 * 64);
+    const int m = threadIdx.x;
+    const int ry = m / p.Wp;
+    const int xx = m - ry * p.Wp;
+    const uint32_t lane_addr = ((uint32_t)(warp * 32) << 16);
+    int lt = 0;
+    for (int item = blockIdx.x; item < pp.total_items; item += gridDim.x, ++lt) {
+      int tile_n, img, y0, x0;
+      decode(item, tile_n, img, y0, x0);
+      const int buf = lt & 1;
+      const int x = x0 + xx, y = y0 + ry;
+      const bool valid = (ry < p.R) && (xx < p.Wt) && (x < p.W) && (y < p.H);
+      const int pix = valid ? (int)(((long long)img * p.H + y) * p.W + x) : -1;
+      mbar_wait(&acc_full[buf], (lt >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int cc = 0; cc < BN / 32; ++cc) {
+        const int n0 = tile_n * BN + cc * 32;
+        if (n0 >= p.n_out) break;  // uniform across the CTA
+        uint32_t v[32];
+        tmem_ld32(tmem_base + buf * BN + lane_addr + cc * 32, v);
+        tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (n0 + j < p.n_out) f[j] += __ldg(p.bias + n0 + j);
+        }
+        if (p.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint4 q;
+          q.x = pack_bf16x2(f[c * 8 + 0], f[c * 8 + 1]);
+          q.y = pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]);
+          q.z = pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]);
+          q.w = pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]);
+          *reinterpret_cast<uint4*>(stage + lane * 64 + ((c ^ (lane & 3)) << 4)) = q;
+        }
+        __syncwarp();
+        const int chunk = lane & 3;
+        const int n = n0 + chunk * 8;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = i * 8 + (lane >> 2);
+          const int pr = __shfl_sync(0xffffffffu, pix, r);
+          const uint4 q = *reinterpret_cast<const uint4*>(stage + r * 64 + ((chunk ^ (r & 3)) << 4));
+          if (pr >= 0 && n + 8 <= p.n_out)
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)pr * p.n_out + n) = q;
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<2 * BN>(tmem_base);
+  }
+}
+
 // --------------------------------------------------------------------------------------------------------------
 // Filter gradient on halo tiles: dW[tap, ci, co] = sum over pixels p of x[p + shift(tap), ci] * dy[p, co].
 // A CTA owns one (64 ci) x (64 co) block of ALL taps and walks a range of image tiles. Per tile one TMA load brings
@@ -232,6 +468,8 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_consta
   uint64_t* empty = full + WG_STAGES;
   uint64_t* tmem_full = empty + WG_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint64_t* pair_desc = reinterpret_cast<uint64_t*>(smem + data_bytes + 128);  // [8]
+  uint32_t* pair_off = reinterpret_cast<uint32_t*>(smem + data_bytes + 192);   // [8]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int co0 = blockIdx.x * 64, ci0 = blockIdx.y * 64;
@@ -257,6 +495,14 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_consta
     tma_prefetch_desc(&tma_x);
     tma_prefetch_desc(&tma_dy);
   }
+  if (threadIdx.x < npairs) {  // tap pair j: shift of its first tap and the descriptor with LBO = shift difference
+    const int t0 = 2 * threadIdx.x, t1 = min(t0 + 1, ntaps - 1);
+    const int sh0 = (t0 / p.KW) * p.Wp + (t0 % p.KW);
+    const int sh1 = (t1 / p.KW) * p.Wp + (t1 % p.KW);
+    pair_off[threadIdx.x] = (uint32_t)sh0 * 128u;
+    // odd tail: the second half is a dummy view of the next row
+    pair_desc[threadIdx.x] = make_smem_desc(0, (t1 == t0) ? 128u : (uint32_t)(sh1 - sh0) * 128u, 1024);
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -279,31 +525,32 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_consta
     }
     __syncwarp();
   } else if (warp == 4) {
-    constexpr uint32_t idesc = make_idesc_bf16(128, 64, /*a_mn=*/true, /*b_mn=*/true);
-    int it = 0;
-    for (int t = t_begin; t < t_end; ++t, ++it) {
-      const int s = it % WG_STAGES;
-      mbar_wait(&full[s], (it / WG_STAGES) & 1);
-      tc_fence_after();
-      if (lane == 0) {
+    if (lane == 0) {  // one thread runs the whole issue loop; per-pair descriptor parts come from a table
+      constexpr uint32_t idesc = make_idesc_bf16(128, 64, /*a_mn=*/true, /*b_mn=*/true);
+      const uint64_t bdesc0 = make_smem_desc(0, 8192, 1024);
+      int s = 0;
+      uint32_t ph = 0, accum0 = 0;
+      for (int t = t_begin; t < t_end; ++t) {
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_stage = a_base + s * p.a_stage_bytes;
+        const uint64_t bdesc = bdesc0 + ((b_base + s * WG_B_BYTES) >> 4);
         for (int j = 0; j < npairs; ++j) {
-          const int t0 = 2 * j, t1 = min(2 * j + 1, ntaps - 1);
-          const int sh0 = (t0 / p.KW) * p.Wp + (t0 % p.KW);
-          const int sh1 = (t1 / p.KW) * p.Wp + (t1 % p.KW);
-          const uint32_t a_tap = a_base + s * p.a_stage_bytes + (uint32_t)sh0 * 128u;
-          const uint32_t lbo = (t1 == t0) ? 128u : (uint32_t)(sh1 - sh0) * 128u;  // odd tail: second half is a dummy
+          const uint64_t adesc = pair_desc[j] + ((a_stage + pair_off[j]) >> 4);
+          const uint32_t d_tmem = tmem_base + j * 64;
+          umma_bf16(d_tmem, adesc, bdesc, idesc, accum0);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const uint64_t adesc = make_smem_desc(a_tap + k * 2048, lbo, 1024);
-            const uint64_t bdesc = make_smem_desc(b_base + s * WG_B_BYTES + k * 2048, 8192, 1024);
-            umma_bf16(tmem_base + j * 64, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
-          }
+          for (int k = 1; k < 8; ++k) umma_bf16(d_tmem, adesc + k * 128, bdesc + k * 128, idesc, 1u);
         }
+        accum0 = 1;
         umma_commit(&empty[s]);
+        if (++s == WG_STAGES) {
+          s = 0;
+          ph ^= 1;
+        }
       }
-      __syncwarp();
+      umma_commit(tmem_full);
     }
-    if (lane == 0) umma_commit(tmem_full);
     __syncwarp();
   } else {
     mbar_wait(tmem_full, 0);
@@ -376,6 +623,46 @@ static int launch(const CUtensorMap& tx, const CUtensorMap& tw, const Params& p,
   return DTF_CHECK_LAUNCH();
 }
 
+
+static int g_halo_persistent = 1;
+
+// Persistent launch: returns DTF_ERR_UNSUPPORTED when the shared-memory plan does not fit (caller falls back).
+template <int BN>
+static int launch_persistent(const CUtensorMap& tx, const CUtensorMap& tw, const Params& p, cudaStream_t stream) {
+  constexpr int B_BYTES = BN * 128;
+  const int fixed = 1024 /*alignment*/ + A_STAGES * p.a_stage_bytes + 1024 /*barriers*/ + PERSIST_STAGE_BYTES;
+  const int avail = 227 * 1024 - fixed;
+  const int total_b = p.KH * p.KW * (p.C >> 6);
+  PersistParams pp{};
+  pp.tiles_n = (p.n_out + BN - 1) / BN;
+  const long long items = (long long)p.n_img * p.tiles_per_img * pp.tiles_n;
+  if (items > 0x7fffffffLL || (long long)p.n_img * p.H * p.W > 0x7fffffffLL) return DTF_ERR_UNSUPPORTED;
+  pp.total_items = (int)items;
+  if (pp.tiles_n == 1 && total_b <= MAX_B_STAGES && total_b * B_BYTES <= avail) {
+    pp.resident = 1;
+    pp.nb = total_b;
+  } else {
+    pp.resident = 0;
+    pp.nb = avail / B_BYTES;
+    if (pp.nb > 8) pp.nb = 8;
+    if (pp.nb < 2) return DTF_ERR_UNSUPPORTED;
+  }
+  const int smem = fixed + pp.nb * B_BYTES;
+  auto kern = conv_halo_persistent_kernel<BN>;
+  static int attr[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr[dev & 63] < smem) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return DTF_ERR_CUDA;
+    attr[dev & 63] = smem;
+  }
+  static int sms[64] = {};
+  if (sms[dev & 63] == 0) cudaDeviceGetAttribute(&sms[dev & 63], cudaDevAttrMultiProcessorCount, dev);
+  const int grid = pp.total_items < sms[dev & 63] ? pp.total_items : sms[dev & 63];
+  kern<<<grid, NUM_THREADS, smem, stream>>>(tx, tw, p, pp);
+  return DTF_CHECK_LAUNCH();
+}
+
 }  // namespace halo
 }  // namespace dtf
 
@@ -433,7 +720,7 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
   p.a_tx_bytes = halo_rows * p.Wp * 128;
   const int span = (128 + (KH - 1) * p.Wp + (KW - 1)) * 128;
   p.a_stage_bytes = ((span > p.a_tx_bytes ? span : p.a_tx_bytes) + 1023) & ~1023;
-  p.base_off_mode = (flags >> 8) & 1;
+  p.base_off_mode = (flags >> 8) & 0xff;
   p.out = out; p.bias = bias; p.relu = flags & 1;
   CUtensorMap tx, tw;
   {
@@ -457,8 +744,19 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
       return DTF_ERR_TENSORMAP;
   }
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (g_halo_persistent) {
+    const int rc = (n_out <= 64) ? launch_persistent<64>(tx, tw, p, stream) : launch_persistent<128>(tx, tw, p, stream);
+    if (rc != DTF_ERR_UNSUPPORTED) return rc;
+  }
   if (n_out <= 64) return launch<64, 4>(tx, tw, p, stream);
   return launch<128, 4>(tx, tw, p, stream);
+}
+
+// 1 (default): the persistent halo kernel; 0: one tile per CTA. Returns the previous setting.
+extern "C" int dtf_set_persistent_halo(int on) {
+  const int prev = dtf::halo::g_halo_persistent;
+  dtf::halo::g_halo_persistent = on ? 1 : 0;
+  return prev;
 }
 
 // 1 if dtf_conv_wgrad_halo_bf16 supports the geometry (stride 1, C % 64 == 0, n_out % 64 == 0, <= 16 taps).

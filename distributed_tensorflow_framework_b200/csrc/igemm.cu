@@ -441,31 +441,33 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
     tc_fence_after();
     igemm_epilogue<BN>(p, tmem_base, tile_m, tile_n, warp);
   } else if (warp == 4) {
-    // ===================================================== MMA issuer
-    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, /*b_mn=*/true);
-    int it = 0;
-    for (int kb = kb0; kb < kb1; ++kb, ++it) {
-      const int s = it % STAGES;
-      const uint32_t ph = (it / STAGES) & 1;
-      mbar_wait(&full_bar[s], ph);
-      tc_fence_after();
-      if (lane == 0) {
+    // ===================================================== MMA issuer (one thread runs the whole loop)
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, /*b_mn=*/true);
+      const uint64_t adesc0 = kAMn ? make_smem_desc(0, /*lbo=*/8192, /*sbo=*/1024) : make_smem_desc(0, 16, 1024);
+      const uint64_t bdesc0 = make_smem_desc(0, /*lbo=*/8192, /*sbo=*/1024);
+      constexpr uint32_t kAStep = kAMn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      constexpr uint32_t kBStep = (UMMA_K * 128) >> 4;
+      int s = 0;
+      uint32_t ph = 0, accum = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint64_t adesc = adesc0 + (a_stage(s) >> 4);
+        const uint64_t bdesc = bdesc0 + (b_stage(s) >> 4);
 #pragma unroll
         for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-          uint64_t adesc, bdesc;
-          if constexpr (kAMn) {
-            adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 128), /*lbo=*/8192, /*sbo=*/1024);
-          } else {
-            adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 2), /*lbo=*/16, /*sbo=*/1024);
-          }
-          bdesc = make_smem_desc(b_stage(s) + k * (UMMA_K * 128), /*lbo=*/8192, /*sbo=*/1024);
-          umma_bf16(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          umma_bf16(tmem_base, adesc + k * kAStep, bdesc + k * kBStep, idesc, accum);
+          accum = 1;
         }
         umma_commit(&empty_bar[s]);
+        if (++s == STAGES) {
+          s = 0;
+          ph ^= 1;
+        }
       }
-      __syncwarp();
+      umma_commit(tmem_full_bar);
     }
-    if (lane == 0) umma_commit(tmem_full_bar);
     __syncwarp();
   } else {
     // ===================================================== TMA producer (B always; A in dense modes)
@@ -585,33 +587,42 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
     }
     __syncwarp();
   } else if (warp == 4) {
-    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, true);
-    int it = 0, lt = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
-      int tile_m, tile_n, kb0, kb1;
-      decode(t, tile_m, tile_n, kb0, kb1);
-      const int buf = lt & 1;
-      mbar_wait(&acc_empty[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
-      tc_fence_after();
-      for (int kb = kb0; kb < kb1; ++kb, ++it) {
-        const int s = it % STAGES;
-        mbar_wait(&full_bar[s], (it / STAGES) & 1);
+    if (lane == 0) {  // one thread runs the whole issue loop; ring indices and phases are counters
+      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, true);
+      const uint64_t adesc0 = kAMn ? make_smem_desc(0, 8192, 1024) : make_smem_desc(0, 16, 1024);
+      const uint64_t bdesc0 = make_smem_desc(0, 8192, 1024);
+      constexpr uint32_t kAStep = kAMn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+      constexpr uint32_t kBStep = (UMMA_K * 128) >> 4;
+      int s = 0, buf = 0;
+      uint32_t ph = 0, acc_par = 1;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        int tile_m, tile_n, kb0, kb1;
+        decode(t, tile_m, tile_n, kb0, kb1);
+        mbar_wait(&acc_empty[buf], acc_par);  // epilogue has drained this accumulator
         tc_fence_after();
-        if (lane == 0) {
+        const uint32_t d_tmem = tmem_base + buf * BN;
+        uint32_t accum = 0;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint64_t adesc = adesc0 + (a_stage(s) >> 4);
+          const uint64_t bdesc = bdesc0 + (b_stage(s) >> 4);
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            uint64_t adesc;
-            if constexpr (kAMn) adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 128), 8192, 1024);
-            else adesc = make_smem_desc(a_stage(s) + k * (UMMA_K * 2), 16, 1024);
-            const uint64_t bdesc = make_smem_desc(b_stage(s) + k * (UMMA_K * 128), 8192, 1024);
-            umma_bf16(tmem_base + buf * BN, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_bf16(d_tmem, adesc + k * kAStep, bdesc + k * kBStep, idesc, accum);
+            accum = 1;
           }
           umma_commit(&empty_bar[s]);
-          if (kb == kb1 - 1) umma_commit(&acc_full[buf]);
+          if (++s == STAGES) {
+            s = 0;
+            ph ^= 1;
+          }
         }
-        __syncwarp();
+        umma_commit(&acc_full[buf]);
+        if ((buf ^= 1) == 0) acc_par ^= 1;
       }
     }
+    __syncwarp();
   } else {
     int lt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {

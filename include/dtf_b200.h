@@ -38,6 +38,7 @@ int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int 
  * buffered in TMEM so the epilogue overlaps the next tile). bit0 of `on`: persistent kernel (0 = one tile per CTA);
  * bit1: allow 128x256 tiles for N >= 256. Default 3. Returns the previous setting. */
 int dtf_set_persistent_gemm(int on);
+int dtf_set_persistent_halo(int on);
 
 /* K-AG-GEMM: the all-gather of parameter-server weights fused into the consuming GEMM. B is sharded over the heaps
  * of `world` ranks (peer_b[r] = rank r's mapping of the matrix, `bounds` = owned arena ranges, b_arena_off = arena
