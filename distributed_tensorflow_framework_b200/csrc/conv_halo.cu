@@ -436,6 +436,273 @@ conv_halo_persistent_kernel(const __grid_constant__ CUtensorMap tma_x, const __g
 }
 
 // --------------------------------------------------------------------------------------------------------------
+// Pixels-as-N variant (the default). A single thread issues every tcgen05.mma of a CTA, and that thread needs a
+// fixed number of scalar instructions per MMA; with 64 or 128 output channels as the N dimension an MMA is only
+// 32-64 tensor-core cycles long and the issue loop, not the tensor core, sets the pace (ncu: tensor pipe 15-19 %).
+// Here the roles are swapped: D^T[co, pixel] = W^T[co, k] * X^T[k, pixel], so A is the weight tile (MN-major,
+// M = 128 output channels) and B is the halo tile (K-major, N = 256 padded-linear pixels); every MMA is the
+// largest shape (128x256x16, 128 cycles), the per-FLOP instruction count drops 2-4x, and weights stream at half the
+// rate. A tap is again just a shifted start address, now of the B descriptor. Whole small images are packed G per
+// tile (4-D TMA box over the image index) so 14x14 and 7x7 layers fill the 256-pixel N. The accumulator
+// [co lanes x pixel columns] is double-buffered in TMEM (2 x 256 columns); the epilogue transposes it through a
+// per-warp staging tile into 64-byte NHWC row segments.
+constexpr int PN_PIX = 256;
+constexpr int PN_STAGE_BYTES = 4 * 32 * 64;  // per warp: 32 pixels x 32 channels bf16
+constexpr int PN_TAB_BYTES = 4 * PN_PIX * 4; // per warp: output pixel index (or -1) of every GEMM column
+
+struct PnParams {
+  int tiles_co;     // output-channel tiles of MW
+  int total_items;  // pixel tiles x channel tiles
+  int nb;           // weight stages
+  int resident;     // all weight tiles stay in shared memory
+  int G;            // images per tile (whole-image tiles only), else 1
+  int img_rows;     // padded-linear rows per packed image: (R+KH-1)*Wp
+  int groups;       // pixel tiles: n_img*tiles_per_img (G == 1) or ceil(n_img / G)
+};
+
+template <int MW>  // output channels per item: 64 (single 64-channel weight box) or 128
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w,
+                    const Params p, const PnParams pp) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int W_BYTES = MW * 64 * 2;
+  const uint32_t smem_base = smem_u32(smem);
+  const uint32_t x_base = smem_base;
+  const uint32_t w_base = smem_base + A_STAGES * p.a_stage_bytes;
+  const int bar_off = A_STAGES * p.a_stage_bytes + pp.nb * W_BYTES;
+  uint64_t* x_full = reinterpret_cast<uint64_t*>(smem + bar_off);
+  uint64_t* x_empty = x_full + A_STAGES;
+  uint64_t* acc_full = x_empty + A_STAGES;  // [2]
+  uint64_t* acc_empty = acc_full + 2;       // [2]
+  uint64_t* w_full = acc_empty + 2;         // [MAX_B_STAGES]
+  uint64_t* w_empty = w_full + MAX_B_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_empty + MAX_B_STAGES);
+  uint32_t* tap_off = reinterpret_cast<uint32_t*>(smem + bar_off + 768);
+  uint8_t* stage_base = smem + bar_off + 1024;
+  int* tab_base = reinterpret_cast<int*>(smem + bar_off + 1024 + PN_STAGE_BYTES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int ntaps = p.KH * p.KW;
+  const int ncblk = p.C >> 6;
+  const int nb = pp.nb;
+  const bool resident = pp.resident != 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < A_STAGES; ++s) {
+      mbar_init(&x_full[s], 1);
+      mbar_init(&x_empty[s], 1);
+    }
+    for (int s = 0; s < nb; ++s) {
+      mbar_init(&w_full[s], 1);
+      mbar_init(&w_empty[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], 4);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 4) tmem_alloc<512>(tmem_slot);
+  if (warp == 5 && lane == 0) {
+    tma_prefetch_desc(&tma_x);
+    tma_prefetch_desc(&tma_w);
+  }
+  if (threadIdx.x < ntaps) {
+    int kh = threadIdx.x / p.KW, kw = threadIdx.x - kh * p.KW;
+    if (p.mirror) {
+      kh = p.KH - 1 - kh;
+      kw = p.KW - 1 - kw;
+    }
+    tap_off[threadIdx.x] = (uint32_t)(kh * p.Wp + kw) * 128u;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // item -> channel tile, first image of the tile, tile origin
+  auto decode = [&](int item, int& tile_co, int& img, int& y0, int& x0) {
+    tile_co = item % pp.tiles_co;
+    const int mt = item / pp.tiles_co;
+    if (pp.G > 1) {
+      img = mt * pp.G;
+      y0 = 0;
+      x0 = 0;
+    } else {
+      img = mt / p.tiles_per_img;
+      const int tin = mt - img * p.tiles_per_img;
+      y0 = (tin / p.tiles_x) * p.R;
+      x0 = (tin % p.tiles_x) * p.Wt;
+    }
+  };
+
+  if (warp == 5) {
+    if (lane == 0) {
+      int xs = 0, ws = 0;
+      uint32_t x_par = 1, w_par = 1;
+      bool first = true;
+      for (int item = blockIdx.x; item < pp.total_items; item += gridDim.x) {
+        int tile_co, img, y0, x0;
+        decode(item, tile_co, img, y0, x0);
+        for (int cb = 0; cb < ncblk; ++cb) {
+          mbar_wait(&x_empty[xs], x_par);
+          mbar_arrive_expect_tx(&x_full[xs], p.a_tx_bytes);
+          tma_load_4d(x_base + xs * p.a_stage_bytes, &tma_x, &x_full[xs], cb * 64, x0 + p.org_x, y0 + p.org_y, img);
+          if (++xs == A_STAGES) {
+            xs = 0;
+            x_par ^= 1;
+          }
+          if (resident && !first) continue;
+          int krow = cb * 64;
+          for (int t = 0; t < ntaps; ++t, krow += p.C) {
+            if (!resident) mbar_wait(&w_empty[ws], w_par);
+            mbar_arrive_expect_tx(&w_full[ws], W_BYTES);
+#pragma unroll
+            for (int j = 0; j < MW / 64; ++j)
+              tma_load_2d(w_base + ws * W_BYTES + j * 8192, &tma_w, &w_full[ws], tile_co * MW + j * 64, krow);
+            if (++ws == nb) {
+              ws = 0;
+              w_par ^= 1;
+            }
+          }
+        }
+        first = false;
+      }
+    }
+    __syncwarp();
+  } else if (warp == 4) {
+    // The whole warp walks the loop with warp-uniform state (everything derives from kernel parameters and
+    // counters, so descriptors live in uniform registers); one elected lane issues the MMAs and commits.
+    // M = 128 even for MW = 64: the upper 64 accumulator lanes then hold products of whatever follows the weight
+    // tile in shared memory and are never read.
+    constexpr uint32_t idesc = make_idesc_bf16(128, PN_PIX, /*a_mn=*/true, /*b_mn=*/false);
+    const uint64_t wdesc0 = make_smem_desc(w_base, 8192, 1024);
+    const uint64_t xdesc0 = make_smem_desc(x_base, 16, 1024);
+    // tap t -> start-address shift (16-byte units) of the halo tile: +-1 pixel per tap, row wrap every KW taps
+    const int sgn = p.mirror ? -1 : 1;
+    const int off_first = p.mirror ? ((p.KH - 1) * p.Wp + (p.KW - 1)) * 8 : 0;
+    const int off_step = sgn * 8;
+    const int off_wrap = sgn * (p.Wp - p.KW + 1) * 8;
+    const uint32_t x_stage16 = (uint32_t)p.a_stage_bytes >> 4;
+    int xs = 0, ws = 0, buf = 0;
+    uint32_t x_par = 0, w_par = 0, acc_par = 1;
+    for (int item = blockIdx.x; item < pp.total_items; item += gridDim.x) {
+      mbar_wait(&acc_empty[buf], acc_par);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + buf * PN_PIX;
+      uint32_t accum = 0;
+      for (int cb = 0; cb < ncblk; ++cb) {
+        mbar_wait(&x_full[xs], x_par);
+        const uint64_t xdesc_s = xdesc0 + xs * x_stage16;
+        int off = off_first, kw = 0;
+        for (int t = 0; t < ntaps; ++t) {
+          mbar_wait(&w_full[ws], w_par);  // resident: phase 0 completes once, w_par stays 0
+          tc_fence_after();
+          if (elect_one()) {
+            const uint64_t wdesc = wdesc0 + (uint32_t)(ws * (W_BYTES >> 4));
+            const uint64_t xdesc = xdesc_s + (uint32_t)off;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(d_tmem, wdesc + 128 * k, xdesc + 2 * k, idesc, (k > 0) ? 1u : accum);
+            if (!resident) umma_commit(&w_empty[ws]);
+            if (t == ntaps - 1) {
+              umma_commit(&x_empty[xs]);
+              if (cb == ncblk - 1) umma_commit(&acc_full[buf]);
+            }
+          }
+          __syncwarp();
+          accum = 1;
+          if (++kw == p.KW) {
+            kw = 0;
+            off += off_wrap;
+          } else {
+            off += off_step;
+          }
+          if (++ws == nb) {
+            ws = 0;
+            if (!resident) w_par ^= 1;
+          }
+        }
+        if (++xs == A_STAGES) {
+          xs = 0;
+          x_par ^= 1;
+        }
+      }
+      if ((buf ^= 1) == 0) acc_par ^= 1;
+    }
+  } else {
+    // epilogue warp w owns channels [32w, 32w+32) of the item: TMEM lane = channel, column = padded-linear pixel
+    uint8_t* stage = stage_base + warp * (32 * 64);
+    int* tab = tab_base + warp * PN_PIX;
+    const uint32_t lane_addr = ((uint32_t)(warp * 32) << 16);
+    const int m_limit = (pp.G - 1) * pp.img_rows + p.R * p.Wp;  // columns beyond carry no output pixel
+    int buf = 0;
+    uint32_t acc_par = 0;
+    for (int item = blockIdx.x; item < pp.total_items; item += gridDim.x) {
+      int tile_co, img, y0, x0;
+      decode(item, tile_co, img, y0, x0);
+      const int co = tile_co * MW + warp * 32 + lane;
+      const bool warp_live = (warp * 32 < MW) && (tile_co * MW + warp * 32 < p.n_out);
+      if (warp_live) {
+#pragma unroll 1
+        for (int q = 0; q < PN_PIX / 32; ++q) {
+          const int m = q * 32 + lane;
+          const int g = m / pp.img_rows;
+          const int rem = m - g * pp.img_rows;
+          const int ry = rem / p.Wp;
+          const int xx = rem - ry * p.Wp;
+          const int x = x0 + xx, y = y0 + ry, im = img + g;
+          const bool valid = (g < pp.G) && (im < p.n_img) && (ry < p.R) && (xx < p.Wt) && (x < p.W) && (y < p.H);
+          tab[m] = valid ? (int)(((long long)im * p.H + y) * p.W + x) : -1;
+        }
+        __syncwarp();
+      }
+      const float bias = (warp_live && p.bias != nullptr && co < p.n_out) ? __ldg(p.bias + co) : 0.f;
+      mbar_wait(&acc_full[buf], acc_par);
+      tc_fence_after();
+      if (warp_live) {
+#pragma unroll 1
+        for (int cc = 0; cc < PN_PIX / 32; ++cc) {
+          if (cc * 32 >= m_limit) break;
+          uint32_t v[32];
+          tmem_ld32(tmem_base + buf * PN_PIX + lane_addr + cc * 32, v);
+          tmem_ld_wait();
+          __nv_bfloat16* st = reinterpret_cast<__nv_bfloat16*>(stage) + lane;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float f = __uint_as_float(v[j]) + bias;
+            if (p.relu) f = fmaxf(f, 0.f);
+            st[j * 32] = __float2bfloat16(f);  // stage[pixel j][channel lane]
+          }
+          __syncwarp();
+          const int c8 = (lane & 3) * 8;
+          const int n = tile_co * MW + warp * 32 + c8;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int r = i * 8 + (lane >> 2);
+            const int pr = tab[cc * 32 + r];
+            const uint4 q = *reinterpret_cast<const uint4*>(stage + r * 64 + c8 * 2);
+            if (pr >= 0 && n + 8 <= p.n_out)
+              *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)pr * p.n_out + n) = q;
+          }
+          __syncwarp();
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      if ((buf ^= 1) == 0) acc_par ^= 1;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// --------------------------------------------------------------------------------------------------------------
 // Filter gradient on halo tiles: dW[tap, ci, co] = sum over pixels p of x[p + shift(tap), ci] * dy[p, co].
 // A CTA owns one (64 ci) x (64 co) block of ALL taps and walks a range of image tiles. Per tile one TMA load brings
 // the x halo (same box as fprop) and R row loads bring the dy tile into the padded-linear layout (gap positions stay
@@ -525,16 +792,17 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_consta
     }
     __syncwarp();
   } else if (warp == 4) {
-    if (lane == 0) {  // one thread runs the whole issue loop; per-pair descriptor parts come from a table
-      constexpr uint32_t idesc = make_idesc_bf16(128, 64, /*a_mn=*/true, /*b_mn=*/true);
-      const uint64_t bdesc0 = make_smem_desc(0, 8192, 1024);
-      int s = 0;
-      uint32_t ph = 0, accum0 = 0;
-      for (int t = t_begin; t < t_end; ++t) {
-        mbar_wait(&full[s], ph);
-        tc_fence_after();
+    // warp-uniform loop; one elected lane issues. Per-pair shift / LBO are read from a small table.
+    constexpr uint32_t idesc = make_idesc_bf16(128, 64, /*a_mn=*/true, /*b_mn=*/true);
+    const uint64_t bdesc0 = make_smem_desc(b_base, 8192, 1024);
+    int s = 0;
+    uint32_t ph = 0, accum0 = 0;
+    for (int t = t_begin; t < t_end; ++t) {
+      mbar_wait(&full[s], ph);
+      tc_fence_after();
+      if (elect_one()) {
         const uint32_t a_stage = a_base + s * p.a_stage_bytes;
-        const uint64_t bdesc = bdesc0 + ((b_base + s * WG_B_BYTES) >> 4);
+        const uint64_t bdesc = bdesc0 + (uint32_t)(s * (WG_B_BYTES >> 4));
         for (int j = 0; j < npairs; ++j) {
           const uint64_t adesc = pair_desc[j] + ((a_stage + pair_off[j]) >> 4);
           const uint32_t d_tmem = tmem_base + j * 64;
@@ -542,15 +810,17 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_consta
 #pragma unroll
           for (int k = 1; k < 8; ++k) umma_bf16(d_tmem, adesc + k * 128, bdesc + k * 128, idesc, 1u);
         }
-        accum0 = 1;
         umma_commit(&empty[s]);
-        if (++s == WG_STAGES) {
-          s = 0;
-          ph ^= 1;
-        }
+        if (t == t_end - 1) umma_commit(tmem_full);
       }
-      umma_commit(tmem_full);
+      __syncwarp();
+      accum0 = 1;
+      if (++s == WG_STAGES) {
+        s = 0;
+        ph ^= 1;
+      }
     }
+    if (t_end <= t_begin && elect_one()) umma_commit(tmem_full);
     __syncwarp();
   } else {
     mbar_wait(tmem_full, 0);
@@ -624,7 +894,7 @@ static int launch(const CUtensorMap& tx, const CUtensorMap& tw, const Params& p,
 }
 
 
-static int g_halo_persistent = 1;
+static int g_halo_persistent = 2;  // 2: pixels-as-N kernel, 1: persistent channel-as-N, 0: one tile per CTA
 
 // Persistent launch: returns DTF_ERR_UNSUPPORTED when the shared-memory plan does not fit (caller falls back).
 template <int BN>
@@ -663,6 +933,109 @@ static int launch_persistent(const CUtensorMap& tx, const CUtensorMap& tw, const
   return DTF_CHECK_LAUNCH();
 }
 
+
+// Tile plan of the pixels-as-N kernel: Wt x R output pixels per tile with R*(Wt+KW-1) <= 256 GEMM columns, or G
+// whole images per tile when one image needs less than half of them. Returns the fraction of useful columns.
+static double pn_plan(int H, int W, int KH, int KW, int* Wt_out, int* R_out, int* G_out) {
+  double best = 0.0;
+  long long best_load = 0;
+  int bw = 0, br = 0, bg = 1;
+  for (int Wt = 1; Wt <= W && Wt + KW - 1 <= 256; ++Wt) {
+    const int Wp = Wt + KW - 1;
+    int R = PN_PIX / Wp;
+    if (R > H) R = H;
+    if (R < 1 || R + KH - 1 > 256) continue;
+    const int hp = R + KH - 1;
+    int G = 1;
+    if (Wt == W && R == H) {
+      G = 1 + (PN_PIX - R * Wp) / (hp * Wp);
+      if (G > 64) G = 64;
+    }
+    const long long tiles = (long long)((W + Wt - 1) / Wt) * ((H + R - 1) / R);
+    const double util = (double)G * H * W / (double)(tiles * PN_PIX);
+    const long long load = tiles * hp * Wp;  // halo pixels fetched per image
+    if (util > best + 1e-9 || (util > best - 1e-9 && load < best_load)) {
+      best = util;
+      best_load = load;
+      bw = Wt;
+      br = R;
+      bg = G;
+    }
+  }
+  *Wt_out = bw;
+  *R_out = br;
+  *G_out = bg;
+  return best;
+}
+
+struct PnHost {
+  Params p;
+  PnParams pp;
+  int smem;
+  int halo_rows;
+};
+
+// Fills the kernel parameters; false when the geometry does not suit the pixels-as-N kernel.
+static bool pn_setup(int n_img, int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror,
+                     PnHost* h) {
+  if ((C & 63) || (n_out & 7) || KH * KW < 2 || KH * KW > 49) return false;
+  Params& p = h->p;
+  PnParams& pp = h->pp;
+  p = Params{};
+  pp = PnParams{};
+  p.n_img = n_img; p.H = H; p.W = W; p.C = C; p.n_out = n_out; p.KH = KH; p.KW = KW;
+  if (pn_plan(H, W, KH, KW, &p.Wt, &p.R, &pp.G) < 0.5) return false;
+  p.Wp = p.Wt + KW - 1;
+  p.tiles_x = (W + p.Wt - 1) / p.Wt;
+  p.tiles_per_img = p.tiles_x * ((H + p.R - 1) / p.R);
+  p.mirror = mirror;
+  p.org_x = mirror ? -(KW - 1 - pad_w) : -pad_w;
+  p.org_y = mirror ? -(KH - 1 - pad_h) : -pad_h;
+  h->halo_rows = p.R + KH - 1;
+  pp.img_rows = h->halo_rows * p.Wp;
+  p.a_tx_bytes = pp.G * pp.img_rows * 128;
+  const int span = (PN_PIX + (KH - 1) * p.Wp + (KW - 1)) * 128;
+  p.a_stage_bytes = ((span > p.a_tx_bytes ? span : p.a_tx_bytes) + 1023) & ~1023;
+  const int mw = n_out <= 64 ? 64 : 128;
+  const int w_bytes = mw * 128;
+  pp.tiles_co = (n_out + mw - 1) / mw;
+  pp.groups = pp.G > 1 ? (n_img + pp.G - 1) / pp.G : n_img * p.tiles_per_img;
+  const long long items = (long long)pp.groups * pp.tiles_co;
+  if (items > 0x7fffffffLL || (long long)n_img * H * W > 0x7fffffffLL) return false;
+  pp.total_items = (int)items;
+  const int fixed = 1024 + A_STAGES * p.a_stage_bytes + 1024 + PN_STAGE_BYTES + PN_TAB_BYTES;
+  const int avail = 227 * 1024 - fixed;
+  const int total_w = KH * KW * (C >> 6);
+  if (pp.tiles_co == 1 && total_w <= MAX_B_STAGES && total_w * w_bytes <= avail) {
+    pp.resident = 1;
+    pp.nb = total_w;
+  } else {
+    pp.nb = avail / w_bytes;
+    if (pp.nb > 8) pp.nb = 8;
+    if (pp.nb < 2) return false;
+  }
+  h->smem = fixed + pp.nb * w_bytes;
+  return true;
+}
+
+template <int MW>
+static int launch_pn(const CUtensorMap& tx, const CUtensorMap& tw, const PnHost& h, cudaStream_t stream) {
+  auto kern = conv_halo_pn_kernel<MW>;
+  static int attr[64] = {};
+  static int sms[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (attr[dev & 63] < h.smem) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, h.smem) != cudaSuccess)
+      return DTF_ERR_CUDA;
+    attr[dev & 63] = h.smem;
+  }
+  if (sms[dev & 63] == 0) cudaDeviceGetAttribute(&sms[dev & 63], cudaDevAttrMultiProcessorCount, dev);
+  const int grid = h.pp.total_items < sms[dev & 63] ? h.pp.total_items : sms[dev & 63];
+  kern<<<grid, NUM_THREADS, h.smem, stream>>>(tx, tw, h.p, h.pp);
+  return DTF_CHECK_LAUNCH();
+}
+
 }  // namespace halo
 }  // namespace dtf
 
@@ -691,10 +1064,18 @@ static double halo_plan(int H, int W, int KH, int KW, int* Wt_out, int* R_out) {
 }
 
 // 1 if dtf_conv_halo_bf16 supports the geometry (stride 1, C % 64 == 0, tile utilisation >= 60 %).
-extern "C" int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int n_out) {
+static int legacy_halo_supported(int H, int W, int C, int KH, int KW, int n_out) {
   if ((C & 63) || (n_out & 7) || KH * KW < 2 || KH > 7 || KW > 7) return 0;
   int Wt, R;
   return halo_plan(H, W, KH, KW, &Wt, &R) >= 0.60 ? 1 : 0;
+}
+extern "C" int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int n_out) {
+  if (KH > 7 || KW > 7) return 0;
+  if (dtf::halo::g_halo_persistent >= 2) {
+    dtf::halo::PnHost h;
+    if (dtf::halo::pn_setup(1 << 10, H, W, C, KH, KW, n_out, 0, 0, 0, &h)) return 1;
+  }
+  return legacy_halo_supported(H, W, C, KH, KW, n_out);
 }
 
 // src: x (fprop) or dy (mirror = 1, data gradient) [n_img, H, W, C]; W2d: [KH*KW*C, n_out] row-major bf16 (HWIO for
@@ -704,9 +1085,31 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
                                   int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags,
                                   void* stream_) {
   using namespace dtf::halo;
-  if (!dtf_conv_halo_supported(H, W, C, KH, KW, n_out)) return DTF_ERR_UNSUPPORTED;
+  if (KH > 7 || KW > 7) return DTF_ERR_UNSUPPORTED;
   EncodeTiledFn fn = encode_fn();
   if (!fn) return DTF_ERR_DRIVER;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PnHost h;
+  if (g_halo_persistent >= 2 && pn_setup(n_img, H, W, C, KH, KW, n_out, pad_h, pad_w, mirror, &h)) {
+    h.p.out = out; h.p.bias = bias; h.p.relu = flags & 1;
+    CUtensorMap tx, tw;
+    cuuint32_t es4[4] = {1, 1, 1, 1};
+    cuuint64_t xd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n_img};
+    cuuint64_t xs[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t xb[4] = {64, (cuuint32_t)h.p.Wp, (cuuint32_t)h.halo_rows, (cuuint32_t)h.pp.G};
+    cuuint64_t wd[2] = {(cuuint64_t)n_out, (cuuint64_t)KH * KW * C};
+    cuuint64_t ws[1] = {(cuuint64_t)n_out * 2};
+    cuuint32_t wb[2] = {64, 64};
+    if (fn(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(src), xd, xs, xb, es4,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS ||
+        fn(&tw, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(W2d), wd, ws, wb, es4,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return DTF_ERR_TENSORMAP;
+    return n_out <= 64 ? launch_pn<64>(tx, tw, h, stream) : launch_pn<128>(tx, tw, h, stream);
+  }
+  if (!legacy_halo_supported(H, W, C, KH, KW, n_out)) return DTF_ERR_UNSUPPORTED;
   Params p{};
   p.n_img = n_img; p.H = H; p.W = W; p.C = C; p.n_out = n_out; p.KH = KH; p.KW = KW;
   halo_plan(H, W, KH, KW, &p.Wt, &p.R);
@@ -743,7 +1146,6 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return DTF_ERR_TENSORMAP;
   }
-  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   if (g_halo_persistent) {
     const int rc = (n_out <= 64) ? launch_persistent<64>(tx, tw, p, stream) : launch_persistent<128>(tx, tw, p, stream);
     if (rc != DTF_ERR_UNSUPPORTED) return rc;
@@ -752,10 +1154,11 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
   return launch<128, 4>(tx, tw, p, stream);
 }
 
-// 1 (default): the persistent halo kernel; 0: one tile per CTA. Returns the previous setting.
-extern "C" int dtf_set_persistent_halo(int on) {
+// 2 (default): pixels-as-N persistent kernel; 1: persistent channels-as-N kernel; 0: one tile per CTA.
+// Returns the previous setting.
+extern "C" int dtf_set_persistent_halo(int mode) {
   const int prev = dtf::halo::g_halo_persistent;
-  dtf::halo::g_halo_persistent = on ? 1 : 0;
+  dtf::halo::g_halo_persistent = mode < 0 ? 0 : (mode > 2 ? 2 : mode);
   return prev;
 }
 

@@ -441,33 +441,37 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
     tc_fence_after();
     igemm_epilogue<BN>(p, tmem_base, tile_m, tile_n, warp);
   } else if (warp == 4) {
-    // ===================================================== MMA issuer (one thread runs the whole loop)
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, /*b_mn=*/true);
-      const uint64_t adesc0 = kAMn ? make_smem_desc(0, /*lbo=*/8192, /*sbo=*/1024) : make_smem_desc(0, 16, 1024);
-      const uint64_t bdesc0 = make_smem_desc(0, /*lbo=*/8192, /*sbo=*/1024);
-      constexpr uint32_t kAStep = kAMn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
-      constexpr uint32_t kBStep = (UMMA_K * 128) >> 4;
-      int s = 0;
-      uint32_t ph = 0, accum = 0;
-      for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(&full_bar[s], ph);
-        tc_fence_after();
-        const uint64_t adesc = adesc0 + (a_stage(s) >> 4);
-        const uint64_t bdesc = bdesc0 + (b_stage(s) >> 4);
+    // ===================================================== MMA issuer
+    // The warp walks the loop with warp-uniform state (descriptors stay in uniform registers, ring index and phase
+    // are counters); one elected lane issues the MMAs and the commits.
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, /*b_mn=*/true);
+    const uint64_t adesc0 = kAMn ? make_smem_desc(a_stage(0), /*lbo=*/8192, /*sbo=*/1024) : make_smem_desc(a_stage(0), 16, 1024);
+    const uint64_t bdesc0 = make_smem_desc(b_stage(0), /*lbo=*/8192, /*sbo=*/1024);
+    constexpr uint32_t kAStep = kAMn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+    constexpr uint32_t kBStep = (UMMA_K * 128) >> 4;
+    constexpr uint32_t kStage16 = L::STAGE_BYTES >> 4;
+    int s = 0;
+    uint32_t ph = 0, accum = 0;
+    for (int kb = kb0; kb < kb1; ++kb) {
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t adesc = adesc0 + (uint32_t)s * kStage16;
+        const uint64_t bdesc = bdesc0 + (uint32_t)s * kStage16;
 #pragma unroll
-        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-          umma_bf16(tmem_base, adesc + k * kAStep, bdesc + k * kBStep, idesc, accum);
-          accum = 1;
-        }
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+          umma_bf16(tmem_base, adesc + k * kAStep, bdesc + k * kBStep, idesc, (k > 0) ? 1u : accum);
         umma_commit(&empty_bar[s]);
-        if (++s == STAGES) {
-          s = 0;
-          ph ^= 1;
-        }
+        if (kb == kb1 - 1) umma_commit(tmem_full_bar);
       }
-      umma_commit(tmem_full_bar);
+      __syncwarp();
+      accum = 1;
+      if (++s == STAGES) {
+        s = 0;
+        ph ^= 1;
+      }
     }
+    if (kb1 <= kb0 && elect_one()) umma_commit(tmem_full_bar);
     __syncwarp();
   } else {
     // ===================================================== TMA producer (B always; A in dense modes)
@@ -587,42 +591,43 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
     }
     __syncwarp();
   } else if (warp == 4) {
-    if (lane == 0) {  // one thread runs the whole issue loop; ring indices and phases are counters
-      constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, true);
-      const uint64_t adesc0 = kAMn ? make_smem_desc(0, 8192, 1024) : make_smem_desc(0, 16, 1024);
-      const uint64_t bdesc0 = make_smem_desc(0, 8192, 1024);
-      constexpr uint32_t kAStep = kAMn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
-      constexpr uint32_t kBStep = (UMMA_K * 128) >> 4;
-      int s = 0, buf = 0;
-      uint32_t ph = 0, acc_par = 1;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        int tile_m, tile_n, kb0, kb1;
-        decode(t, tile_m, tile_n, kb0, kb1);
-        mbar_wait(&acc_empty[buf], acc_par);  // epilogue has drained this accumulator
+    // warp-uniform loop state (descriptors in uniform registers); one elected lane issues MMAs and commits
+    constexpr uint32_t idesc = make_idesc_bf16(BLOCK_M, BN, kAMn, true);
+    const uint64_t adesc0 = kAMn ? make_smem_desc(a_stage(0), 8192, 1024) : make_smem_desc(a_stage(0), 16, 1024);
+    const uint64_t bdesc0 = make_smem_desc(b_stage(0), 8192, 1024);
+    constexpr uint32_t kAStep = kAMn ? (UMMA_K * 128) >> 4 : (UMMA_K * 2) >> 4;
+    constexpr uint32_t kBStep = (UMMA_K * 128) >> 4;
+    constexpr uint32_t kStage16 = L::STAGE_BYTES >> 4;
+    int s = 0, buf = 0;
+    uint32_t ph = 0, acc_par = 1;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      int tile_m, tile_n, kb0, kb1;
+      decode(t, tile_m, tile_n, kb0, kb1);
+      mbar_wait(&acc_empty[buf], acc_par);  // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + buf * BN;
+      uint32_t accum = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[s], ph);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + buf * BN;
-        uint32_t accum = 0;
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(&full_bar[s], ph);
-          tc_fence_after();
-          const uint64_t adesc = adesc0 + (a_stage(s) >> 4);
-          const uint64_t bdesc = bdesc0 + (b_stage(s) >> 4);
+        if (elect_one()) {
+          const uint64_t adesc = adesc0 + (uint32_t)s * kStage16;
+          const uint64_t bdesc = bdesc0 + (uint32_t)s * kStage16;
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            umma_bf16(d_tmem, adesc + k * kAStep, bdesc + k * kBStep, idesc, accum);
-            accum = 1;
-          }
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            umma_bf16(d_tmem, adesc + k * kAStep, bdesc + k * kBStep, idesc, (k > 0) ? 1u : accum);
           umma_commit(&empty_bar[s]);
-          if (++s == STAGES) {
-            s = 0;
-            ph ^= 1;
-          }
+          if (kb == kb1 - 1) umma_commit(&acc_full[buf]);
         }
-        umma_commit(&acc_full[buf]);
-        if ((buf ^= 1) == 0) acc_par ^= 1;
+        __syncwarp();
+        accum = 1;
+        if (++s == STAGES) {
+          s = 0;
+          ph ^= 1;
+        }
       }
+      if ((buf ^= 1) == 0) acc_par ^= 1;
     }
-    __syncwarp();
   } else {
     int lt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
