@@ -108,6 +108,119 @@ __global__ void add_kernel(const __nv_bfloat16* __restrict__ a, const __nv_bfloa
   }
 }
 
+// ------------------------------------------------------------------------------------------- window packing
+// Strided and few-channel convolutions are turned into stride-1 convolutions over 64-channel-aligned pixels (the
+// halo kernels' home ground) by packing a small input window into the channel dimension:
+//   P[n, j, i, (r*kwn + q)*cs + c] = x[n, rp*j + r - oy, sx*i + q - ox, c]      (0 outside the image / unused channels)
+// space-to-depth (rp = kwn = sx = 2, cs = C) serves the stride-2 3x3 layers; packing all KW horizontal taps of rp
+// rows (kwn = KW, cs = C) serves the 3-channel first layers. conv weights are re-indexed to match (block_copy below).
+struct PackParams {
+  int n_img, H, W, Cx, C;  // source [n, H, W, Cx], first C channels used
+  int Hp, Wq, Cp;          // packed [n, Hp, Wq, Cp]
+  int rp, kwn, sx, cs, oy, ox;
+};
+template <bool VEC>
+__global__ void pack_window_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ P,
+                                   const PackParams p) {
+  const int cpr = p.Cp / 8;
+  const long long total = (long long)p.n_img * p.Hp * p.Wq * cpr;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int ch0 = (int)(idx % cpr) * 8;
+    long long t = idx / cpr;
+    const int i = (int)(t % p.Wq);
+    t /= p.Wq;
+    const int j = (int)(t % p.Hp);
+    const int n = (int)(t / p.Hp);
+    BF8 v;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v.v[k] = __floats2bfloat162_rn(0.f, 0.f);
+    if (VEC) {  // cs % 8 == 0 and C % 8 == 0: the 8 channels are contiguous in the source
+      const int slot = ch0 / p.cs, c = ch0 - slot * p.cs;
+      const int r = slot / p.kwn, q = slot - r * p.kwn;
+      const int y = p.rp * j + r - p.oy, xx = p.sx * i + q - p.ox;
+      if (r < p.rp && c < p.C && y >= 0 && y < p.H && xx >= 0 && xx < p.W)
+        v = ld8(x + (((long long)n * p.H + y) * p.W + xx) * p.Cx + c);
+    } else {
+      // few channels per window slot: walk (slot, channel) incrementally, fetch each source pixel once as a
+      // 16-byte vector (its first 8 channels) and pick the live channels out of registers
+      __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(&v);
+      int slot = ch0 / p.cs, c = ch0 - slot * p.cs;
+      const bool vec_src = (p.Cx % 8 == 0) && (p.C <= 8);
+      unsigned long long pix_lo = 0, pix_hi = 0;
+      const __nv_bfloat16* src = nullptr;
+      bool fresh = true;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (fresh) {
+          const int r = slot / p.kwn, q = slot - r * p.kwn;
+          const int y = p.rp * j + r - p.oy, xx = p.sx * i + q - p.ox;
+          src = (r < p.rp && y >= 0 && y < p.H && xx >= 0 && xx < p.W)
+                    ? x + (((long long)n * p.H + y) * p.W + xx) * p.Cx : nullptr;
+          if (vec_src && src) {
+            const uint4 raw = *reinterpret_cast<const uint4*>(src);
+            pix_lo = raw.x | ((unsigned long long)raw.y << 32);
+            pix_hi = raw.z | ((unsigned long long)raw.w << 32);
+          }
+          fresh = false;
+        }
+        if (src != nullptr && c < p.C)
+          e[k] = vec_src ? __ushort_as_bfloat16((unsigned short)(((c < 4) ? pix_lo : pix_hi) >> ((c & 3) * 16))) : src[c];
+        if (++c == p.cs) {
+          c = 0;
+          ++slot;
+          fresh = true;
+        }
+      }
+    }
+    st8(P + idx * 8, v);
+  }
+}
+// Inverse of the space-to-depth packing (rp = kwn = sx = 2, cs = C): dx[n, y, x, c] = dP[n, j, i, (r*2+q)*C + c].
+__global__ void unpack_s2d_kernel(const __nv_bfloat16* __restrict__ dP, __nv_bfloat16* __restrict__ dx, int n_img,
+                                  int H, int W, int C, int Hp, int Wq, int oy, int ox) {
+  const int cpr = C / 8;
+  const long long total = (long long)n_img * H * W * cpr;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(idx % cpr) * 8;
+    long long t = idx / cpr;
+    const int xx = (int)(t % W);
+    t /= W;
+    const int y = (int)(t % H);
+    const int n = (int)(t / H);
+    const int j = (y + oy) >> 1, r = (y + oy) & 1, i = (xx + ox) >> 1, q = (xx + ox) & 1;
+    BF8 v;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v.v[k] = __floats2bfloat162_rn(0.f, 0.f);
+    if (j < Hp && i < Wq) v = ld8(dP + (((long long)n * Hp + j) * Wq + i) * (4LL * C) + (r * 2 + q) * C + c0);
+    st8(dx + idx * 8, v);
+  }
+}
+// Rectangular block moves between row-major matrices (weight re-indexing for the packed convolutions and the
+// scatter of packed filter gradients back into the gradient arena). src_off < 0 writes zeros.
+struct BlockDesc {
+  long long src_off, dst_off;  // element offsets of the block's first element
+  int rows, cols;
+};
+template <typename T, bool ACC>
+__global__ void block_copy_kernel(const T* __restrict__ src, int ld_src, T* __restrict__ dst, int ld_dst,
+                                  const BlockDesc* __restrict__ descs) {
+  const BlockDesc d = descs[blockIdx.y];
+  const int total = d.rows * d.cols;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const int r = e / d.cols, c = e - r * d.cols;
+    T* o = dst + d.dst_off + (long long)r * ld_dst + c;
+    if (d.src_off < 0) {
+      if (!ACC) *o = T(0.f);
+    } else {
+      const T v = src[d.src_off + (long long)r * ld_src + c];
+      if (ACC) *o = *o + v;
+      else *o = v;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------- strided pixel sampling
 // y[n, oh, ow, :] = x[n, oh*s, ow*s, :] (forward of a 1x1 stride-s convolution's input selection), and its adjoint:
 // dx[n, h, w, :] = dy[n, h/s, w/s, :] if h % s == 0 and w % s == 0 else 0.
@@ -993,6 +1106,44 @@ extern "C" int dtf_convert_input(const void* src, void* dst, long long pixels, i
   else
     convert_input_kernel<float><<<g, 256, 0, ST(stream)>>>((const float*)src, (__nv_bfloat16*)dst, pixels, C, Cpad,
                                                            scale, shift);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_pack_window(const void* x, void* P, int n_img, int H, int W, int Cx, int C, int Hp, int Wq, int Cp,
+                               int rp, int kwn, int sx, int cs, int oy, int ox, void* stream) {
+  if ((Cp % 8) || rp < 1 || kwn < 1 || cs < 1 || rp * kwn * cs > Cp) return DTF_ERR_ALIGN;
+  PackParams p{n_img, H, W, Cx, C, Hp, Wq, Cp, rp, kwn, sx, cs, oy, ox};
+  const long long total = (long long)n_img * Hp * Wq * (Cp / 8);
+  const bool vec = (cs % 8 == 0) && (C % 8 == 0) && (Cx % 8 == 0);
+  if (vec)
+    pack_window_kernel<true><<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)P, p);
+  else
+    pack_window_kernel<false><<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)P, p);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_unpack_s2d(const void* dP, void* dx, int n_img, int H, int W, int C, int Hp, int Wq, int oy, int ox,
+                              void* stream) {
+  if (C % 8) return DTF_ERR_ALIGN;
+  unpack_s2d_kernel<<<grid_for((long long)n_img * H * W * (C / 8), 256), 256, 0, ST(stream)>>>(
+      (const __nv_bfloat16*)dP, (__nv_bfloat16*)dx, n_img, H, W, C, Hp, Wq, oy, ox);
+  return DTF_CHECK_LAUNCH();
+}
+// descs: device array of n_blocks {int64 src_off, int64 dst_off, int32 rows, int32 cols}; dtype 0 bf16, 1 fp32.
+extern "C" int dtf_block_copy(const void* src, int ld_src, void* dst, int ld_dst, const void* descs, int n_blocks,
+                              int max_elems, int dtype, int accumulate, void* stream) {
+  if (n_blocks <= 0) return DTF_OK;
+  int gx = (max_elems + 255) / 256;
+  if (gx < 1) gx = 1;
+  if (gx > 64) gx = 64;
+  dim3 grid(gx, n_blocks);
+  const BlockDesc* d = (const BlockDesc*)descs;
+  if (dtype == 0 && !accumulate)
+    block_copy_kernel<__nv_bfloat16, false><<<grid, 256, 0, ST(stream)>>>((const __nv_bfloat16*)src, ld_src, (__nv_bfloat16*)dst, ld_dst, d);
+  else if (dtype == 1 && accumulate)
+    block_copy_kernel<float, true><<<grid, 256, 0, ST(stream)>>>((const float*)src, ld_src, (float*)dst, ld_dst, d);
+  else if (dtype == 1)
+    block_copy_kernel<float, false><<<grid, 256, 0, ST(stream)>>>((const float*)src, ld_src, (float*)dst, ld_dst, d);
+  else
+    return DTF_ERR_UNSUPPORTED;
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_subsample(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int s,

@@ -42,9 +42,13 @@ class ConvFn(torch.autograd.Function):
         KH, KW, Ci, Co = wvar.store_shape
         w2d = w_shadow.detach().view(KH * KW * Ci, Co)
         bias = bvar.master if bvar is not None else None
-        y = raw.conv_fprop(x, w2d, bias, KH, KW, stride, relu=relu)
+        keep = {}
+        y = raw.conv_fprop(x, w2d, bias, KH, KW, stride, relu=relu, c_used=wvar.shape[2], keep=keep)
         ctx.wvar, ctx.bvar, ctx.stride, ctx.relu = wvar, bvar, stride, relu
-        ctx.save_for_backward(x, y if relu else None)
+        # strided / few-channel layers ran on a packed copy of x: keep that for the filter gradient instead of x
+        ctx.packed = "packed" in keep
+        ctx.x_shape = tuple(x.shape)
+        ctx.save_for_backward(keep["packed"] if ctx.packed else x, y if relu else None)
         ctx.x_needs_grad = x.requires_grad
         return y
 
@@ -66,13 +70,17 @@ class ConvFn(torch.autograd.Function):
             if bvar is not None:
                 raw.bias_grad(dy2, bvar.grad)
         dz = dz2.view(n, OH, OW, Co)
-        raw.conv_wgrad(x, dz, KH, KW, ctx.stride, out=wvar.grad.view(KH * KW * Ci, Co))
+        if ctx.packed:
+            raw.conv_wgrad(None, dz, KH, KW, ctx.stride, out=wvar.grad.view(KH * KW * Ci, Co), c_used=wvar.shape[2],
+                           packed=x, x_shape=ctx.x_shape)
+        else:
+            raw.conv_wgrad(x, dz, KH, KW, ctx.stride, out=wvar.grad.view(KH * KW * Ci, Co), c_used=wvar.shape[2])
         _ready(wvar)
         if bvar is not None:
             _ready(bvar)
         dx = None
         if ctx.x_needs_grad:
-            dx = raw.conv_dgrad(dz, wvar.shadow_t.view(KH * KW * Co, Ci), (x.shape[1], x.shape[2]), KH, KW, ctx.stride)
+            dx = raw.conv_dgrad(dz, wvar.shadow_t.view(KH * KW * Co, Ci), ctx.x_shape[1:3], KH, KW, ctx.stride)
         return dx, None, None, None, None, None, None
 
 

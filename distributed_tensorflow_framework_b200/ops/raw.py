@@ -75,7 +75,113 @@ def upsample_zero(dy, in_hw, s):
     return dx
 
 
-def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False):
+# ------------------------------------------------------------------------------------------------ window packing
+USE_PACK = True  # strided KxK and few-channel convolutions run as stride-1 halo convolutions over packed windows
+_PLANS = {}
+
+
+class _PackPlan(object):
+    """Geometry of `P[n, j, i, (r*kwn + q)*cs + c] = x[n, rp*j + r, sx*i + q - ox, c]` and of the stride-1
+    convolution over P that equals the original one (see csrc/ops.cu pack_window_kernel)."""
+
+    def __init__(self, H, W, Cx, C, KH, KW, stride, pt, pl, mode):
+        self.H, self.W, self.Cx, self.C, self.KH, self.KW, self.stride = H, W, Cx, C, KH, KW, stride
+        self.mode = mode
+        self.Hp, self.Wq = -(-H // stride), -(-W // stride)
+        if mode == "s2d":
+            self.rp, self.kwn, self.sx, self.cs, self.ox, self.Cp = 2, 2, 2, Cx, 0, 4 * Cx
+        else:
+            self.rp, self.kwn, self.sx, self.cs, self.ox, self.Cp = stride, KW, stride, C, pl, 64
+        self.taps = []  # (kh, kw, a, b, slot)
+        for kh in range(KH):
+            a, r = divmod(kh - pt, self.rp)
+            for kw in range(KW):
+                if mode == "s2d":
+                    b, q = divmod(kw - pl, 2)
+                else:
+                    b, q = 0, kw
+                self.taps.append((kh, kw, a, b, r * self.kwn + q))
+        amin = min(t[2] for t in self.taps)
+        bmin = min(t[3] for t in self.taps)
+        self.KH2 = max(t[2] for t in self.taps) - amin + 1
+        self.KW2 = max(t[3] for t in self.taps) - bmin + 1
+        self.pad_h2, self.pad_w2 = -amin, -bmin
+        self.taps = [(kh, kw, (a - amin) * self.KW2 + (b - bmin), slot) for (kh, kw, a, b, slot) in self.taps]
+        self._descs = {}
+
+    def descs(self, kind, n_out, device, flip=False):
+        """Device block list for dtf_block_copy. kind 'w': [KH*KW*Cx, n_out] -> packed [KH2*KW2*Cp, n_out];
+        'wt': per-tap transposed [KH*KW*n_out, Cx] -> [KH2*KW2*n_out, Cp]; 'dw': packed gradient -> filter gradient."""
+        key = (kind, n_out, str(device), flip)
+        if key not in self._descs:
+            rows = []
+            for (kh, kw, tap2, slot) in self.taps:
+                tsrc = ((self.KH - 1 - kh) * self.KW + (self.KW - 1 - kw)) if flip else (kh * self.KW + kw)
+                if kind == "wt":
+                    src = tsrc * n_out * self.Cx
+                    dst = tap2 * n_out * self.Cp + slot * self.cs
+                    r, c = n_out, self.C
+                else:
+                    src = tsrc * self.Cx * n_out
+                    dst = (tap2 * self.Cp + slot * self.cs) * n_out
+                    r, c = self.C, n_out
+                    if kind == "dw":
+                        src, dst = dst, src
+                rows.append([src, dst, r | (c << 32)])
+            self._descs[key] = (torch.tensor(rows, dtype=torch.int64, device=device), len(rows), rows[0][2] & 0xffffffff,
+                                rows[0][2] >> 32)
+        return self._descs[key]
+
+
+def _pack_plan(H, W, Cx, c_used, KH, KW, stride, pads=None):
+    """The packing plan for a convolution over x[n, H, W, Cx] (first c_used channels live), or None."""
+    if not USE_PACK or KH * KW < 2:
+        return None
+    if pads is None:
+        pads = (same_pad(H, KH, stride)[1], same_pad(W, KW, stride)[1])
+    key = (H, W, Cx, c_used, KH, KW, stride, pads)
+    if key not in _PLANS:
+        if stride == 2 and c_used == Cx and Cx % 16 == 0 and KH > 1 and KW > 1:
+            _PLANS[key] = _PackPlan(H, W, Cx, Cx, KH, KW, stride, pads[0], pads[1], "s2d")
+        elif stride in (1, 2) and stride * KW * c_used <= 64 and Cx % 64 != 0:
+            _PLANS[key] = _PackPlan(H, W, Cx, c_used, KH, KW, stride, pads[0], pads[1], "full")
+        else:
+            _PLANS[key] = None
+    return _PLANS[key]
+
+
+def pack_window(x, plan):
+    n = x.shape[0]
+    P = torch.empty((n, plan.Hp, plan.Wq, plan.Cp), device=x.device, dtype=bf16)
+    _lib.call("dtf_pack_window", x, P, n, plan.H, plan.W, plan.Cx, plan.C, plan.Hp, plan.Wq, plan.Cp, plan.rp, plan.kwn,
+              plan.sx, plan.cs, 0, plan.ox, _sp())
+    return P
+
+
+def _block_copy(src, dst, desc, fp32=False, accumulate=False):
+    t, nblk, r, c = desc
+    _lib.call("dtf_block_copy", src, src.stride(0), dst, dst.stride(0), t, nblk, r * c, 1 if fp32 else 0,
+              1 if accumulate else 0, _sp())
+
+
+def _packed_fprop(x, w2d, bias, plan, relu, flip=False, keep=None):
+    """The convolution of `plan` as pack + stride-1 halo convolution; None if the halo kernel does not take it."""
+    n_out = w2d.shape[1]
+    if not _lib.lib().dtf_conv_halo_supported(plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out):
+        return None
+    n = x.shape[0]
+    P = pack_window(x, plan)
+    if keep is not None:
+        keep["packed"] = P  # the caller may hand it back to conv_wgrad instead of x
+    Wp = torch.zeros((plan.KH2 * plan.KW2 * plan.Cp, n_out), device=x.device, dtype=bf16)
+    _block_copy(w2d, Wp, plan.descs("w", n_out, x.device, flip))
+    out = torch.empty((n, plan.Hp, plan.Wq, n_out), device=x.device, dtype=bf16)
+    _lib.call("dtf_conv_halo_bf16", P, Wp, out, bias, n, plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out,
+              plan.pad_h2, plan.pad_w2, 0, 1 if relu else 0, _sp())
+    return out
+
+
+def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False, c_used=None, keep=None):
     n, H, W, C = x.shape
     n_out = w2d.shape[1]
     if KH == 1 and KW == 1 and stride > 1:  # strided 1x1: select the sampled pixels, then a dense GEMM
@@ -84,6 +190,12 @@ def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False):
         return gemm(x.view(-1, C), w2d, bias, relu=relu, out_fp32=out_fp32).view(n, H, W, n_out)
     OH, pt = same_pad(H, KH, stride)
     OW, pl = same_pad(W, KW, stride)
+    if USE_HALO and not out_fp32 and (stride > 1 or C % 64 != 0):
+        plan = _pack_plan(H, W, C, C if c_used is None else c_used, KH, KW, stride)
+        if plan is not None:
+            y = _packed_fprop(x, w2d, bias, plan, relu, keep=keep)
+            if y is not None:
+                return y
     out = torch.empty((n, OH, OW, n_out), device=x.device, dtype=torch.float32 if out_fp32 else bf16)
     if stride == 1 and not out_fp32 and USE_HALO and _lib.lib().dtf_conv_halo_supported(H, W, C, KH, KW, n_out):
         # halo-tile kernel: one TMA load per tile, all taps are shifted views of the same shared-memory tile
@@ -107,6 +219,25 @@ def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False):
         return upsample_zero(small, (H, W), stride)
     _, pt = same_pad(H, KH, stride)
     _, pl = same_pad(W, KW, stride)
+    if USE_HALO and bias is None and not relu:
+        if stride == 2:  # space-to-depth: dP = stride-1 data gradient over packed channels, then unpack
+            plan = _pack_plan(H, W, Ci, Ci, KH, KW, 2)
+            if plan is not None and plan.mode == "s2d" and \
+                    _lib.lib().dtf_conv_halo_supported(OH, OW, Co, plan.KH2, plan.KW2, plan.Cp):
+                WpT = torch.zeros((plan.KH2 * plan.KW2 * Co, plan.Cp), device=dy.device, dtype=bf16)
+                _block_copy(w2d_t, WpT, plan.descs("wt", Co, dy.device))
+                dP = torch.empty((n, OH, OW, plan.Cp), device=dy.device, dtype=bf16)
+                _lib.call("dtf_conv_halo_bf16", dy, WpT, dP, None, n, OH, OW, Co, plan.KH2, plan.KW2, plan.Cp,
+                          plan.pad_h2, plan.pad_w2, 1, 0, _sp())
+                dx = torch.empty((n, H, W, Ci), device=dy.device, dtype=bf16)
+                _lib.call("dtf_unpack_s2d", dP, dx, n, H, W, Ci, OH, OW, 0, 0, _sp())
+                return dx
+        elif stride == 1 and Co % 64 != 0:  # few output channels: the gradient is a convolution of dy with flipped taps
+            plan = _pack_plan(H, W, Co, Co, KH, KW, 1, pads=(KH - 1 - pt, KW - 1 - pl))
+            if plan is not None:
+                dx = _packed_fprop(dy, w2d_t, None, plan, False, flip=True)
+                if dx is not None:
+                    return dx
     dx = torch.empty((n, H, W, Ci), device=dy.device, dtype=bf16)
     if stride == 1 and USE_HALO and _lib.lib().dtf_conv_halo_supported(H, W, Co, KH, KW, Ci):
         _lib.call("dtf_conv_halo_bf16", dy, w2d_t, dx, bias, n, H, W, Co, KH, KW, Ci, pt, pl, 1, 1 if relu else 0, _sp())
@@ -116,14 +247,15 @@ def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False):
     return dx
 
 
-def conv_wgrad(x, dy, KH, KW, stride=1, out=None):
-    """dW[KH*KW*Cin, Cout] fp32 accumulated into `out` (zeroed if not given)."""
-    n, H, W, C = x.shape
+def conv_wgrad(x, dy, KH, KW, stride=1, out=None, c_used=None, packed=None, x_shape=None):
+    """dW[KH*KW*Cin, Cout] fp32 accumulated into `out` (zeroed if not given). `packed` (with `x_shape`) is the packed
+    window tensor conv_fprop produced for the same x; x itself may then be None."""
+    n, H, W, C = x.shape if x is not None else x_shape
     _, OH, OW, Co = dy.shape
     _, pt = same_pad(H, KH, stride)
     _, pl = same_pad(W, KW, stride)
     if out is None:
-        out = torch.zeros((KH * KW * C, Co), device=x.device, dtype=torch.float32)
+        out = torch.zeros((KH * KW * C, Co), device=dy.device, dtype=torch.float32)
     if KH == 1 and KW == 1 and stride > 1:
         x = subsample(x, stride)
         stride = 1
@@ -132,6 +264,22 @@ def conv_wgrad(x, dy, KH, KW, stride=1, out=None):
     if stride == 1 and USE_HALO and _lib.lib().dtf_conv_wgrad_halo_supported(H, W, C, KH, KW, Co):
         _lib.call("dtf_conv_wgrad_halo_bf16", x, dy, out, n, H, W, C, KH, KW, Co, pt, pl, _sp())
         return out
+    if (USE_HALO or packed is not None) and (stride > 1 or C % 64 != 0):
+        plan = _pack_plan(H, W, C, C if c_used is None else c_used, KH, KW, stride)
+        halo_ok = plan is not None and _lib.lib().dtf_conv_wgrad_halo_supported(plan.Hp, plan.Wq, plan.Cp, plan.KH2,
+                                                                                plan.KW2, Co)
+        if plan is not None and (halo_ok or packed is not None):
+            P = pack_window(x, plan) if packed is None else packed
+            dWp = torch.zeros((plan.KH2 * plan.KW2 * plan.Cp, Co), device=dy.device, dtype=torch.float32)
+            if halo_ok:
+                _lib.call("dtf_conv_wgrad_halo_bf16", P, dy, dWp, n, plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, Co,
+                          plan.pad_h2, plan.pad_w2, _sp())
+            else:  # small maps: the gather kernel on the packed (stride-1) problem
+                _lib.call("dtf_conv_wgrad_bf16", P, dy, dWp, n, plan.Hp, plan.Wq, plan.Cp, plan.Hp, plan.Wq, plan.KH2,
+                          plan.KW2, Co, 1, plan.pad_h2, plan.pad_w2, _sp())
+            _block_copy(dWp, out, plan.descs("dw", Co, dy.device), fp32=True, accumulate=True)
+            return out
+    assert x is not None, "conv_wgrad: x is required when no packed tensor fits the geometry"
     _lib.call("dtf_conv_wgrad_bf16", x, dy, out, n, H, W, C, OH, OW, KH, KW, Co, stride, pt, pl, _sp())
     return out
 

@@ -85,6 +85,12 @@ int dtf_convert_input(const void* src, void* dst, long long pixels, int C, int C
                       int src_is_u8, void* stream);
 /* y[n,oh,ow,:] = x[n,oh*s,ow*s,:] and its adjoint (zero-filled scatter): a 1x1 stride-s convolution becomes
  * "select pixels, then dense GEMM" instead of an im2col gather. */
+int dtf_pack_window(const void* x, void* P, int n_img, int H, int W, int Cx, int C, int Hp, int Wq, int Cp,
+                    int rp, int kwn, int sx, int cs, int oy, int ox, void* stream);
+int dtf_unpack_s2d(const void* dP, void* dx, int n_img, int H, int W, int C, int Hp, int Wq, int oy, int ox,
+                   void* stream);
+int dtf_block_copy(const void* src, int ld_src, void* dst, int ld_dst, const void* descs, int n_blocks,
+                   int max_elems, int dtype, int accumulate, void* stream);
 int dtf_subsample(const void* x, void* y, int n_img, int H, int W, int C, int OH, int OW, int s, void* stream);
 int dtf_upsample_zero(const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW, int s, void* stream);
 int dtf_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream);

@@ -104,3 +104,37 @@ def test_strided_pixel_select_and_scatter(raw):
     ref = torch.zeros_like(x)
     ref[:, ::2, ::2, :] = y
     assert torch.equal(back, ref)
+
+
+PACKED = [(2, 224, 224, 8, 3, 64, 7, 2), (3, 24, 24, 8, 3, 64, 5, 1), (2, 40, 36, 8, 3, 64, 3, 1), (2, 56, 56, 128, 128, 128, 3, 2),
+          (2, 14, 14, 512, 512, 512, 3, 2), (2, 33, 31, 64, 64, 128, 3, 2), (2, 16, 16, 64, 64, 8, 3, 1)]
+
+
+@pytest.mark.parametrize("n,H,W,Cx,Cu,Co,K,s", PACKED)
+def test_packed_window_convs(raw, n, H, W, Cx, Cu, Co, K, s):
+    """Strided / few-channel convolutions as pack + stride-1 halo convolution (fprop, dgrad, wgrad) vs PyTorch."""
+    x = rnd(n, H, W, Cx)
+    x[..., Cu:] = 0
+    w = (torch.randn(K, K, Cx, Co, device="cuda") * 0.05).to(torch.bfloat16)
+    xf = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wf = w.float().permute(3, 2, 0, 1).requires_grad_(True)
+    OH, pt = raw.same_pad(H, K, s)
+    OW, pl = raw.same_pad(W, K, s)
+    pb = max((OH - 1) * s + K - H, 0) - pt
+    pr = max((OW - 1) * s + K - W, 0) - pl
+    yref = F.conv2d(F.pad(xf, (pl, pr, pt, pb)), wf, stride=s)
+    assert raw._pack_plan(H, W, Cx, Cu, K, K, s) is not None or Co % 64 != 0
+    y = raw.conv_fprop(x, w.reshape(K * K * Cx, Co), None, K, K, s, c_used=Cu)
+    close(y, yref.permute(0, 2, 3, 1))
+    dy = rnd(n, OH, OW, Co)
+    yref.backward(dy.float().permute(0, 3, 1, 2))
+    w_t = w.permute(0, 1, 3, 2).contiguous().reshape(K * K * Co, Cx)
+    close(raw.conv_dgrad(dy, w_t, (H, W), K, K, s), xf.grad.permute(0, 2, 3, 1))
+    dw = raw.conv_wgrad(x, dy, K, K, s, c_used=Cu).view(K, K, Cx, Co)
+    close(dw[:, :, :Cu], wf.grad.permute(2, 3, 1, 0)[:, :, :Cu], 3e-2)
+    raw.USE_PACK = False
+    try:
+        y0 = raw.conv_fprop(x, w.reshape(K * K * Cx, Co), None, K, K, s)
+    finally:
+        raw.USE_PACK = True
+    close(y, y0, 1e-2)
