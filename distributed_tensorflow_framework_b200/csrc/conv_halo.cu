@@ -1191,7 +1191,7 @@ extern "C" int dtf_conv_wgrad_halo_bf16(const void* x, const void* dy, float* dw
   p.b_tx_bytes = p.R * p.Wt * 128;
   p.total_tiles = n_img * p.tiles_per_img;
   const int blocks_xy = (n_out / 64) * (C / 64);
-  int splits = (148 + blocks_xy - 1) / blocks_xy;
+  int splits = 148 / blocks_xy;  // one wave of (1 CTA per SM): never spill a few CTAs into a second wave
   if (splits > p.total_tiles) splits = p.total_tiles;
   if (splits < 1) splits = 1;
   p.tiles_per_split = (p.total_tiles + splits - 1) / splits;

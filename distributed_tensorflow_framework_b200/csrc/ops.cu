@@ -387,12 +387,14 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
   }
 }
 
+static int g_tune[4] = {2, 8, 0, 0};  // [0] column-reduction blocks per SM, [1] row-walking elementwise blocks per SM
+
 static void colreduce_geometry(long long R, int N, int* gx_out, int* gy_out, int* rows_per_block_out) {
   const int cpr = N / 8;
   const int gx = (cpr + 255) / 256;
   const int cprg = cpr < 256 ? cpr : 256;
   const int rpp = 256 / cprg;
-  long long want_blocks = 148 * 2 / gx;
+  long long want_blocks = 148 * g_tune[0] / gx;
   if (want_blocks < 1) want_blocks = 1;
   long long rows_per_block = (R + want_blocks - 1) / want_blocks;
   const long long min_rows = (long long)rpp * 8;
@@ -408,7 +410,7 @@ static void elementwise_geometry(long long R, int N, int* gx_out, int* gy_out, i
   const int gx = (cpr + 255) / 256;
   const int cprg = cpr < 256 ? cpr : 256;
   const int rpp = 256 / cprg;
-  long long want_blocks = 148 * 8 / gx;
+  long long want_blocks = 148 * g_tune[1] / gx;
   if (want_blocks < 1) want_blocks = 1;
   long long rows_per_block = (R + want_blocks - 1) / want_blocks;
   const long long min_rows = (long long)rpp * 4;
@@ -1107,6 +1109,13 @@ extern "C" int dtf_convert_input(const void* src, void* dst, long long pixels, i
     convert_input_kernel<float><<<g, 256, 0, ST(stream)>>>((const float*)src, (__nv_bfloat16*)dst, pixels, C, Cpad,
                                                            scale, shift);
   return DTF_CHECK_LAUNCH();
+}
+// Tuning knobs (see g_tune); returns the previous value. Set before buffers sized by dtf_colreduce_blocks are made.
+extern "C" int dtf_set_tuning(int key, int value) {
+  if (key < 0 || key >= 4) return -1;
+  const int prev = g_tune[key];
+  if (value > 0) g_tune[key] = value;
+  return prev;
 }
 extern "C" int dtf_pack_window(const void* x, void* P, int n_img, int H, int W, int Cx, int C, int Hp, int Wq, int Cp,
                                int rp, int kwn, int sx, int cs, int oy, int ox, void* stream) {

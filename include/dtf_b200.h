@@ -85,6 +85,7 @@ int dtf_convert_input(const void* src, void* dst, long long pixels, int C, int C
                       int src_is_u8, void* stream);
 /* y[n,oh,ow,:] = x[n,oh*s,ow*s,:] and its adjoint (zero-filled scatter): a 1x1 stride-s convolution becomes
  * "select pixels, then dense GEMM" instead of an im2col gather. */
+int dtf_set_tuning(int key, int value);
 int dtf_pack_window(const void* x, void* P, int n_img, int H, int W, int Cx, int C, int Hp, int Wq, int Cp,
                     int rp, int kwn, int sx, int cs, int oy, int ox, void* stream);
 int dtf_unpack_s2d(const void* dP, void* dx, int n_img, int H, int W, int C, int Hp, int Wq, int oy, int ox,
