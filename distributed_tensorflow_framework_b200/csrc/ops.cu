@@ -34,6 +34,29 @@ __device__ __forceinline__ BF8 pack8(const float (&f)[8]) {
 __device__ __forceinline__ BF8 ld8(const __nv_bfloat16* p) { return *reinterpret_cast<const BF8*>(p); }
 __device__ __forceinline__ void st8(__nv_bfloat16* p, const BF8& b) { *reinterpret_cast<BF8*>(p) = b; }
 
+// i = ((n*A + a)*B + b)*cpr + c  ->  (c, b, a, n); 32-bit divisions when the index fits (64-bit ones cost ~100
+// instructions each and used to dominate the NHWC gather / scatter kernels).
+__device__ __forceinline__ void split4(long long i, int cpr, int B, int A, int& c, int& b, int& a, int& n) {
+  if (i <= 0xffffffffLL) {
+    uint32_t u = (uint32_t)i;
+    uint32_t q = u / (uint32_t)cpr;
+    c = (int)(u - q * (uint32_t)cpr);
+    u = q;
+    q = u / (uint32_t)B;
+    b = (int)(u - q * (uint32_t)B);
+    u = q;
+    q = u / (uint32_t)A;
+    a = (int)(u - q * (uint32_t)A);
+    n = (int)q;
+  } else {
+    c = (int)(i % cpr);
+    long long t = i / cpr;
+    b = (int)(t % B);
+    t /= B;
+    a = (int)(t % A);
+    n = (int)(t / A);
+  }
+}
 static inline int grid_for(long long n, int block, int cap = 148 * 16) {
   long long g = (n + block - 1) / block;
   if (g < 1) g = 1;
@@ -126,12 +149,9 @@ __global__ void pack_window_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
   const long long total = (long long)p.n_img * p.Hp * p.Wq * cpr;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const int ch0 = (int)(idx % cpr) * 8;
-    long long t = idx / cpr;
-    const int i = (int)(t % p.Wq);
-    t /= p.Wq;
-    const int j = (int)(t % p.Hp);
-    const int n = (int)(t / p.Hp);
+    int ch0, i, j, n;
+    split4(idx, cpr, p.Wq, p.Hp, ch0, i, j, n);
+    ch0 *= 8;
     BF8 v;
 #pragma unroll
     for (int k = 0; k < 4; ++k) v.v[k] = __floats2bfloat162_rn(0.f, 0.f);
@@ -176,6 +196,42 @@ __global__ void pack_window_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
     st8(P + idx * 8, v);
   }
 }
+// Tap-packing (cs == C, all kwn horizontal taps of rp rows) with the source rows staged compactly in shared memory:
+// P[n, j, i, r*kwn*C + t] = row_r[(sx*i - ox)*C + t], a contiguous window of the C-channel row. One block per (n, j).
+__global__ void __launch_bounds__(256)
+pack_taps_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ P, const PackParams p) {
+  extern __shared__ __nv_bfloat16 rows_sm[];  // [rp][W*C]
+  const int wc = p.W * p.C;
+  const int span = p.kwn * p.C;  // live channels per packed row slot
+  const int cpr = p.Cp / 8;
+  for (int row = blockIdx.x; row < p.n_img * p.Hp; row += gridDim.x) {
+    const int n = row / p.Hp, j = row - n * p.Hp;
+    __syncthreads();
+    for (int e = threadIdx.x; e < p.rp * p.W; e += blockDim.x) {
+      const int r = e / p.W, xx = e - r * p.W;
+      const int y = p.rp * j + r - p.oy;
+      const bool ok = y >= 0 && y < p.H;
+      const __nv_bfloat16* src = x + (((long long)n * p.H + (ok ? y : 0)) * p.W + xx) * p.Cx;
+      for (int c = 0; c < p.C; ++c) rows_sm[r * wc + xx * p.C + c] = ok ? src[c] : __float2bfloat16(0.f);
+    }
+    __syncthreads();
+    __nv_bfloat16* out = P + (long long)row * p.Wq * p.Cp;
+    for (int e = threadIdx.x; e < p.Wq * cpr; e += blockDim.x) {
+      const int i = e / cpr, ch0 = (e - i * cpr) * 8;
+      const int base = (p.sx * i - p.ox) * p.C;
+      BF8 v;
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(&v);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int ch = ch0 + k;
+        const int r = ch >= span ? (ch >= 2 * span ? 2 : 1) : 0;
+        const int pos = base + ch - r * span;
+        o[k] = (r < p.rp && pos >= 0 && pos < wc) ? rows_sm[r * wc + pos] : __float2bfloat16(0.f);
+      }
+      st8(out + (long long)e * 8, v);
+    }
+  }
+}
 // Inverse of the space-to-depth packing (rp = kwn = sx = 2, cs = C): dx[n, y, x, c] = dP[n, j, i, (r*2+q)*C + c].
 __global__ void unpack_s2d_kernel(const __nv_bfloat16* __restrict__ dP, __nv_bfloat16* __restrict__ dx, int n_img,
                                   int H, int W, int C, int Hp, int Wq, int oy, int ox) {
@@ -183,12 +239,9 @@ __global__ void unpack_s2d_kernel(const __nv_bfloat16* __restrict__ dP, __nv_bfl
   const long long total = (long long)n_img * H * W * cpr;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(idx % cpr) * 8;
-    long long t = idx / cpr;
-    const int xx = (int)(t % W);
-    t /= W;
-    const int y = (int)(t % H);
-    const int n = (int)(t / H);
+    int c0, xx, y, n;
+    split4(idx, cpr, W, H, c0, xx, y, n);
+    c0 *= 8;
     const int j = (y + oy) >> 1, r = (y + oy) & 1, i = (xx + ox) >> 1, q = (xx + ox) & 1;
     BF8 v;
 #pragma unroll
@@ -230,12 +283,9 @@ __global__ void subsample_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloa
   const long long total = (long long)n_img * OH * OW * cpr;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cpr) * 8;
-    long long t = i / cpr;
-    const int ow = (int)(t % OW);
-    t /= OW;
-    const int oh = (int)(t % OH);
-    const int n = (int)(t / OH);
+    int c0, ow, oh, n;
+    split4(i, cpr, OW, OH, c0, ow, oh, n);
+    c0 *= 8;
     st8(y + i * 8, ld8(x + (((long long)n * H + oh * s) * W + ow * s) * C + c0));
   }
 }
@@ -245,12 +295,9 @@ __global__ void upsample_zero_kernel(const __nv_bfloat16* __restrict__ dy, __nv_
   const long long total = (long long)n_img * H * W * cpr;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cpr) * 8;
-    long long t = i / cpr;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+    int c0, w, h, n;
+    split4(i, cpr, W, H, c0, w, h, n);
+    c0 *= 8;
     BF8 v;
 #pragma unroll
     for (int j = 0; j < 4; ++j) v.v[j] = __floats2bfloat162_rn(0.f, 0.f);
@@ -647,12 +694,9 @@ __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
   const long long total = (long long)n_img * OH * OW * cpr;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cpr) * 8;
-    long long t = i / cpr;
-    const int ow = (int)(t % OW);
-    t /= OW;
-    const int oh = (int)(t % OH);
-    const int n = (int)(t / OH);
+    int c0, ow, oh, n;
+    split4(i, cpr, OW, OH, c0, ow, oh, n);
+    c0 *= 8;
     float a[8];
     uint32_t am[8];
 #pragma unroll
@@ -707,12 +751,9 @@ __global__ void pool_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_bflo
   const long long total = (long long)n_img * H * W * cpr;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % cpr) * 8;
-    long long t = i / cpr;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+    int c0, w, h, n;
+    split4(i, cpr, W, H, c0, w, h, n);
+    c0 *= 8;
     float g[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) g[j] = 0.f;
@@ -1123,6 +1164,12 @@ extern "C" int dtf_pack_window(const void* x, void* P, int n_img, int H, int W, 
   PackParams p{n_img, H, W, Cx, C, Hp, Wq, Cp, rp, kwn, sx, cs, oy, ox};
   const long long total = (long long)n_img * Hp * Wq * (Cp / 8);
   const bool vec = (cs % 8 == 0) && (C % 8 == 0) && (Cx % 8 == 0);
+  if (!vec && cs == C && rp <= 2 && (size_t)rp * W * C * 2 <= 48 * 1024) {
+    const long long rows = (long long)n_img * Hp;
+    pack_taps_kernel<<<(int)(rows < 148 * 16 ? rows : 148 * 16), 256, (size_t)rp * W * C * 2, ST(stream)>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)P, p);
+    return DTF_CHECK_LAUNCH();
+  }
   if (vec)
     pack_window_kernel<true><<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)P, p);
   else
