@@ -447,6 +447,7 @@ conv_halo_persistent_kernel(const __grid_constant__ CUtensorMap tma_x, const __g
 // [co lanes x pixel columns] is double-buffered in TMEM (2 x 256 columns); the epilogue transposes it through a
 // per-warp staging tile into 64-byte NHWC row segments.
 constexpr int PN_PIX = 256;
+constexpr int PN_MAX_X_STAGES = 4;
 constexpr int PN_STAGE_BYTES = 4 * 32 * 64;  // per warp: 32 pixels x 32 channels bf16
 constexpr int PN_TAB_BYTES = 4 * PN_PIX * 4; // per warp: output pixel index (or -1) of every GEMM column
 
@@ -458,6 +459,7 @@ struct PnParams {
   int G;            // images per tile (whole-image tiles only), else 1
   int img_rows;     // padded-linear rows per packed image: (R+KH-1)*Wp
   int groups;       // pixel tiles: n_img*tiles_per_img (G == 1) or ceil(n_img / G)
+  int xst;          // halo-tile stages (2 or 3)
 };
 
 template <int MW>  // output channels per item: 64 (single 64-channel weight box) or 128
@@ -469,11 +471,11 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
   constexpr int W_BYTES = MW * 64 * 2;
   const uint32_t smem_base = smem_u32(smem);
   const uint32_t x_base = smem_base;
-  const uint32_t w_base = smem_base + A_STAGES * p.a_stage_bytes;
-  const int bar_off = A_STAGES * p.a_stage_bytes + pp.nb * W_BYTES;
+  const uint32_t w_base = smem_base + pp.xst * p.a_stage_bytes;
+  const int bar_off = pp.xst * p.a_stage_bytes + pp.nb * W_BYTES;
   uint64_t* x_full = reinterpret_cast<uint64_t*>(smem + bar_off);
-  uint64_t* x_empty = x_full + A_STAGES;
-  uint64_t* acc_full = x_empty + A_STAGES;  // [2]
+  uint64_t* x_empty = x_full + PN_MAX_X_STAGES;
+  uint64_t* acc_full = x_empty + PN_MAX_X_STAGES;  // [2]
   uint64_t* acc_empty = acc_full + 2;       // [2]
   uint64_t* w_full = acc_empty + 2;         // [MAX_B_STAGES]
   uint64_t* w_empty = w_full + MAX_B_STAGES;
@@ -489,7 +491,7 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
   const bool resident = pp.resident != 0;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < A_STAGES; ++s) {
+    for (int s = 0; s < pp.xst; ++s) {
       mbar_init(&x_full[s], 1);
       mbar_init(&x_empty[s], 1);
     }
@@ -549,7 +551,7 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
           mbar_wait(&x_empty[xs], x_par);
           mbar_arrive_expect_tx(&x_full[xs], p.a_tx_bytes);
           tma_load_4d(x_base + xs * p.a_stage_bytes, &tma_x, &x_full[xs], cb * 64, x0 + p.org_x, y0 + p.org_y, img);
-          if (++xs == A_STAGES) {
+          if (++xs == pp.xst) {
             xs = 0;
             x_par ^= 1;
           }
@@ -623,7 +625,7 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
             if (!resident) w_par ^= 1;
           }
         }
-        if (++xs == A_STAGES) {
+        if (++xs == pp.xst) {
           xs = 0;
           x_par ^= 1;
         }
@@ -1003,19 +1005,24 @@ static bool pn_setup(int n_img, int H, int W, int C, int KH, int KW, int n_out, 
   const long long items = (long long)pp.groups * pp.tiles_co;
   if (items > 0x7fffffffLL || (long long)n_img * H * W > 0x7fffffffLL) return false;
   pp.total_items = (int)items;
-  const int fixed = 1024 + A_STAGES * p.a_stage_bytes + 1024 + PN_STAGE_BYTES + PN_TAB_BYTES;
-  const int avail = 227 * 1024 - fixed;
   const int total_w = KH * KW * (C >> 6);
-  if (pp.tiles_co == 1 && total_w <= MAX_B_STAGES && total_w * w_bytes <= avail) {
-    pp.resident = 1;
-    pp.nb = total_w;
-  } else {
-    pp.nb = avail / w_bytes;
-    if (pp.nb > 8) pp.nb = 8;
-    if (pp.nb < 2) return false;
+  // two halo stages: a third one measured slower (it shrinks the weight ring, which matters more)
+  for (pp.xst = 2; pp.xst >= 2; --pp.xst) {
+    const int fixed = 1024 + pp.xst * p.a_stage_bytes + 1024 + PN_STAGE_BYTES + PN_TAB_BYTES;
+    const int avail = 227 * 1024 - fixed;
+    pp.resident = 0;
+    if (pp.tiles_co == 1 && total_w <= MAX_B_STAGES && total_w * w_bytes <= avail) {
+      pp.resident = 1;
+      pp.nb = total_w;
+    } else {
+      pp.nb = avail / w_bytes;
+      if (pp.nb > 8) pp.nb = 8;
+      if (pp.nb < (pp.xst == 3 ? 4 : 2)) continue;
+    }
+    h->smem = fixed + pp.nb * w_bytes;
+    return true;
   }
-  h->smem = fixed + pp.nb * w_bytes;
-  return true;
+  return false;
 }
 
 template <int MW>
