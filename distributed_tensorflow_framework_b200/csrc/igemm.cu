@@ -49,6 +49,9 @@ struct IgemmParams {
   int out_fp32;
   int atomic;
   int kb_per_split;
+  // optional bf16 [M, N] (row stride ldc) added to the result before the ReLU: residual inputs, and the second
+  // gradient of a tensor with two consumers (so autograd never has to sum them in a separate pass)
+  const __nv_bfloat16* addend;
 };
 
 template <int BN, int STAGES>
@@ -87,6 +90,11 @@ __device__ __forceinline__ void igemm_epilogue(const IgemmParams& p, uint32_t tm
 #pragma unroll
         for (int j = 0; j < 32; ++j)
           if (n0 + j < p.N) f[j] += __ldg(p.bias + n0 + j);
+      }
+      if (p.addend != nullptr) {
+        const __nv_bfloat16* ad = p.addend + (size_t)m * p.ldc + n0;
+        for (int j = 0; j < 32; ++j)
+          if (n0 + j < p.N) f[j] += __bfloat162float(ad[j]);
       }
       if (p.relu) {
 #pragma unroll
@@ -147,13 +155,28 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
   constexpr int ROWB = COLS * 2;        // bytes per staged row
   constexpr int CPR = ROWB / 16;        // 16-byte chunks per row (8 or 4)
   constexpr int RPI = 32 / CPR;         // rows written per store instruction
+  constexpr int NIT = 32 / RPI;         // store instructions per staged group
   const int lane = threadIdx.x & 31;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
   const int row0 = tile_m * BLOCK_M + warp * 32;
   __nv_bfloat16* outp = reinterpret_cast<__nv_bfloat16*>(p.out);
+  const int chunk = lane & (CPR - 1);
+  const bool has_add = p.addend != nullptr;
 #pragma unroll 1
   for (int cg = 0; cg < BN / COLS; ++cg) {
     const int n0 = tile_n * BN + cg * COLS;
+    const int n = n0 + chunk * 8;
+    // the addend pieces of this group are requested first, all at once, so their latency overlaps the TMEM load
+    // and the staging below (a load issued between the stores could not be hoisted: out and addend may alias)
+    uint4 av[NIT];
+    if (has_add) {
+#pragma unroll
+      for (int i = 0; i < NIT; ++i) {
+        const int m = row0 + i * RPI + lane / CPR;
+        av[i] = (m < p.M && n + 8 <= p.N) ? __ldg(reinterpret_cast<const uint4*>(p.addend + (size_t)m * p.ldc + n))
+                                          : make_uint4(0, 0, 0, 0);
+      }
+    }
 #pragma unroll
     for (int h = 0; h < COLS / 32; ++h) {
       uint32_t v[32];
@@ -167,7 +190,7 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
         for (int j = 0; j < 32; ++j)
           if (n0 + h * 32 + j < p.N) f[j] += __ldg(p.bias + n0 + h * 32 + j);
       }
-      if (p.relu) {
+      if (p.relu && !has_add) {  // with an addend the ReLU follows the add, in the write-out below
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
       }
@@ -178,22 +201,48 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
         q.y = pack_bf16x2(f[c * 8 + 2], f[c * 8 + 3]);
         q.z = pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]);
         q.w = pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]);
-        const int chunk = h * 4 + c;
-        *reinterpret_cast<uint4*>(stage + lane * ROWB + ((chunk ^ (lane & (CPR - 1))) << 4)) = q;
+        const int ch = h * 4 + c;
+        *reinterpret_cast<uint4*>(stage + lane * ROWB + ((ch ^ (lane & (CPR - 1))) << 4)) = q;
       }
     }
     __syncwarp();
-    const int chunk = lane & (CPR - 1);
 #pragma unroll
-    for (int i = 0; i < 32 / RPI; ++i) {
+    for (int i = 0; i < NIT; ++i) {
       const int r = i * RPI + lane / CPR;
-      const uint4 q = *reinterpret_cast<const uint4*>(stage + r * ROWB + ((chunk ^ (r & (CPR - 1))) << 4));
+      uint4 q = *reinterpret_cast<const uint4*>(stage + r * ROWB + ((chunk ^ (r & (CPR - 1))) << 4));
       const int m = row0 + r;
-      const int n = n0 + chunk * 8;
-      if (m < p.M && n + 8 <= p.N) *reinterpret_cast<uint4*>(outp + (size_t)m * p.ldc + n) = q;
+      if (m < p.M && n + 8 <= p.N) {
+        if (has_add) {  // add in fp32, ReLU, round once more
+          const __nv_bfloat162* qa = reinterpret_cast<const __nv_bfloat162*>(&q);
+          const __nv_bfloat162* aa = reinterpret_cast<const __nv_bfloat162*>(&av[i]);
+          uint32_t o[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 x = __bfloat1622float2(qa[e]), y = __bfloat1622float2(aa[e]);
+            float s0 = x.x + y.x, s1 = x.y + y.y;
+            if (p.relu) {
+              s0 = fmaxf(s0, 0.f);
+              s1 = fmaxf(s1, 0.f);
+            }
+            o[e] = pack_bf16x2(s0, s1);
+          }
+          q = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+        *reinterpret_cast<uint4*>(outp + (size_t)m * p.ldc + n) = q;
+      }
     }
     __syncwarp();
   }
+}
+
+// Pull the addend rows of a tile towards L2 ahead of the epilogue that will read them (one 128-byte line per call).
+template <int BN>
+__device__ __forceinline__ void prefetch_addend_tile(const IgemmParams& p, int tile_m, int tile_n) {
+  const int m = tile_m * BLOCK_M + threadIdx.x;  // epilogue threads 0..127 = tile rows
+  if (m >= p.M) return;
+  const char* row = reinterpret_cast<const char*>(p.addend + (size_t)m * p.ldc + (size_t)tile_n * BN);
+  const int bytes = min(BN, p.N - tile_n * BN) * 2;
+  for (int b = 0; b < bytes; b += 128) asm volatile("prefetch.global.L2 [%0];\n" ::"l"(row + b));
 }
 
 // K-AG-GEMM support: the B operand (weights) is sharded over the ranks of a parameter-server group and is NOT
@@ -531,7 +580,8 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
   constexpr bool kAMn = (AMODE == A_TMA_MN);
   // bf16 output with 16-byte aligned rows and whole 8-column groups: use the coalescing epilogue
   const bool staged = !p.atomic && !p.out_fp32 && (p.ldc % 8 == 0) && (p.N % 8 == 0) &&
-                      ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0);
+                      ((reinterpret_cast<uintptr_t>(p.out) & 15) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(p.addend) & 15) == 0);
   const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
   const int total_tiles = tiles_m * tiles_n * splits;
 
@@ -634,6 +684,15 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
       int tile_m, tile_n, kb0, kb1;
       decode(t, tile_m, tile_n, kb0, kb1);
       const int buf = lt & 1;
+      if (p.addend != nullptr) {  // this tile's rows (first tile only) and the next tile's, one tile period ahead
+        if (lt == 0) prefetch_addend_tile<BN>(p, tile_m, tile_n);
+        const int tn = t + gridDim.x;
+        if (tn < total_tiles) {
+          int m2, n2, k0, k1;
+          decode(tn, m2, n2, k0, k1);
+          prefetch_addend_tile<BN>(p, m2, n2);
+        }
+      }
       mbar_wait(&acc_full[buf], (lt >> 1) & 1);
       tc_fence_after();
       if (staged)
@@ -695,7 +754,7 @@ igemm_ag_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
 // C[M,N] = act(A*B + bias); a_t: A stored [K,M]; b_t: B stored [N,K]. One thread per output element.
 __global__ void gemm_simt_kernel(const __nv_bfloat16* A, const __nv_bfloat16* B, void* C, const float* bias, int M,
                                  int N, int K, int lda, int ldb, int ldc, int a_t, int b_t, int relu, int out_fp32,
-                                 int accumulate) {
+                                 int accumulate, const __nv_bfloat16* addend = nullptr) {
   const int n = blockIdx.x * blockDim.x + threadIdx.x;
   const int m = blockIdx.y * blockDim.y + threadIdx.y;
   if (m >= M || n >= N) return;
@@ -706,6 +765,7 @@ __global__ void gemm_simt_kernel(const __nv_bfloat16* A, const __nv_bfloat16* B,
     acc = fmaf(a, b, acc);
   }
   if (bias) acc += bias[n];
+  if (addend) acc += __bfloat162float(addend[(size_t)m * ldc + n]);
   if (relu) acc = fmaxf(acc, 0.f);
   if (out_fp32) {
     float* o = reinterpret_cast<float*>(C) + (size_t)m * ldc + n;
@@ -815,17 +875,26 @@ extern "C" int dtf_set_persistent_gemm(int on) {
 
 // flags
 //   bit0 relu, bit1 out_fp32, bit2 atomic accumulate into fp32 out (split-K allowed), bit3 A is stored [K,M]
+extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend, int M,
+                                int N, int K, int lda, int ldb, int ldc, int flags, void* stream_);
 extern "C" int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda,
                              int ldb, int ldc, int flags, void* stream_) {
+  return dtf_gemm_bf16_ex(A, B, C, bias, nullptr, M, N, K, lda, ldb, ldc, flags, stream_);
+}
+// Same with `addend` (bf16 [M, N], row stride ldc, may be NULL): C = act(A*B + bias + addend); bf16 outputs only.
+extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend, int M,
+                                int N, int K, int lda, int ldb, int ldc, int flags, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   const int relu = flags & 1, out_fp32 = (flags >> 1) & 1, atomic = (flags >> 2) & 1, a_t = (flags >> 3) & 1;
   if (M <= 0 || N <= 0 || K <= 0) return DTF_ERR_ARG;
+  if (addend != nullptr && (out_fp32 || atomic)) return DTF_ERR_UNSUPPORTED;
   const bool tc_ok = aligned16(A) && aligned16(B) && (lda % 8 == 0) && (ldb % 8 == 0) && (M * (long long)N >= 4096);
   if (!tc_ok) {
     dim3 block(32, 8), grid((N + 31) / 32, (M + 7) / 8);
     gemm_simt_kernel<<<grid, block, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(A),
                                                  reinterpret_cast<const __nv_bfloat16*>(B), C, bias, M, N, K, lda, ldb,
-                                                 ldc, a_t, 0, relu, out_fp32 | atomic, atomic);
+                                                 ldc, a_t, 0, relu, out_fp32 | atomic, atomic,
+                                                 reinterpret_cast<const __nv_bfloat16*>(addend));
     return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
   }
   CUtensorMap ta, tb;
@@ -838,6 +907,7 @@ extern "C" int dtf_gemm_bf16(const void* A, const void* B, void* C, const float*
   IgemmParams p{};
   p.M = M; p.N = N; p.K = K;
   p.out = C; p.ldc = ldc; p.bias = bias; p.relu = relu; p.out_fp32 = out_fp32; p.atomic = atomic;
+  p.addend = reinterpret_cast<const __nv_bfloat16*>(addend);
   const int total_kb = (K + BLOCK_K - 1) / BLOCK_K;
   const int splits = pick_splits(M, N, total_kb, atomic);
   p.kb_per_split = (total_kb + splits - 1) / splits;

@@ -38,7 +38,7 @@ class ConvFn(torch.autograd.Function):
     """conv2d(SAME) + bias (+ ReLU) on the implicit-GEMM tcgen05 kernel."""
 
     @staticmethod
-    def forward(ctx, x, w_shadow, b_shadow, wvar, bvar, stride, relu):
+    def forward(ctx, x, w_shadow, b_shadow, wvar, bvar, stride, relu, fork=False):
         KH, KW, Ci, Co = wvar.store_shape
         w2d = w_shadow.detach().view(KH * KW * Ci, Co)
         bias = bvar.master if bvar is not None else None
@@ -50,13 +50,21 @@ class ConvFn(torch.autograd.Function):
         ctx.x_shape = tuple(x.shape)
         ctx.save_for_backward(keep["packed"] if ctx.packed else x, y if relu else None)
         ctx.x_needs_grad = x.requires_grad
+        ctx.fork = fork
+        if fork:
+            # second output: x itself, for the other consumer of x (the shortcut branch). Its gradient comes back
+            # into THIS backward and is summed inside the data-gradient kernel, so autograd never runs a separate
+            # accumulation pass over the block input.
+            return y, x.view_as(x)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, d_alias=None):
         x, y = ctx.saved_tensors
         wvar, bvar = ctx.wvar, ctx.bvar
         KH, KW, Ci, Co = wvar.store_shape
+        if dy is None:  # only the forwarded copy of x was used
+            return d_alias, None, None, None, None, None, None, None
         dy = dy.contiguous()
         n, OH, OW, _ = dy.shape
         dy2 = dy.view(-1, Co)
@@ -80,12 +88,14 @@ class ConvFn(torch.autograd.Function):
             _ready(bvar)
         dx = None
         if ctx.x_needs_grad:
-            dx = raw.conv_dgrad(dz, wvar.shadow_t.view(KH * KW * Co, Ci), ctx.x_shape[1:3], KH, KW, ctx.stride)
-        return dx, None, None, None, None, None, None
+            dx = raw.conv_dgrad(dz, wvar.shadow_t.view(KH * KW * Co, Ci), ctx.x_shape[1:3], KH, KW, ctx.stride,
+                                addend=d_alias)
+        return dx, None, None, None, None, None, None, None
 
 
-def conv2d(x, wvar, bvar, stride=1, relu=False):
-    return ConvFn.apply(x, wvar.shadow, bvar.shadow if bvar is not None else None, wvar, bvar, stride, relu)
+def conv2d(x, wvar, bvar, stride=1, relu=False, fork=False):
+    """`fork=True` returns (y, x'): x' is x for a second consumer whose gradient is summed inside this op's backward."""
+    return ConvFn.apply(x, wvar.shadow, bvar.shadow if bvar is not None else None, wvar, bvar, stride, relu, fork)
 
 
 class DeconvFn(torch.autograd.Function):

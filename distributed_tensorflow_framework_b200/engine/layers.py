@@ -94,15 +94,20 @@ def _prep_cuda_input(x, cin_store):
     return x.contiguous()
 
 
-def _conv_impl(x, w, b, stride, relu):
+def _conv_impl(x, w, b, stride, relu, fork=False):
     sh, sw = _stride_hw(stride)
     KH, KW = w.shape[0], w.shape[1]
     if x.is_cuda:
         assert sh == sw, "anisotropic strides are not supported on the CUDA path"
         x = _prep_cuda_input(x, w.store_shape[2])
+        if fork:
+            y, x_fwd = Fn.conv2d(x, w, b, sh, relu, fork=True)
+            return (y if w.store_shape[3] == w.shape[3] else y[..., :w.shape[3]]), x_fwd
         y = Fn.conv2d(x, w, b, sh, relu)
         # an output-channel count that is not a multiple of 8 is stored padded (zero filters); slice it off
         return y if w.store_shape[3] == w.shape[3] else y[..., :w.shape[3]]
+    if fork:
+        return _conv_impl(x, w, b, stride, relu), x
     xn = x.float().permute(0, 3, 1, 2)
     xn = F.pad(xn, _same_pad_nchw(xn, (KH, KW), (sh, sw)))
     y = F.conv2d(xn, w.master.permute(3, 2, 0, 1), b.master if b is not None else None, stride=(sh, sw))
@@ -127,16 +132,19 @@ def conv_eval(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stri
     return conv(layer_name, x, in_channels, out_channels, kernel_size, stride)
 
 
-def conv_nonacti(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1], use_bias=True):
+def conv_nonacti(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1], use_bias=True,
+                 fork_input=False):
     """conv2d + bias, Xavier init, variables `weights_nonacti` / `biases_nonacti` -- distribute_tools.py:93-106.
-    `use_bias=False` (extension) drops the bias for convolutions that feed a batch norm, where it is redundant."""
+    `use_bias=False` (extension) drops the bias for convolutions that feed a batch norm, where it is redundant.
+    `fork_input=True` (extension) returns (y, x'): feed x' to the other consumer of x (a residual shortcut) and the
+    two gradients of x are summed inside this layer's data-gradient kernel instead of by a separate pass."""
     with variable_scope(layer_name):
         shape = [kernel_size[0], kernel_size[1], in_channels, out_channels]
         store = [kernel_size[0], kernel_size[1], _pad8(in_channels), _pad8(out_channels)] if x.is_cuda else None
         w = _get("weights_nonacti", shape, XavierInitializer(), kind="conv_w", store_shape=store)
         b = _get("biases_nonacti", [out_channels], ConstantInitializer(0.0), kind="bias",
                  store_shape=[_pad8(out_channels)] if x.is_cuda else None) if use_bias else None
-        return _conv_impl(x, w, b, stride, relu=False)
+        return _conv_impl(x, w, b, stride, relu=False, fork=fork_input)
 
 
 def conv_nonacti_eval(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1]):

@@ -7,27 +7,29 @@ from ..plugins.input import SyntheticDataLoader
 from ..plugins.model import Model
 
 
-def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None):
-    y = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1], use_bias=False)
+def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None, fork_input=False):
+    y = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1], use_bias=False,
+                       fork_input=fork_input)
+    if fork_input:  # (conv output, x forwarded for the shortcut branch)
+        return L.batch_norm_channel(name + "/bn", y[0], relu=relu, residual=residual), y[1]
     return L.batch_norm_channel(name + "/bn", y, relu=relu, residual=residual)
 
 
 def _basic_block(name, x, cin, cout, stride):
     with variable_scope(name):
-        shortcut = x
+        # conv1 forwards x to the shortcut branch so that both gradients of x meet inside conv1's backward
+        y, shortcut = _conv_bn("conv1", x, cin, cout, 3, stride, fork_input=True)
         if stride != 1 or cin != cout:
-            shortcut = _conv_bn("shortcut", x, cin, cout, 1, stride, relu=False)
-        y = _conv_bn("conv1", x, cin, cout, 3, stride)
+            shortcut = _conv_bn("shortcut", shortcut, cin, cout, 1, stride, relu=False)
         return _conv_bn("conv2", y, cout, cout, 3, 1, relu=True, residual=shortcut)
 
 
 def _bottleneck(name, x, cin, mid, stride):
     cout = mid * 4
     with variable_scope(name):
-        shortcut = x
+        y, shortcut = _conv_bn("conv1", x, cin, mid, 1, 1, fork_input=True)
         if stride != 1 or cin != cout:
-            shortcut = _conv_bn("shortcut", x, cin, cout, 1, stride, relu=False)
-        y = _conv_bn("conv1", x, cin, mid, 1, 1)
+            shortcut = _conv_bn("shortcut", shortcut, cin, cout, 1, stride, relu=False)
         y = _conv_bn("conv2", y, mid, mid, 3, stride)
         return _conv_bn("conv3", y, mid, cout, 1, 1, relu=True, residual=shortcut)
 

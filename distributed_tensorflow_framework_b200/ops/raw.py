@@ -23,7 +23,7 @@ def _sp():
     return _lib.stream_ptr()
 
 
-def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=None, accumulate=False):
+def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=None, accumulate=False, addend=None):
     """act(A @ B + bias). a: [M,K] (or [K,M] if a_transposed), b: [K,N], both bf16 row-major."""
     if a_transposed:
         K, M = a.shape
@@ -35,7 +35,9 @@ def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=No
         out = torch.empty((M, N), device=a.device, dtype=torch.float32 if (out_fp32 or accumulate) else bf16)
     flags = (1 if relu else 0) | (2 if (out_fp32 or accumulate) else 0) | (4 if accumulate else 0) | \
             (8 if a_transposed else 0)
-    _lib.call("dtf_gemm_bf16", a, b, out, bias, M, N, K, a.stride(0), b.stride(0), out.stride(0), flags, _sp())
+    if addend is not None:  # act(A @ B + bias + addend), addend bf16 [M, N] laid out like `out`
+        assert addend.dtype == bf16 and addend.shape == out.shape and addend.stride(0) == out.stride(0)
+    _lib.call("dtf_gemm_bf16_ex", a, b, out, bias, addend, M, N, K, a.stride(0), b.stride(0), out.stride(0), flags, _sp())
     return out
 
 
@@ -207,11 +209,16 @@ def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False, c_use
     return out
 
 
-def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False):
-    """Data gradient of the SAME conv (H,W)->dy spatial; also the forward of conv2d_transpose. w2d_t: [KH*KW*Cout, Cin]."""
+def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False, addend=None):
+    """Data gradient of the SAME conv (H,W)->dy spatial; also the forward of conv2d_transpose. w2d_t: [KH*KW*Cout, Cin].
+    `addend` [n, H, W, Cin] is summed into the result: inside the GEMM epilogue for 1x1 layers, by the add kernel else."""
     n, OH, OW, Co = dy.shape
     H, W = in_hw
     Ci = w2d_t.shape[1]
+    if addend is not None:
+        if KH == 1 and KW == 1 and stride == 1:
+            return gemm(dy.view(-1, Co), w2d_t, bias, relu=relu, addend=addend.reshape(-1, Ci)).view(n, H, W, Ci)
+        return add(conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride, bias, relu), addend.contiguous())
     if KH == 1 and KW == 1 and stride == 1:
         return gemm(dy.view(-1, Co), w2d_t, bias, relu=relu).view(n, H, W, Ci)
     if KH == 1 and KW == 1 and stride > 1 and bias is None and not relu:

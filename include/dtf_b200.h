@@ -33,6 +33,8 @@ extern "C" {
  * Replaces tf.matmul + bias_add + relu of FC_layer (distribute_tools.py:190-208) and its gradients. */
 int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
                   int ldc, int flags, void* stream);
+int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend, int M, int N,
+                     int K, int lda, int ldb, int ldc, int flags, void* stream);
 
 /* Dense GEMMs run a persistent kernel (tile loop per CTA, smem ring kept full across tiles, accumulator double
  * buffered in TMEM so the epilogue overlaps the next tile). bit0 of `on`: persistent kernel (0 = one tile per CTA);

@@ -138,3 +138,30 @@ def test_packed_window_convs(raw, n, H, W, Cx, Cu, Co, K, s):
     finally:
         raw.USE_PACK = True
     close(y, y0, 1e-2)
+
+
+@pytest.mark.parametrize("M,N,K", [(4096, 256, 64), (1000, 72, 136), (128, 512, 1024)])
+def test_gemm_addend(raw, M, N, K):
+    """act(A @ B + bias + addend): the addend is read in the (staged) epilogue of the tcgen05 GEMM."""
+    a, b, add, bias = rnd(M, K), rnd(K, N), rnd(M, N), torch.randn(N, device="cuda")
+    ref = a.float() @ b.float() + add.float()
+    close(raw.gemm(a, b, addend=add), ref)
+    close(raw.gemm(a, b, bias, relu=True, addend=add), torch.relu(ref + bias))
+
+
+def test_conv_fork_sums_both_gradients_of_x():
+    """conv2d(fork=True) forwards x to a second consumer; its backward adds that consumer's gradient inside the
+    data-gradient kernel (1x1: GEMM epilogue; 3x3: add kernel). Compared with plain autograd accumulation."""
+    from distributed_tensorflow_framework_b200.engine import functional as Fn, variables as V
+    from distributed_tensorflow_framework_b200.engine.variables import XavierInitializer
+    for k in (1, 3):
+        store = V.VariableStore(device="cuda")
+        w = store.get_variable("w%d" % k, [k, k, 64, 128], XavierInitializer(), kind="conv_w")
+        x = rnd(2, 16, 16, 64).requires_grad_(True)
+        g1, g2 = rnd(2, 16, 16, 128), rnd(2, 16, 16, 64)
+        y, xf = Fn.conv2d(x, w, None, 1, False, fork=True)
+        (y * g1).sum().backward(retain_graph=True, inputs=[x])
+        gx_main = x.grad.clone()
+        x.grad = None
+        ((y * g1).sum() + (xf * g2).sum()).backward(inputs=[x])
+        close(x.grad, gx_main.float() + g2.float())
