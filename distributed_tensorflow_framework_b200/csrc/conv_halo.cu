@@ -40,6 +40,7 @@ struct Params {
   void* out;
   const float* bias;
   int relu;
+  float* stats;  // pixels-as-N kernel: [pixel tiles][2][n_out] per-tile column sums / sums of squares (batch norm)
 };
 
 template <int BN, int B_STAGES>
@@ -462,7 +463,9 @@ struct PnParams {
   int xst;          // halo-tile stages (2 or 3)
 };
 
-template <int MW>  // output channels per item: 64 (single 64-channel weight box) or 128
+// MW: output channels per item, 64 (single 64-channel weight box) or 128. STATS: also emit per-tile batch-norm
+// statistics (a separate instantiation: it needs the chunk loop fully unrolled, which costs the plain kernel speed).
+template <int MW, bool STATS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constant__ CUtensorMap tma_w,
                     const Params p, const PnParams pp) {
@@ -645,8 +648,9 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
       decode(item, tile_co, img, y0, x0);
       const int co = tile_co * MW + warp * 32 + lane;
       const bool warp_live = (warp * 32 < MW) && (tile_co * MW + warp * 32 < p.n_out);
+      uint32_t vmask[STATS ? PN_PIX / 32 : 1];  // validity of the 32 pixels of every chunk (warp-uniform)
       if (warp_live) {
-#pragma unroll 1
+#pragma unroll(STATS ? PN_PIX / 32 : 1)
         for (int q = 0; q < PN_PIX / 32; ++q) {
           const int m = q * 32 + lane;
           const int g = m / pp.img_rows;
@@ -656,14 +660,16 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
           const int x = x0 + xx, y = y0 + ry, im = img + g;
           const bool valid = (g < pp.G) && (im < p.n_img) && (ry < p.R) && (xx < p.Wt) && (x < p.W) && (y < p.H);
           tab[m] = valid ? (int)(((long long)im * p.H + y) * p.W + x) : -1;
+          if (STATS) vmask[STATS ? q : 0] = __ballot_sync(0xffffffffu, valid);
         }
         __syncwarp();
       }
+      float st_sum = 0.f, st_sq = 0.f;
       const float bias = (warp_live && p.bias != nullptr && co < p.n_out) ? __ldg(p.bias + co) : 0.f;
       mbar_wait(&acc_full[buf], acc_par);
       tc_fence_after();
       if (warp_live) {
-#pragma unroll 1
+#pragma unroll(STATS ? PN_PIX / 32 : 1)
         for (int cc = 0; cc < PN_PIX / 32; ++cc) {
           if (cc * 32 >= m_limit) break;
           uint32_t v[32];
@@ -673,6 +679,10 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             float f = __uint_as_float(v[j]) + bias;
+            if (STATS && ((vmask[STATS ? cc : 0] >> j) & 1u)) {  // this thread's channel, valid pixels only
+              st_sum += f;
+              st_sq = fmaf(f, f, st_sq);
+            }
             if (p.relu) f = fmaxf(f, 0.f);
             st[j * 32] = __float2bfloat16(f);  // stage[pixel j][channel lane]
           }
@@ -694,6 +704,11 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
       if ((buf ^= 1) == 0) acc_par ^= 1;
+      if (STATS && warp_live && co < p.n_out) {
+        float* o = p.stats + (size_t)(item / pp.tiles_co) * 2 * p.n_out + co;
+        o[0] = st_sum;
+        o[p.n_out] = st_sq;
+      }
     }
   }
   tc_fence_before();
@@ -1025,9 +1040,9 @@ static bool pn_setup(int n_img, int H, int W, int C, int KH, int KW, int n_out, 
   return false;
 }
 
-template <int MW>
+template <int MW, bool STATS>
 static int launch_pn(const CUtensorMap& tx, const CUtensorMap& tw, const PnHost& h, cudaStream_t stream) {
-  auto kern = conv_halo_pn_kernel<MW>;
+  auto kern = conv_halo_pn_kernel<MW, STATS>;
   static int attr[64] = {};
   static int sms[64] = {};
   int dev = 0;
@@ -1088,9 +1103,28 @@ extern "C" int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int 
 // src: x (fprop) or dy (mirror = 1, data gradient) [n_img, H, W, C]; W2d: [KH*KW*C, n_out] row-major bf16 (HWIO for
 // fprop, per-tap transposed filters for the gradient); out [n_img, H, W, n_out] bf16. SAME padding, stride 1.
 // flags: bit0 relu, bit8 use the descriptor base-offset field for the shifted tap views.
+extern "C" int dtf_conv_halo_bf16_ex(const void* src, const void* W2d, void* out, const float* bias, float* stats,
+                                     int n_img, int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w,
+                                     int mirror, int flags, void* stream_);
 extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H,
                                   int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags,
                                   void* stream_) {
+  return dtf_conv_halo_bf16_ex(src, W2d, out, bias, nullptr, n_img, H, W, C, KH, KW, n_out, pad_h, pad_w, mirror, flags,
+                               stream_);
+}
+// Rows of the per-tile statistics buffer [rows][2][n_out] that dtf_conv_halo_bf16_ex fills (0: this geometry does
+// not run on the pixels-as-N kernel and cannot emit statistics).
+extern "C" int dtf_conv_halo_stats_rows(int n_img, int H, int W, int C, int KH, int KW, int n_out) {
+  if (KH > 7 || KW > 7 || dtf::halo::g_halo_persistent < 2) return 0;
+  dtf::halo::PnHost h;
+  if (!dtf::halo::pn_setup(n_img, H, W, C, KH, KW, n_out, 0, 0, 0, &h)) return 0;
+  return h.pp.groups;
+}
+// stats (optional): per pixel tile, the column sums and sums of squares of the fp32 results (bias included, before
+// the ReLU) -- the batch-norm statistics of the layer's output without another pass over it.
+extern "C" int dtf_conv_halo_bf16_ex(const void* src, const void* W2d, void* out, const float* bias, float* stats,
+                                     int n_img, int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w,
+                                     int mirror, int flags, void* stream_) {
   using namespace dtf::halo;
   if (KH > 7 || KW > 7) return DTF_ERR_UNSUPPORTED;
   EncodeTiledFn fn = encode_fn();
@@ -1098,7 +1132,7 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PnHost h;
   if (g_halo_persistent >= 2 && pn_setup(n_img, H, W, C, KH, KW, n_out, pad_h, pad_w, mirror, &h)) {
-    h.p.out = out; h.p.bias = bias; h.p.relu = flags & 1;
+    h.p.out = out; h.p.bias = bias; h.p.relu = flags & 1; h.p.stats = stats;
     CUtensorMap tx, tw;
     cuuint32_t es4[4] = {1, 1, 1, 1};
     cuuint64_t xd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)n_img};
@@ -1114,9 +1148,10 @@ extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, c
            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return DTF_ERR_TENSORMAP;
-    return n_out <= 64 ? launch_pn<64>(tx, tw, h, stream) : launch_pn<128>(tx, tw, h, stream);
+    if (stats != nullptr) return n_out <= 64 ? launch_pn<64, true>(tx, tw, h, stream) : launch_pn<128, true>(tx, tw, h, stream);
+    return n_out <= 64 ? launch_pn<64, false>(tx, tw, h, stream) : launch_pn<128, false>(tx, tw, h, stream);
   }
-  if (!legacy_halo_supported(H, W, C, KH, KW, n_out)) return DTF_ERR_UNSUPPORTED;
+  if (stats != nullptr || !legacy_halo_supported(H, W, C, KH, KW, n_out)) return DTF_ERR_UNSUPPORTED;
   Params p{};
   p.n_img = n_img; p.H = H; p.W = W; p.C = C; p.n_out = n_out; p.KH = KH; p.KW = KW;
   halo_plan(H, W, KH, KW, &p.Wt, &p.R);

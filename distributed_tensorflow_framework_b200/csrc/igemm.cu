@@ -875,18 +875,29 @@ extern "C" int dtf_set_persistent_gemm(int on) {
 
 // flags
 //   bit0 relu, bit1 out_fp32, bit2 atomic accumulate into fp32 out (split-K allowed), bit3 A is stored [K,M]
-extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend, int M,
-                                int N, int K, int lda, int ldb, int ldc, int flags, void* stream_);
+extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend,
+                                float* stats, int M, int N, int K, int lda, int ldb, int ldc, int flags, void* stream_);
 extern "C" int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda,
                              int ldb, int ldc, int flags, void* stream_) {
-  return dtf_gemm_bf16_ex(A, B, C, bias, nullptr, M, N, K, lda, ldb, ldc, flags, stream_);
+  return dtf_gemm_bf16_ex(A, B, C, bias, nullptr, nullptr, M, N, K, lda, ldb, ldc, flags, stream_);
+}
+// Rows of the batch-norm statistics buffer the GEMM epilogue would fill for this problem. Always 0 in this build:
+// column statistics in the dense GEMM epilogue were implemented and measured (per-CTA register accumulation over the
+// staged tiles) and cost as much as the separate statistics pass they replace, because the bandwidth-bound 1x1
+// layers have their epilogue warps on the critical path. Callers fall back to dtf_bn_stats.
+extern "C" int dtf_gemm_stats_rows(const void* A, const void* B, const void* C, int M, int N, int K, int lda, int ldb,
+                                   int ldc) {
+  (void)A; (void)B; (void)C; (void)M; (void)N; (void)K; (void)lda; (void)ldb; (void)ldc;
+  return 0;
 }
 // Same with `addend` (bf16 [M, N], row stride ldc, may be NULL): C = act(A*B + bias + addend); bf16 outputs only.
-extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend, int M,
-                                int N, int K, int lda, int ldb, int ldc, int flags, void* stream_) {
+// `stats` must be NULL (see dtf_gemm_stats_rows).
+extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend,
+                                float* stats, int M, int N, int K, int lda, int ldb, int ldc, int flags, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   const int relu = flags & 1, out_fp32 = (flags >> 1) & 1, atomic = (flags >> 2) & 1, a_t = (flags >> 3) & 1;
   if (M <= 0 || N <= 0 || K <= 0) return DTF_ERR_ARG;
+  if (stats != nullptr) return DTF_ERR_UNSUPPORTED;
   if (addend != nullptr && (out_fp32 || atomic)) return DTF_ERR_UNSUPPORTED;
   const bool tc_ok = aligned16(A) && aligned16(B) && (lda % 8 == 0) && (ldb % 8 == 0) && (M * (long long)N >= 4096);
   if (!tc_ok) {

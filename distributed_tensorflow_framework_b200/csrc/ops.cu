@@ -1270,6 +1270,17 @@ extern "C" int dtf_bn_finalize(const float* part, const float* gamma, const floa
                                                             momentum, unbias);
   return DTF_CHECK_LAUNCH();
 }
+// Same for partial statistics produced elsewhere (the convolution / GEMM epilogues): part is [n_rows][2][N].
+extern "C" int dtf_bn_finalize_rows(const float* part, int n_rows, const float* gamma, const float* beta, float* mean,
+                                    float* rstd, float* scale, float* shift, float* run_mean, float* run_var, int N,
+                                    long long R, float eps, float momentum, void* stream) {
+  if (n_rows <= 0) return DTF_ERR_ARG;
+  const float unbias = R > 1 ? (float)R / (float)(R - 1) : 1.f;
+  bn_finalize_kernel<<<(N + 31) / 32, 1024, 0, ST(stream)>>>(part, n_rows, gamma, beta, mean, rstd, scale, shift,
+                                                            run_mean, run_var, N, 1.f / (float)R, eps, momentum,
+                                                            unbias);
+  return DTF_CHECK_LAUNCH();
+}
 extern "C" int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma, const float* beta,
                            float* scale, float* shift, int N, float eps, void* stream) {
   bn_fold_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(run_mean, run_var, gamma, beta, scale, shift, N, eps);

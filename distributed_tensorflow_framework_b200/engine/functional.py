@@ -38,12 +38,13 @@ class ConvFn(torch.autograd.Function):
     """conv2d(SAME) + bias (+ ReLU) on the implicit-GEMM tcgen05 kernel."""
 
     @staticmethod
-    def forward(ctx, x, w_shadow, b_shadow, wvar, bvar, stride, relu, fork=False):
+    def forward(ctx, x, w_shadow, b_shadow, wvar, bvar, stride, relu, fork=False, emit_stats=False):
         KH, KW, Ci, Co = wvar.store_shape
         w2d = w_shadow.detach().view(KH * KW * Ci, Co)
         bias = bvar.master if bvar is not None else None
         keep = {}
-        y = raw.conv_fprop(x, w2d, bias, KH, KW, stride, relu=relu, c_used=wvar.shape[2], keep=keep)
+        stats = {} if emit_stats else None
+        y = raw.conv_fprop(x, w2d, bias, KH, KW, stride, relu=relu, c_used=wvar.shape[2], keep=keep, stats=stats)
         ctx.wvar, ctx.bvar, ctx.stride, ctx.relu = wvar, bvar, stride, relu
         # strided / few-channel layers ran on a packed copy of x: keep that for the filter gradient instead of x
         ctx.packed = "packed" in keep
@@ -51,20 +52,24 @@ class ConvFn(torch.autograd.Function):
         ctx.save_for_backward(keep["packed"] if ctx.packed else x, y if relu else None)
         ctx.x_needs_grad = x.requires_grad
         ctx.fork = fork
-        if fork:
+        if fork or emit_stats:
             # second output: x itself, for the other consumer of x (the shortcut branch). Its gradient comes back
             # into THIS backward and is summed inside the data-gradient kernel, so autograd never runs a separate
             # accumulation pass over the block input.
-            return y, x.view_as(x)
+            # third output: per-tile batch-norm statistics of y computed in the kernel's epilogue (or None).
+            part = stats.get("part") if stats is not None else None
+            if part is not None:
+                ctx.mark_non_differentiable(part)
+            return y, (x.view_as(x) if fork else None), part
         return y
 
     @staticmethod
-    def backward(ctx, dy, d_alias=None):
+    def backward(ctx, dy, d_alias=None, _d_part=None):
         x, y = ctx.saved_tensors
         wvar, bvar = ctx.wvar, ctx.bvar
         KH, KW, Ci, Co = wvar.store_shape
         if dy is None:  # only the forwarded copy of x was used
-            return d_alias, None, None, None, None, None, None, None
+            return d_alias, None, None, None, None, None, None, None, None
         dy = dy.contiguous()
         n, OH, OW, _ = dy.shape
         dy2 = dy.view(-1, Co)
@@ -90,12 +95,14 @@ class ConvFn(torch.autograd.Function):
         if ctx.x_needs_grad:
             dx = raw.conv_dgrad(dz, wvar.shadow_t.view(KH * KW * Co, Ci), ctx.x_shape[1:3], KH, KW, ctx.stride,
                                 addend=d_alias)
-        return dx, None, None, None, None, None, None, None
+        return dx, None, None, None, None, None, None, None, None
 
 
-def conv2d(x, wvar, bvar, stride=1, relu=False, fork=False):
-    """`fork=True` returns (y, x'): x' is x for a second consumer whose gradient is summed inside this op's backward."""
-    return ConvFn.apply(x, wvar.shadow, bvar.shadow if bvar is not None else None, wvar, bvar, stride, relu, fork)
+def conv2d(x, wvar, bvar, stride=1, relu=False, fork=False, emit_stats=False):
+    """With `fork` or `emit_stats` the result is (y, x', part): x' (fork) is x for a second consumer whose gradient is
+    summed inside this op's backward; part (emit_stats) holds per-tile batch-norm statistics of y, or None."""
+    return ConvFn.apply(x, wvar.shadow, bvar.shadow if bvar is not None else None, wvar, bvar, stride, relu, fork,
+                        emit_stats)
 
 
 class DeconvFn(torch.autograd.Function):
@@ -263,13 +270,16 @@ class BatchNormFn(torch.autograd.Function):
     """Training-mode batch norm over the rows of x viewed as [R, N] (+ residual, + ReLU)."""
 
     @staticmethod
-    def forward(ctx, x, res, g_shadow, gvar, bvar, run_mean, run_var, rows, eps, momentum, relu):
+    def forward(ctx, x, res, g_shadow, gvar, bvar, run_mean, run_var, rows, eps, momentum, relu, part=None):
         shape = x.shape
         x2 = x.reshape(rows, -1)
         res2 = res.reshape(rows, -1) if res is not None else None
         gamma = gvar.master if gvar is not None else None
         beta = bvar.master if bvar is not None else None
-        y2, mean, rstd, scale, shift = raw.bn_train_fwd(x2, gamma, beta, run_mean, run_var, eps, momentum, res2, relu)
+        if part is not None and tuple(part.shape[1:]) != (2, x2.shape[1]):
+            part = None
+        y2, mean, rstd, scale, shift = raw.bn_train_fwd(x2, gamma, beta, run_mean, run_var, eps, momentum, res2, relu,
+                                                        part=part)
         ctx.gvar, ctx.bvar, ctx.relu, ctx.rows, ctx.has_res = gvar, bvar, relu, rows, res is not None
         # without a residual the ReLU mask is a function of x alone: keep the folded coefficients instead of y
         ctx.mask_from_x = relu and res is None
@@ -294,13 +304,13 @@ class BatchNormFn(torch.autograd.Function):
         if bvar is not None:
             _ready(bvar)
         dres = dz2.view(shape) if ctx.has_res else None
-        return dx2.view(shape), dres, None, None, None, None, None, None, None, None, None
+        return dx2.view(shape), dres, None, None, None, None, None, None, None, None, None, None
 
 
 def batch_norm_train(x, rows, gvar=None, bvar=None, run_mean=None, run_var=None, eps=1e-3, momentum=0.1, res=None,
-                     relu=False):
+                     relu=False, part=None):
     return BatchNormFn.apply(x, res, gvar.shadow if gvar is not None else None, gvar, bvar, run_mean, run_var, rows,
-                             eps, momentum, relu)
+                             eps, momentum, relu, part)
 
 
 def batch_norm_eval(x, rows, gvar, bvar, run_mean, run_var, eps=1e-3, res=None, relu=False):

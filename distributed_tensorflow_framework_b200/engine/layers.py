@@ -94,20 +94,22 @@ def _prep_cuda_input(x, cin_store):
     return x.contiguous()
 
 
-def _conv_impl(x, w, b, stride, relu, fork=False):
+def _conv_impl(x, w, b, stride, relu, fork=False, emit_stats=False):
     sh, sw = _stride_hw(stride)
     KH, KW = w.shape[0], w.shape[1]
     if x.is_cuda:
         assert sh == sw, "anisotropic strides are not supported on the CUDA path"
         x = _prep_cuda_input(x, w.store_shape[2])
-        if fork:
-            y, x_fwd = Fn.conv2d(x, w, b, sh, relu, fork=True)
-            return (y if w.store_shape[3] == w.shape[3] else y[..., :w.shape[3]]), x_fwd
+        if fork or emit_stats:
+            y, x_fwd, part = Fn.conv2d(x, w, b, sh, relu, fork=fork, emit_stats=emit_stats and _training)
+            if w.store_shape[3] != w.shape[3]:
+                y, part = y[..., :w.shape[3]], None
+            return y, x_fwd, part
         y = Fn.conv2d(x, w, b, sh, relu)
         # an output-channel count that is not a multiple of 8 is stored padded (zero filters); slice it off
         return y if w.store_shape[3] == w.shape[3] else y[..., :w.shape[3]]
-    if fork:
-        return _conv_impl(x, w, b, stride, relu), x
+    if fork or emit_stats:
+        return _conv_impl(x, w, b, stride, relu), (x if fork else None), None
     xn = x.float().permute(0, 3, 1, 2)
     xn = F.pad(xn, _same_pad_nchw(xn, (KH, KW), (sh, sw)))
     y = F.conv2d(xn, w.master.permute(3, 2, 0, 1), b.master if b is not None else None, stride=(sh, sw))
@@ -133,18 +135,20 @@ def conv_eval(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stri
 
 
 def conv_nonacti(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1], use_bias=True,
-                 fork_input=False):
+                 fork_input=False, emit_stats=False):
     """conv2d + bias, Xavier init, variables `weights_nonacti` / `biases_nonacti` -- distribute_tools.py:93-106.
     `use_bias=False` (extension) drops the bias for convolutions that feed a batch norm, where it is redundant.
-    `fork_input=True` (extension) returns (y, x'): feed x' to the other consumer of x (a residual shortcut) and the
-    two gradients of x are summed inside this layer's data-gradient kernel instead of by a separate pass."""
+    With `fork_input` or `emit_stats` (extensions) the result is (y, x', part). x' (fork_input): feed it to the other
+    consumer of x (a residual shortcut) and the two gradients of x are summed inside this layer's data-gradient
+    kernel instead of by a separate pass. part (emit_stats): per-tile batch-norm statistics of y computed in the
+    convolution's epilogue, for batch_norm_channel(..., stats_part=part); None where the kernel cannot."""
     with variable_scope(layer_name):
         shape = [kernel_size[0], kernel_size[1], in_channels, out_channels]
         store = [kernel_size[0], kernel_size[1], _pad8(in_channels), _pad8(out_channels)] if x.is_cuda else None
         w = _get("weights_nonacti", shape, XavierInitializer(), kind="conv_w", store_shape=store)
         b = _get("biases_nonacti", [out_channels], ConstantInitializer(0.0), kind="bias",
                  store_shape=[_pad8(out_channels)] if x.is_cuda else None) if use_bias else None
-        return _conv_impl(x, w, b, stride, relu=False, fork=fork_input)
+        return _conv_impl(x, w, b, stride, relu=False, fork=fork_input, emit_stats=emit_stats)
 
 
 def conv_nonacti_eval(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1]):
@@ -220,9 +224,10 @@ def batch_norm(x):
     return (xf - mean) * torch.rsqrt(var + epsilon)
 
 
-def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momentum=0.1):
+def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momentum=0.1, stats_part=None):
     """Standard per-channel batch norm with affine parameters and running statistics (needed by the ResNet
-    configs of BASELINE.json; optionally fused with a residual add and ReLU)."""
+    configs of BASELINE.json; optionally fused with a residual add and ReLU). `stats_part`: per-tile statistics of x
+    from the convolution that produced it (conv_nonacti(..., emit_stats=True)); saves the statistics pass."""
     C = x.shape[-1]
     with variable_scope(layer_name):
         beta = _get("beta", [C], ConstantInitializer(0.0), kind="bias")  # beta first: [beta | gamma] are adjacent in
@@ -233,7 +238,8 @@ def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momen
     if x.is_cuda:
         x = x.contiguous()
         if _training:
-            return Fn.batch_norm_train(x, rows, gamma, beta, rm.master, rv.master, eps, momentum, residual, relu)
+            return Fn.batch_norm_train(x, rows, gamma, beta, rm.master, rv.master, eps, momentum, residual, relu,
+                                       part=stats_part)
         return Fn.batch_norm_eval(x, rows, gamma, beta, rm.master, rv.master, eps, residual, relu)
     xf = x.float().reshape(rows, C)
     y = F.batch_norm(xf, rm.master.detach(), rv.master.detach(), gamma.master, beta.master, _training, momentum, eps)

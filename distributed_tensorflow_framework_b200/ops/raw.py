@@ -23,7 +23,8 @@ def _sp():
     return _lib.stream_ptr()
 
 
-def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=None, accumulate=False, addend=None):
+def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=None, accumulate=False, addend=None,
+         stats=None):
     """act(A @ B + bias). a: [M,K] (or [K,M] if a_transposed), b: [K,N], both bf16 row-major."""
     if a_transposed:
         K, M = a.shape
@@ -37,7 +38,17 @@ def gemm(a, b, bias=None, relu=False, out_fp32=False, a_transposed=False, out=No
             (8 if a_transposed else 0)
     if addend is not None:  # act(A @ B + bias + addend), addend bf16 [M, N] laid out like `out`
         assert addend.dtype == bf16 and addend.shape == out.shape and addend.stride(0) == out.stride(0)
-    _lib.call("dtf_gemm_bf16_ex", a, b, out, bias, addend, M, N, K, a.stride(0), b.stride(0), out.stride(0), flags, _sp())
+    part = None
+    if stats is not None:  # dict: receives "part" = [rows, 2, N] per-tile column sums / sums of squares of the output
+        rows = 0
+        if not (relu or out_fp32 or accumulate or a_transposed or addend is not None):
+            rows = _lib.lib().dtf_gemm_stats_rows(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a.stride(0),
+                                                  b.stride(0), out.stride(0))
+        if rows > 0:
+            part = torch.empty((rows, 2, N), device=a.device, dtype=torch.float32)
+            stats["part"] = part
+    _lib.call("dtf_gemm_bf16_ex", a, b, out, bias, addend, part, M, N, K, a.stride(0), b.stride(0), out.stride(0), flags,
+              _sp())
     return out
 
 
@@ -166,7 +177,7 @@ def _block_copy(src, dst, desc, fp32=False, accumulate=False):
               1 if accumulate else 0, _sp())
 
 
-def _packed_fprop(x, w2d, bias, plan, relu, flip=False, keep=None):
+def _packed_fprop(x, w2d, bias, plan, relu, flip=False, keep=None, stats=None):
     """The convolution of `plan` as pack + stride-1 halo convolution; None if the halo kernel does not take it."""
     n_out = w2d.shape[1]
     if not _lib.lib().dtf_conv_halo_supported(plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out):
@@ -178,30 +189,46 @@ def _packed_fprop(x, w2d, bias, plan, relu, flip=False, keep=None):
     Wp = torch.zeros((plan.KH2 * plan.KW2 * plan.Cp, n_out), device=x.device, dtype=bf16)
     _block_copy(w2d, Wp, plan.descs("w", n_out, x.device, flip))
     out = torch.empty((n, plan.Hp, plan.Wq, n_out), device=x.device, dtype=bf16)
-    _lib.call("dtf_conv_halo_bf16", P, Wp, out, bias, n, plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out,
+    part = _halo_stats_buffer(stats, relu, n, plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out, x.device)
+    _lib.call("dtf_conv_halo_bf16_ex", P, Wp, out, bias, part, n, plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out,
               plan.pad_h2, plan.pad_w2, 0, 1 if relu else 0, _sp())
     return out
 
 
-def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False, c_used=None, keep=None):
+def _halo_stats_buffer(stats, relu, n, H, W, C, KH, KW, n_out, device):
+    """The [rows, 2, n_out] statistics buffer of a halo convolution (registered in `stats`), or None."""
+    if stats is None or relu:
+        return None
+    rows = _lib.lib().dtf_conv_halo_stats_rows(n, H, W, C, KH, KW, n_out)
+    if rows <= 0:
+        return None
+    stats["part"] = torch.empty((rows, 2, n_out), device=device, dtype=torch.float32)
+    return stats["part"]
+
+
+def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False, c_used=None, keep=None, stats=None):
+    """`stats` (dict, optional): where the kernel can, it receives "part" = [rows, 2, n_out] per-tile column sums and
+    sums of squares of the output (batch-norm statistics without another pass); absent if the path cannot."""
     n, H, W, C = x.shape
     n_out = w2d.shape[1]
     if KH == 1 and KW == 1 and stride > 1:  # strided 1x1: select the sampled pixels, then a dense GEMM
-        return conv_fprop(subsample(x, stride), w2d, bias, 1, 1, 1, relu, out_fp32)
+        return conv_fprop(subsample(x, stride), w2d, bias, 1, 1, 1, relu, out_fp32, stats=stats)
     if KH == 1 and KW == 1 and stride == 1:  # a 1x1 convolution is a dense GEMM: TMA-fed A operand, no gather
-        return gemm(x.view(-1, C), w2d, bias, relu=relu, out_fp32=out_fp32).view(n, H, W, n_out)
+        return gemm(x.view(-1, C), w2d, bias, relu=relu, out_fp32=out_fp32, stats=stats).view(n, H, W, n_out)
     OH, pt = same_pad(H, KH, stride)
     OW, pl = same_pad(W, KW, stride)
     if USE_HALO and not out_fp32 and (stride > 1 or C % 64 != 0):
         plan = _pack_plan(H, W, C, C if c_used is None else c_used, KH, KW, stride)
         if plan is not None:
-            y = _packed_fprop(x, w2d, bias, plan, relu, keep=keep)
+            y = _packed_fprop(x, w2d, bias, plan, relu, keep=keep, stats=stats)
             if y is not None:
                 return y
     out = torch.empty((n, OH, OW, n_out), device=x.device, dtype=torch.float32 if out_fp32 else bf16)
     if stride == 1 and not out_fp32 and USE_HALO and _lib.lib().dtf_conv_halo_supported(H, W, C, KH, KW, n_out):
         # halo-tile kernel: one TMA load per tile, all taps are shifted views of the same shared-memory tile
-        _lib.call("dtf_conv_halo_bf16", x, w2d, out, bias, n, H, W, C, KH, KW, n_out, pt, pl, 0, 1 if relu else 0, _sp())
+        part = _halo_stats_buffer(stats, relu, n, H, W, C, KH, KW, n_out, x.device)
+        _lib.call("dtf_conv_halo_bf16_ex", x, w2d, out, bias, part, n, H, W, C, KH, KW, n_out, pt, pl, 0,
+                  1 if relu else 0, _sp())
         return out
     flags = (1 if relu else 0) | (2 if out_fp32 else 0)
     _lib.call("dtf_conv_igemm_bf16", x, w2d, out, bias, n, H, W, C, OH, OW, KH, KW, n_out, stride, pt, pl, 0, flags,
@@ -382,16 +409,22 @@ def _part(R, N, device):
     return torch.empty(nblk, 2, N, device=device, dtype=torch.float32)
 
 
-def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, res=None, relu=False):
-    """Training-mode batch norm over rows of x2d [R, N]. Returns (y, mean, rstd)."""
+def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, res=None, relu=False, part=None):
+    """Training-mode batch norm over rows of x2d [R, N]. Returns (y, mean, rstd, scale, shift). `part` [rows, 2, N]:
+    per-tile sums / sums of squares of x2d already produced by the kernel that wrote it (no statistics pass then)."""
     R, N = x2d.shape
     dev = x2d.device
-    part = _part(R, N, dev)
-    _lib.call("dtf_bn_stats", x2d, part, R, N, _sp())
     stat = torch.empty(4, N, device=dev, dtype=torch.float32)
     mean, rstd, scale, shift = stat[0], stat[1], stat[2], stat[3]
-    _lib.call("dtf_bn_finalize", part, gamma, beta, mean, rstd, scale, shift, run_mean, run_var, N, R, eps, momentum,
-              _sp())
+    if part is not None:
+        assert part.shape[1:] == (2, N) and part.dtype == torch.float32
+        _lib.call("dtf_bn_finalize_rows", part, part.shape[0], gamma, beta, mean, rstd, scale, shift, run_mean, run_var,
+                  N, R, eps, momentum, _sp())
+    else:
+        part = _part(R, N, dev)
+        _lib.call("dtf_bn_stats", x2d, part, R, N, _sp())
+        _lib.call("dtf_bn_finalize", part, gamma, beta, mean, rstd, scale, shift, run_mean, run_var, N, R, eps,
+                  momentum, _sp())
     y = torch.empty_like(x2d)
     _lib.call("dtf_bn_apply", x2d, res, y, scale, shift, R, N, 1 if relu else 0, _sp())
     return y, mean, rstd, scale, shift

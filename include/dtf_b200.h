@@ -33,8 +33,9 @@ extern "C" {
  * Replaces tf.matmul + bias_add + relu of FC_layer (distribute_tools.py:190-208) and its gradients. */
 int dtf_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
                   int ldc, int flags, void* stream);
-int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend, int M, int N,
-                     int K, int lda, int ldb, int ldc, int flags, void* stream);
+int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend, float* stats,
+                     int M, int N, int K, int lda, int ldb, int ldc, int flags, void* stream);
+int dtf_gemm_stats_rows(const void* A, const void* B, const void* C, int M, int N, int K, int lda, int ldb, int ldc);
 
 /* Dense GEMMs run a persistent kernel (tile loop per CTA, smem ring kept full across tiles, accumulator double
  * buffered in TMEM so the epilogue overlaps the next tile). bit0 of `on`: persistent kernel (0 = one tile per CTA);
@@ -66,6 +67,10 @@ int dtf_conv_igemm_bf16(const void* src, const void* W2d, void* out, const float
 int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int n_out);
 int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H, int W, int C,
                        int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags, void* stream);
+int dtf_conv_halo_bf16_ex(const void* src, const void* W2d, void* out, const float* bias, float* stats, int n_img,
+                          int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags,
+                          void* stream);
+int dtf_conv_halo_stats_rows(int n_img, int H, int W, int C, int KH, int KW, int n_out);
 
 /* Halo-tile filter gradient (stride 1, C % 64 == 0, n_out % 64 == 0, <= 16 taps): x halo + dy tile per image tile,
  * all taps accumulate in TMEM (tap pairs share one M=128 MMA through the descriptor's leading-dimension offset),
@@ -117,6 +122,9 @@ int dtf_bn_stats(const void* x, float* part, long long R, int N, void* stream);
 int dtf_bn_finalize(const float* part, const float* gamma, const float* beta, float* mean, float* rstd, float* scale,
                     float* shift, float* run_mean, float* run_var, int N, long long R, float eps, float momentum,
                     void* stream);
+int dtf_bn_finalize_rows(const float* part, int n_rows, const float* gamma, const float* beta, float* mean,
+                         float* rstd, float* scale, float* shift, float* run_mean, float* run_var, int N, long long R,
+                         float eps, float momentum, void* stream);
 int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma, const float* beta, float* scale,
                 float* shift, int N, float eps, void* stream);
 int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift, long long R, int N,

@@ -159,9 +159,23 @@ def test_conv_fork_sums_both_gradients_of_x():
         w = store.get_variable("w%d" % k, [k, k, 64, 128], XavierInitializer(), kind="conv_w")
         x = rnd(2, 16, 16, 64).requires_grad_(True)
         g1, g2 = rnd(2, 16, 16, 128), rnd(2, 16, 16, 64)
-        y, xf = Fn.conv2d(x, w, None, 1, False, fork=True)
+        y, xf, _ = Fn.conv2d(x, w, None, 1, False, fork=True)
         (y * g1).sum().backward(retain_graph=True, inputs=[x])
         gx_main = x.grad.clone()
         x.grad = None
         ((y * g1).sum() + (xf * g2).sum()).backward(inputs=[x])
         close(x.grad, gx_main.float() + g2.float())
+
+
+@pytest.mark.parametrize("n,H,C,Co,k,s", [(4, 28, 128, 128, 3, 1), (5, 7, 64, 72, 3, 1), (3, 56, 64, 64, 3, 1),
+                                          (2, 30, 64, 128, 3, 2), (2, 64, 8, 64, 7, 2)])
+def test_conv_epilogue_statistics(raw, n, H, C, Co, k, s):
+    x = rnd(n, H, H, C)
+    w = (torch.randn(k, k, C, Co, device="cuda") * 0.05).to(torch.bfloat16).reshape(k * k * C, Co)
+    st = {}
+    y = raw.conv_fprop(x, w, None, k, k, s, stats=st, c_used=min(C, 3) if C == 8 else None)
+    assert "part" in st
+    tot = st["part"].sum(0)
+    yf = y.float().reshape(-1, Co)
+    assert torch.allclose(tot[0], yf.sum(0), rtol=2e-2, atol=0.5)
+    assert torch.allclose(tot[1], (yf * yf).sum(0), rtol=2e-2, atol=0.5)
