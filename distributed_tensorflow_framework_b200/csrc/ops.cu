@@ -687,9 +687,12 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* _
 
 // ------------------------------------------------------------------------------------------- pooling (NHWC)
 // idx (optional, max pooling): position of the first maximum inside the window (dy*kw + dx), one byte per output.
+// TKH/TKW > 0: compile-time window (loops unrolled, all window loads in flight at once); 0: run-time window.
+template <int TKH, int TKW>
 __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
-                                uint8_t* __restrict__ idx, int n_img, int H, int W, int C, int OH, int OW, int kh,
-                                int kw, int sh, int sw, int pt, int pl, int is_max) {
+                                uint8_t* __restrict__ idx, int n_img, int H, int W, int C, int OH, int OW, int kh_,
+                                int kw_, int sh, int sw, int pt, int pl, int is_max) {
+  const int kh = TKH > 0 ? TKH : kh_, kw = TKW > 0 ? TKW : kw_;
   const int cpr = C / 8;
   const long long total = (long long)n_img * OH * OW * cpr;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -705,6 +708,38 @@ __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
       am[j] = 0;
     }
     int cnt = 0;
+    if (TKH > 0 && TKH * TKW <= 9) {
+      // fixed small window: issue every load first, then reduce (memory-level parallelism instead of a chain)
+      BF8 win[TKH > 0 ? TKH * TKW : 1];
+      bool ok[TKH > 0 ? TKH * TKW : 1];
+#pragma unroll
+      for (int dy = 0; dy < TKH; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < TKW; ++dx) {
+          const int ih = oh * sh - pt + dy, iw = ow * sw - pl + dx;
+          ok[dy * TKW + dx] = ih >= 0 && ih < H && iw >= 0 && iw < W;
+          if (ok[dy * TKW + dx]) win[dy * TKW + dx] = ld8(x + (((long long)n * H + ih) * W + iw) * C + c0);
+        }
+#pragma unroll
+      for (int t = 0; t < TKH * TKW; ++t) {
+        if (!ok[t]) continue;
+        float f[8];
+        unpack8(win[t], f);
+        if (is_max) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (f[j] > a[j] || cnt == 0) {
+              a[j] = f[j];
+              am[j] = t;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a[j] += f[j];
+        }
+        ++cnt;
+      }
+    } else
     for (int dy = 0; dy < kh; ++dy) {
       const int ih = oh * sh - pt + dy;
       if (ih < 0 || ih >= H) continue;
@@ -744,9 +779,12 @@ __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
 }
 // Gather-style backward (deterministic, no atomics): each input element visits the (few) windows that cover it.
 // Max: the window's recorded argmax decides; Avg: dy / (valid elements of the window).
+// TK/TS > 0: compile-time square window / stride (the index divisions become shifts and multiplies).
+template <int TK, int TS>
 __global__ void pool_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ dy,
-                                __nv_bfloat16* __restrict__ dx, int n_img, int H, int W, int C, int OH, int OW, int kh,
-                                int kw, int sh, int sw, int pt, int pl, int is_max) {
+                                __nv_bfloat16* __restrict__ dx, int n_img, int H, int W, int C, int OH, int OW, int kh_,
+                                int kw_, int sh_, int sw_, int pt, int pl, int is_max) {
+  const int kh = TK > 0 ? TK : kh_, kw = TK > 0 ? TK : kw_, sh = TS > 0 ? TS : sh_, sw = TS > 0 ? TS : sw_;
   const int cpr = C / 8;
   const long long total = (long long)n_img * H * W * cpr;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -759,6 +797,35 @@ __global__ void pool_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_bflo
     for (int j = 0; j < 8; ++j) g[j] = 0.f;
     const int oh_lo = max(0, (h + pt - kh + sh) / sh), oh_hi = min(OH - 1, (h + pt) / sh);
     const int ow_lo = max(0, (w + pl - kw + sw) / sw), ow_hi = min(OW - 1, (w + pl) / sw);
+    if (is_max && oh_hi - oh_lo <= 1 && ow_hi - ow_lo <= 1) {
+      // at most 2 x 2 covering windows (kernel <= 2 * stride): fetch all of them before using any
+      BF8 dv[4];
+      uint2 pk[4];
+      bool ok[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int oh = oh_lo + (t >> 1), ow = ow_lo + (t & 1);
+        ok[t] = oh <= oh_hi && ow <= ow_hi;
+        if (ok[t]) {
+          const long long o = (((long long)n * OH + oh) * OW + ow) * C + c0;
+          dv[t] = ld8(dy + o);
+          pk[t] = *reinterpret_cast<const uint2*>(idx + o);
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        if (!ok[t]) continue;
+        const int oh = oh_lo + (t >> 1), ow = ow_lo + (t & 1);
+        const uint32_t pos = (h - (oh * sh - pt)) * kw + (w - (ow * sw - pl));
+        float d[8];
+        unpack8(dv[t], d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t a = ((j < 4 ? pk[t].x : pk[t].y) >> ((j & 3) * 8)) & 0xff;
+          g[j] += (a == pos) ? d[j] : 0.f;
+        }
+      }
+    } else
     for (int oh = oh_lo; oh <= oh_hi; ++oh) {
       for (int ow = ow_lo; ow <= ow_hi; ++ow) {
         const long long o = (((long long)n * OH + oh) * OW + ow) * C + c0;
@@ -1327,9 +1394,13 @@ extern "C" int dtf_pool_fwd(const void* x, void* y, void* idx, int n_img, int H,
   if (C % 8) return DTF_ERR_ALIGN;
   if (kh * kw > 255) return DTF_ERR_UNSUPPORTED;
   const long long total = (long long)n_img * OH * OW * (C / 8);
-  pool_fwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y,
-                                                                (uint8_t*)idx, n_img, H, W, C, OH, OW, kh, kw, sh, sw,
-                                                                pt, pl, is_max);
+#define DTF_POOL_FWD(KH_, KW_)                                                                                 \
+  pool_fwd_kernel<KH_, KW_><<<grid_for(total, 256), 256, 0, ST(stream)>>>(                                     \
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (uint8_t*)idx, n_img, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl, is_max)
+  if (kh == 3 && kw == 3) DTF_POOL_FWD(3, 3);
+  else if (kh == 2 && kw == 2) DTF_POOL_FWD(2, 2);
+  else DTF_POOL_FWD(0, 0);
+#undef DTF_POOL_FWD
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_pool_bwd(const void* idx, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW,
@@ -1337,9 +1408,14 @@ extern "C" int dtf_pool_bwd(const void* idx, const void* dy, void* dx, int n_img
   if (C % 8) return DTF_ERR_ALIGN;
   if (is_max && idx == nullptr) return DTF_ERR_ARG;
   const long long total = (long long)n_img * H * W * (C / 8);
-  pool_bwd_kernel<<<grid_for(total, 256), 256, 0, ST(stream)>>>((const uint8_t*)idx, (const __nv_bfloat16*)dy,
-                                                                (__nv_bfloat16*)dx, n_img, H, W, C, OH, OW, kh, kw,
-                                                                sh, sw, pt, pl, is_max);
+#define DTF_POOL_BWD(K_, S_)                                                                                   \
+  pool_bwd_kernel<K_, S_><<<grid_for(total, 256), 256, 0, ST(stream)>>>(                                        \
+      (const uint8_t*)idx, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, n_img, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl, \
+      is_max)
+  if (kh == 3 && kw == 3 && sh == 2 && sw == 2) DTF_POOL_BWD(3, 2);
+  else if (kh == 2 && kw == 2 && sh == 2 && sw == 2) DTF_POOL_BWD(2, 2);
+  else DTF_POOL_BWD(0, 0);
+#undef DTF_POOL_BWD
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_lrn_fwd(const void* x, void* y, long long pixels, int C, int radius, float bias, float alpha,
