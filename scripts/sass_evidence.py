@@ -1,0 +1,26 @@
+"""Per-kernel counts of the SASS mnemonics that prove tcgen05 / TMEM / TMA / mbarrier / multimem use
+(cuobjdump -sass on the in-tree library; runs on the CPU box). Output: profiles/sass_evidence_r1.txt."""
+import collections, os, re, subprocess, sys
+root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+lib = os.path.join(root, "distributed_tensorflow_framework_b200", "lib", "libdtf_b200_cuda.so")
+KEEP = re.compile(r"^(UTCHMMA|UTCBAR|UTCATOMSWS|LDTM|STTM|UTMALDG|UTMASTG|UTMAPF|SYNCS|LDGSTS|MEMBAR|ELECT|RED\.|ATOM|MULTIMEM|LD\.E\..*SYS|ST\.E\..*SYS|UBLKCP)")
+out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
+counts = collections.OrderedDict()
+fn = None
+for line in out.splitlines():
+    m = re.search(r"Function : (\S+)", line)
+    if m:
+        fn = m.group(1)
+        counts[fn] = collections.Counter()
+        continue
+    m = re.search(r"/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d\s+)?([A-Z][A-Z0-9_.]+)", line)
+    if m and fn:
+        op = m.group(1)
+        if KEEP.match(op):
+            op = re.sub(r"^(LDTM)\..*", r"\1.", op)
+            counts[fn][op] += 1
+with open(os.path.join(root, "profiles", "sass_evidence_r1.txt"), "w") as f:
+    for fn, c in counts.items():
+        for op, n in sorted(c.items()):
+            f.write("%-100s %-34s %d\n" % (fn, op, n))
+print("kernels:", len(counts))
