@@ -282,8 +282,10 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int tile_n = blockIdx.x;
-  const int tile_m = blockIdx.y;
+  // tiles are linearised in grid.x (grid.y is limited to 65535 blocks: 8.4 M rows): consecutive blocks share an A tile
+  const int tiles_n_grid = (p.N + BN - 1) / BN;
+  const int tile_n = blockIdx.x % tiles_n_grid;
+  const int tile_m = blockIdx.x / tiles_n_grid;
   const int total_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
   const int kb0 = blockIdx.z * p.kb_per_split;
   const int kb1 = min(total_kb, kb0 + p.kb_per_split);
@@ -755,8 +757,8 @@ igemm_ag_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant
 __global__ void gemm_simt_kernel(const __nv_bfloat16* A, const __nv_bfloat16* B, void* C, const float* bias, int M,
                                  int N, int K, int lda, int ldb, int ldc, int a_t, int b_t, int relu, int out_fp32,
                                  int accumulate, const __nv_bfloat16* addend = nullptr) {
-  const int n = blockIdx.x * blockDim.x + threadIdx.x;
-  const int m = blockIdx.y * blockDim.y + threadIdx.y;
+  const int n = blockIdx.y * blockDim.x + threadIdx.x;  // rows on grid.x (no 65535 limit), column blocks on grid.y
+  const int m = blockIdx.x * blockDim.y + threadIdx.y;
   if (m >= M || n >= N) return;
   float acc = 0.f;
   for (int k = 0; k < K; ++k) {
@@ -819,7 +821,9 @@ static int launch_igemm(const CUtensorMap& ta, const CUtensorMap& tb, const Igem
     if (e != cudaSuccess) return DTF_ERR_CUDA;
     attr_set[dev & 63] = true;
   }
-  dim3 grid((p.N + BN - 1) / BN, (p.M + BLOCK_M - 1) / BLOCK_M, splits);
+  const long long tiles = (long long)((p.N + BN - 1) / BN) * ((p.M + BLOCK_M - 1) / BLOCK_M);
+  if (tiles > 0x7fffffffLL) return DTF_ERR_TOO_LARGE;
+  dim3 grid((unsigned)tiles, 1, splits);
   kern<<<grid, NUM_THREADS, L::TOTAL, stream>>>(ta, tb, p);
   return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
@@ -901,7 +905,7 @@ extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const flo
   if (addend != nullptr && (out_fp32 || atomic)) return DTF_ERR_UNSUPPORTED;
   const bool tc_ok = aligned16(A) && aligned16(B) && (lda % 8 == 0) && (ldb % 8 == 0) && (M * (long long)N >= 4096);
   if (!tc_ok) {
-    dim3 block(32, 8), grid((N + 31) / 32, (M + 7) / 8);
+    dim3 block(32, 8), grid((M + 7) / 8, (N + 31) / 32);
     gemm_simt_kernel<<<grid, block, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(A),
                                                  reinterpret_cast<const __nv_bfloat16*>(B), C, bias, M, N, K, lda, ldb,
                                                  ldc, a_t, 0, relu, out_fp32 | atomic, atomic,
@@ -1016,7 +1020,8 @@ extern "C" int dtf_gemm_bf16_ag(const void* A, const void* const* peer_b, void* 
       if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) != cudaSuccess) return DTF_ERR_CUDA;
       attr64[dev & 63] = true;
     }
-    kern<<<dim3(1, (M + BLOCK_M - 1) / BLOCK_M, 1), NUM_THREADS, L::TOTAL, stream>>>(ta, pm, ag, p);
+    // N <= 64: one column tile; tiles are linearised in grid.x (see igemm_body)
+    kern<<<dim3(((N + 63) / 64) * ((M + BLOCK_M - 1) / BLOCK_M), 1, 1), NUM_THREADS, L::TOTAL, stream>>>(ta, pm, ag, p);
   } else {
     using L = SmemLayout<128, 3>;
     auto kern = igemm_ag_kernel<128, 3>;
@@ -1024,7 +1029,7 @@ extern "C" int dtf_gemm_bf16_ag(const void* A, const void* const* peer_b, void* 
       if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL) != cudaSuccess) return DTF_ERR_CUDA;
       attr128[dev & 63] = true;
     }
-    kern<<<dim3((N + 127) / 128, (M + BLOCK_M - 1) / BLOCK_M, 1), NUM_THREADS, L::TOTAL, stream>>>(ta, pm, ag, p);
+    kern<<<dim3(((N + 127) / 128) * ((M + BLOCK_M - 1) / BLOCK_M), 1, 1), NUM_THREADS, L::TOTAL, stream>>>(ta, pm, ag, p);
   }
   return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }

@@ -14,6 +14,7 @@ through the TF gRPC runtime (/root/reference/distribute_train.py:109-110,146-160
 (/root/reference/distribute_train.py:43-46,86-90).
 """
 import ctypes
+import os
 from typing import List, Optional
 
 import torch
@@ -89,7 +90,7 @@ class Communicator(object):
         self.heap, self.rank, self.world = heap, rank, world
         self.handle = ctypes.c_void_p()
         self.stream = torch.cuda.Stream(device=heap.device)
-        self.blocks = 64
+        self.blocks = int(os.environ.get("DTF_COMM_BLOCKS", "64"))  # CTAs per collective kernel
         self._version = 0
         if heap.peer_ptrs is not None:  # peers already mapped (torch symmetric memory / NVLS backend)
             arr = (ctypes.c_void_p * world)(*heap.peer_ptrs)
@@ -188,7 +189,8 @@ class GradientEngine(object):
     on the communication stream as soon as backward has produced all of its gradients.
     """
 
-    def __init__(self, store, optimizer, rank=0, world=1, algo="auto", group=None, bucket_bytes=4 << 20,
+    def __init__(self, store, optimizer, rank=0, world=1, algo="auto", group=None,
+                 bucket_bytes=int(os.environ.get("DTF_BUCKET_MB", "4")) << 20,
                  placement="bytes", heap_extra_bytes=0, overlap=True):
         self.store, self.opt, self.rank, self.world, self.group = store, optimizer, rank, world, group
         dev = store.device

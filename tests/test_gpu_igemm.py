@@ -179,3 +179,18 @@ def test_conv_epilogue_statistics(raw, n, H, C, Co, k, s):
     yf = y.float().reshape(-1, Co)
     assert torch.allclose(tot[0], yf.sum(0), rtol=2e-2, atol=0.5)
     assert torch.allclose(tot[1], (yf * yf).sum(0), rtol=2e-2, atol=0.5)
+
+
+def test_gather_conv_with_more_than_65535_row_tiles(raw):
+    """8.5 M output pixels = 66 k row tiles: tiles are linearised in grid.x (grid.y would overflow)."""
+    n, H, W, C, Co = 170, 224, 224, 8, 8
+    x = rnd(n, H, W, C)
+    w = (torch.randn(3, 3, C, Co, device="cuda") * 0.1).to(torch.bfloat16)
+    raw.USE_PACK = False
+    try:
+        y = raw.conv_fprop(x, w.reshape(9 * C, Co), None, 3, 3, 1)
+    finally:
+        raw.USE_PACK = True
+    for img in (0, n - 1):  # the last image lives in the tiles beyond 65535
+        ref = F.conv2d(x[img:img + 1].float().permute(0, 3, 1, 2), w.float().permute(3, 2, 0, 1), padding=1)
+        close(y[img:img + 1], ref.permute(0, 2, 3, 1))
