@@ -461,6 +461,11 @@ struct PnParams {
   int img_rows;     // padded-linear rows per packed image: (R+KH-1)*Wp
   int groups;       // pixel tiles: n_img*tiles_per_img (G == 1) or ceil(n_img / G)
   int xst;          // halo-tile stages (2 or 3)
+  // structurally absent (tap, channel-block) weight tiles (space-to-depth packed filters) are skipped:
+  // mask_by 0: none; 1: the mask is chosen by the input-channel block (cb / blk_per_phase);
+  // 2: by the output-channel tile (tile_co / blk_per_phase). Bit t of a mask = tap t present.
+  int mask_by, blk_per_phase;
+  unsigned long long phase_mask[4];
 };
 
 // MW: output channels per item, 64 (single 64-channel weight box) or 128. STATS: also emit per-tile batch-norm
@@ -542,6 +547,12 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
     }
   };
 
+  auto tap_mask = [&](int cb, int tile_co) -> unsigned long long {
+    if (pp.mask_by == 1) return pp.phase_mask[cb / pp.blk_per_phase];
+    if (pp.mask_by == 2) return pp.phase_mask[tile_co / pp.blk_per_phase];
+    return ~0ull;
+  };
+
   if (warp == 5) {
     if (lane == 0) {
       int xs = 0, ws = 0;
@@ -559,8 +570,10 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
             x_par ^= 1;
           }
           if (resident && !first) continue;
+          const unsigned long long tmask = tap_mask(cb, tile_co);
           int krow = cb * 64;
           for (int t = 0; t < ntaps; ++t, krow += p.C) {
+            if (!((tmask >> t) & 1ull)) continue;
             if (!resident) mbar_wait(&w_empty[ws], w_par);
             mbar_arrive_expect_tx(&w_full[ws], W_BYTES);
 #pragma unroll
@@ -597,11 +610,23 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + buf * PN_PIX;
       uint32_t accum = 0;
+      const int tile_co = item % pp.tiles_co;
       for (int cb = 0; cb < ncblk; ++cb) {
         mbar_wait(&x_full[xs], x_par);
         const uint64_t xdesc_s = xdesc0 + xs * x_stage16;
+        const unsigned long long tmask = tap_mask(cb, tile_co) & ((ntaps < 64) ? ((1ull << ntaps) - 1) : ~0ull);
+        const int last_t = 63 - __clzll((long long)tmask);  // the commits ride on the last tap that is executed
         int off = off_first, kw = 0;
         for (int t = 0; t < ntaps; ++t) {
+          if (!((tmask >> t) & 1ull)) {  // absent weight tile: only advance the tap shift
+            if (++kw == p.KW) {
+              kw = 0;
+              off += off_wrap;
+            } else {
+              off += off_step;
+            }
+            continue;
+          }
           mbar_wait(&w_full[ws], w_par);  // resident: phase 0 completes once, w_par stays 0
           tc_fence_after();
           if (elect_one()) {
@@ -610,7 +635,7 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_bf16(d_tmem, wdesc + 128 * k, xdesc + 2 * k, idesc, (k > 0) ? 1u : accum);
             if (!resident) umma_commit(&w_empty[ws]);
-            if (t == ntaps - 1) {
+            if (t == last_t) {
               umma_commit(&x_empty[xs]);
               if (cb == ncblk - 1) umma_commit(&acc_full[buf]);
             }
@@ -994,7 +1019,7 @@ struct PnHost {
 
 // Fills the kernel parameters; false when the geometry does not suit the pixels-as-N kernel.
 static bool pn_setup(int n_img, int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror,
-                     PnHost* h) {
+                     PnHost* h, int n_phase = 0, const unsigned long long* phase_mask = nullptr) {
   if ((C & 63) || (n_out & 7) || KH * KW < 2 || KH * KW > 49) return false;
   Params& p = h->p;
   PnParams& pp = h->pp;
@@ -1020,13 +1045,28 @@ static bool pn_setup(int n_img, int H, int W, int C, int KH, int KW, int n_out, 
   const long long items = (long long)pp.groups * pp.tiles_co;
   if (items > 0x7fffffffLL || (long long)n_img * H * W > 0x7fffffffLL) return false;
   pp.total_items = (int)items;
-  const int total_w = KH * KW * (C >> 6);
+  int total_w = KH * KW * (C >> 6);
+  if (n_phase > 1 && n_phase <= 4 && phase_mask != nullptr) {
+    // masks select by input-channel block (forward: C = n_phase x block) or by output tile (mirror: n_out = ...)
+    const int blocks = mirror ? pp.tiles_co : (C >> 6);
+    if (blocks % n_phase == 0) {
+      pp.mask_by = mirror ? 2 : 1;
+      pp.blk_per_phase = blocks / n_phase;
+      for (int i = 0; i < n_phase; ++i) pp.phase_mask[i] = phase_mask[i];
+      if (!mirror) {  // executed weight tiles per item (sizes the resident ring)
+        total_w = 0;
+        for (int i = 0; i < n_phase; ++i)
+          total_w += pp.blk_per_phase * __builtin_popcountll(phase_mask[i] & ((1ull << (KH * KW)) - 1));
+      }
+    }
+  }
+  const bool masked_by_tile = pp.mask_by == 2;
   // two halo stages: a third one measured slower (it shrinks the weight ring, which matters more)
   for (pp.xst = 2; pp.xst >= 2; --pp.xst) {
     const int fixed = 1024 + pp.xst * p.a_stage_bytes + 1024 + PN_STAGE_BYTES + PN_TAB_BYTES;
     const int avail = 227 * 1024 - fixed;
     pp.resident = 0;
-    if (pp.tiles_co == 1 && total_w <= MAX_B_STAGES && total_w * w_bytes <= avail) {
+    if (!masked_by_tile && pp.tiles_co == 1 && total_w <= MAX_B_STAGES && total_w * w_bytes <= avail) {
       pp.resident = 1;
       pp.nb = total_w;
     } else {
@@ -1105,12 +1145,13 @@ extern "C" int dtf_conv_halo_supported(int H, int W, int C, int KH, int KW, int 
 // flags: bit0 relu, bit8 use the descriptor base-offset field for the shifted tap views.
 extern "C" int dtf_conv_halo_bf16_ex(const void* src, const void* W2d, void* out, const float* bias, float* stats,
                                      int n_img, int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w,
-                                     int mirror, int flags, void* stream_);
+                                     int mirror, int flags, int n_phase, const unsigned long long* phase_mask,
+                                     void* stream_);
 extern "C" int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, const float* bias, int n_img, int H,
                                   int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags,
                                   void* stream_) {
   return dtf_conv_halo_bf16_ex(src, W2d, out, bias, nullptr, n_img, H, W, C, KH, KW, n_out, pad_h, pad_w, mirror, flags,
-                               stream_);
+                               0, nullptr, stream_);
 }
 // Rows of the per-tile statistics buffer [rows][2][n_out] that dtf_conv_halo_bf16_ex fills (0: this geometry does
 // not run on the pixels-as-N kernel and cannot emit statistics).
@@ -1122,16 +1163,20 @@ extern "C" int dtf_conv_halo_stats_rows(int n_img, int H, int W, int C, int KH, 
 }
 // stats (optional): per pixel tile, the column sums and sums of squares of the fp32 results (bias included, before
 // the ReLU) -- the batch-norm statistics of the layer's output without another pass over it.
+// n_phase / phase_mask (host array, optional): the filter matrix has structurally zero (tap, channel-phase) blocks --
+// space-to-depth packed filters: channels (forward) or output channels (mirror) are n_phase equal groups and bit t of
+// phase_mask[g] says whether tap t has weights for group g; absent tiles are neither loaded nor multiplied.
 extern "C" int dtf_conv_halo_bf16_ex(const void* src, const void* W2d, void* out, const float* bias, float* stats,
                                      int n_img, int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w,
-                                     int mirror, int flags, void* stream_) {
+                                     int mirror, int flags, int n_phase, const unsigned long long* phase_mask,
+                                     void* stream_) {
   using namespace dtf::halo;
   if (KH > 7 || KW > 7) return DTF_ERR_UNSUPPORTED;
   EncodeTiledFn fn = encode_fn();
   if (!fn) return DTF_ERR_DRIVER;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PnHost h;
-  if (g_halo_persistent >= 2 && pn_setup(n_img, H, W, C, KH, KW, n_out, pad_h, pad_w, mirror, &h)) {
+  if (g_halo_persistent >= 2 && pn_setup(n_img, H, W, C, KH, KW, n_out, pad_h, pad_w, mirror, &h, n_phase, phase_mask)) {
     h.p.out = out; h.p.bias = bias; h.p.relu = flags & 1; h.p.stats = stats;
     CUtensorMap tx, tw;
     cuuint32_t es4[4] = {1, 1, 1, 1};

@@ -196,6 +196,44 @@ __global__ void pack_window_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfl
     st8(P + idx * 8, v);
   }
 }
+// Space-to-depth (INVERSE = false: P[n, j, i, ((r*2+q)*C + c)] = x[n, 2j+r, 2i+q, c], zeros outside) and its inverse
+// (dx[n, y, x, c] = dP[n, y/2, x/2, ...]) as plain 16-byte gathers with four independent loads in flight per thread.
+template <bool INVERSE>
+__global__ void __launch_bounds__(256)
+s2d_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, int n_img, int H, int W, int C,
+           int Hp, int Wq) {
+  const int cpr = INVERSE ? C / 8 : C / 2;  // 16-byte chunks per destination pixel
+  const long long total = INVERSE ? (long long)n_img * H * W * cpr : (long long)n_img * Hp * Wq * cpr;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  constexpr int U = 4;
+  for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < total; i0 += U * stride) {
+    BF8 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[u].v[k] = __floats2bfloat162_rn(0.f, 0.f);
+      const long long idx = i0 + u * stride;
+      if (idx < total) {
+        int c8, b, a, n;
+        if (INVERSE) {
+          split4(idx, cpr, W, H, c8, b, a, n);  // destination pixel (a = y, b = x) of the full-resolution tensor
+          const int j = a >> 1, i = b >> 1, slot = (a & 1) * 2 + (b & 1);
+          v[u] = ld8(src + (((long long)n * Hp + j) * Wq + i) * (4LL * C) + slot * C + c8 * 8);
+        } else {
+          split4(idx, cpr, Wq, Hp, c8, b, a, n);  // destination pixel (a = j, b = i) of the packed tensor
+          const int ch = c8 * 8, slot = ch / C, c = ch - slot * C;
+          const int y = 2 * a + (slot >> 1), xx = 2 * b + (slot & 1);
+          if (y < H && xx < W) v[u] = ld8(src + (((long long)n * H + y) * W + xx) * C + c);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long idx = i0 + u * stride;
+      if (idx < total) st8(dst + idx * 8, v[u]);
+    }
+  }
+}
 // Tap-packing (cs == C, all kwn horizontal taps of rp rows) with the source rows staged compactly in shared memory:
 // P[n, j, i, r*kwn*C + t] = row_r[(sx*i - ox)*C + t], a contiguous window of the C-channel row. One block per (n, j).
 __global__ void __launch_bounds__(256)
@@ -1231,6 +1269,11 @@ extern "C" int dtf_pack_window(const void* x, void* P, int n_img, int H, int W, 
   PackParams p{n_img, H, W, Cx, C, Hp, Wq, Cp, rp, kwn, sx, cs, oy, ox};
   const long long total = (long long)n_img * Hp * Wq * (Cp / 8);
   const bool vec = (cs % 8 == 0) && (C % 8 == 0) && (Cx % 8 == 0);
+  if (vec && rp == 2 && kwn == 2 && sx == 2 && cs == C && C == Cx && oy == 0 && ox == 0 && Cp == 4 * C) {
+    s2d_kernel<false><<<grid_for(total / 4 + 1, 256), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)P,
+                                                                           n_img, H, W, C, Hp, Wq);
+    return DTF_CHECK_LAUNCH();
+  }
   if (!vec && cs == C && rp <= 2 && (size_t)rp * W * C * 2 <= 48 * 1024) {
     const long long rows = (long long)n_img * Hp;
     pack_taps_kernel<<<(int)(rows < 148 * 16 ? rows : 148 * 16), 256, (size_t)rp * W * C * 2, ST(stream)>>>(
@@ -1246,6 +1289,11 @@ extern "C" int dtf_pack_window(const void* x, void* P, int n_img, int H, int W, 
 extern "C" int dtf_unpack_s2d(const void* dP, void* dx, int n_img, int H, int W, int C, int Hp, int Wq, int oy, int ox,
                               void* stream) {
   if (C % 8) return DTF_ERR_ALIGN;
+  if (oy == 0 && ox == 0 && 2 * Hp >= H && 2 * Wq >= W) {
+    s2d_kernel<true><<<grid_for((long long)n_img * H * W * (C / 8) / 4 + 1, 256), 256, 0, ST(stream)>>>(
+        (const __nv_bfloat16*)dP, (__nv_bfloat16*)dx, n_img, H, W, C, Hp, Wq);
+    return DTF_CHECK_LAUNCH();
+  }
   unpack_s2d_kernel<<<grid_for((long long)n_img * H * W * (C / 8), 256), 256, 0, ST(stream)>>>(
       (const __nv_bfloat16*)dP, (__nv_bfloat16*)dx, n_img, H, W, C, Hp, Wq, oy, ox);
   return DTF_CHECK_LAUNCH();

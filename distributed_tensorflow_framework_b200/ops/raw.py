@@ -90,6 +90,7 @@ def upsample_zero(dy, in_hw, s):
 
 # ------------------------------------------------------------------------------------------------ window packing
 USE_PACK = True  # strided KxK and few-channel convolutions run as stride-1 halo convolutions over packed windows
+USE_TAP_MASKS = True  # skip the structurally zero (tap, phase) weight tiles of space-to-depth packed filters
 _PLANS = {}
 
 
@@ -120,6 +121,15 @@ class _PackPlan(object):
         self.KW2 = max(t[3] for t in self.taps) - bmin + 1
         self.pad_h2, self.pad_w2 = -amin, -bmin
         self.taps = [(kh, kw, (a - amin) * self.KW2 + (b - bmin), slot) for (kh, kw, a, b, slot) in self.taps]
+        # space-to-depth: which packed taps carry weights for each of the 4 pixel phases (the halo kernel skips the
+        # structurally zero (tap, phase) weight tiles)
+        self.n_phase, self.phase_mask = 0, None
+        if mode == "s2d":
+            import ctypes
+            masks = [0, 0, 0, 0]
+            for (_, _, tap2, slot) in self.taps:
+                masks[slot] |= 1 << tap2
+            self.n_phase, self.phase_mask = 4, (ctypes.c_ulonglong * 4)(*masks)
         self._descs = {}
 
     def descs(self, kind, n_out, device, flip=False):
@@ -191,7 +201,8 @@ def _packed_fprop(x, w2d, bias, plan, relu, flip=False, keep=None, stats=None):
     out = torch.empty((n, plan.Hp, plan.Wq, n_out), device=x.device, dtype=bf16)
     part = _halo_stats_buffer(stats, relu, n, plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out, x.device)
     _lib.call("dtf_conv_halo_bf16_ex", P, Wp, out, bias, part, n, plan.Hp, plan.Wq, plan.Cp, plan.KH2, plan.KW2, n_out,
-              plan.pad_h2, plan.pad_w2, 0, 1 if relu else 0, _sp())
+              plan.pad_h2, plan.pad_w2, 0, 1 if relu else 0, plan.n_phase if USE_TAP_MASKS else 0, plan.phase_mask,
+              _sp())
     return out
 
 
@@ -228,7 +239,7 @@ def conv_fprop(x, w2d, bias, KH, KW, stride=1, relu=False, out_fp32=False, c_use
         # halo-tile kernel: one TMA load per tile, all taps are shifted views of the same shared-memory tile
         part = _halo_stats_buffer(stats, relu, n, H, W, C, KH, KW, n_out, x.device)
         _lib.call("dtf_conv_halo_bf16_ex", x, w2d, out, bias, part, n, H, W, C, KH, KW, n_out, pt, pl, 0,
-                  1 if relu else 0, _sp())
+                  1 if relu else 0, 0, None, _sp())
         return out
     flags = (1 if relu else 0) | (2 if out_fp32 else 0)
     _lib.call("dtf_conv_igemm_bf16", x, w2d, out, bias, n, H, W, C, OH, OW, KH, KW, n_out, stride, pt, pl, 0, flags,
@@ -261,8 +272,8 @@ def conv_dgrad(dy, w2d_t, in_hw, KH, KW, stride=1, bias=None, relu=False, addend
                 WpT = torch.zeros((plan.KH2 * plan.KW2 * Co, plan.Cp), device=dy.device, dtype=bf16)
                 _block_copy(w2d_t, WpT, plan.descs("wt", Co, dy.device))
                 dP = torch.empty((n, OH, OW, plan.Cp), device=dy.device, dtype=bf16)
-                _lib.call("dtf_conv_halo_bf16", dy, WpT, dP, None, n, OH, OW, Co, plan.KH2, plan.KW2, plan.Cp,
-                          plan.pad_h2, plan.pad_w2, 1, 0, _sp())
+                _lib.call("dtf_conv_halo_bf16_ex", dy, WpT, dP, None, None, n, OH, OW, Co, plan.KH2, plan.KW2, plan.Cp,
+                          plan.pad_h2, plan.pad_w2, 1, 0, plan.n_phase if USE_TAP_MASKS else 0, plan.phase_mask, _sp())
                 dx = torch.empty((n, H, W, Ci), device=dy.device, dtype=bf16)
                 _lib.call("dtf_unpack_s2d", dP, dx, n, H, W, Ci, OH, OW, 0, 0, _sp())
                 return dx

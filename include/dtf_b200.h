@@ -69,7 +69,7 @@ int dtf_conv_halo_bf16(const void* src, const void* W2d, void* out, const float*
                        int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags, void* stream);
 int dtf_conv_halo_bf16_ex(const void* src, const void* W2d, void* out, const float* bias, float* stats, int n_img,
                           int H, int W, int C, int KH, int KW, int n_out, int pad_h, int pad_w, int mirror, int flags,
-                          void* stream);
+                          int n_phase, const unsigned long long* phase_mask, void* stream);
 int dtf_conv_halo_stats_rows(int n_img, int H, int W, int C, int KH, int KW, int n_out);
 
 /* Halo-tile filter gradient (stride 1, C % 64 == 0, n_out % 64 == 0, <= 16 taps): x halo + dy tile per image tile,

@@ -194,3 +194,19 @@ def test_gather_conv_with_more_than_65535_row_tiles(raw):
     for img in (0, n - 1):  # the last image lives in the tiles beyond 65535
         ref = F.conv2d(x[img:img + 1].float().permute(0, 3, 1, 2), w.float().permute(3, 2, 0, 1), padding=1)
         close(y[img:img + 1], ref.permute(0, 2, 3, 1))
+
+
+def test_tap_masks_do_not_change_the_result(raw):
+    """Skipping the structurally zero weight tiles of a space-to-depth packed stride-2 convolution is exact."""
+    n, H, C, Co = 3, 28, 128, 256
+    x, dy = rnd(n, H, H, C), rnd(n, H // 2, H // 2, Co)
+    w = (torch.randn(3, 3, C, Co, device="cuda") * 0.05).to(torch.bfloat16)
+    wt = w.permute(0, 1, 3, 2).contiguous().reshape(9 * Co, C)
+    got = (raw.conv_fprop(x, w.reshape(9 * C, Co), None, 3, 3, 2), raw.conv_dgrad(dy, wt, (H, H), 3, 3, 2))
+    raw.USE_TAP_MASKS = False
+    try:
+        ref = (raw.conv_fprop(x, w.reshape(9 * C, Co), None, 3, 3, 2), raw.conv_dgrad(dy, wt, (H, H), 3, 3, 2))
+    finally:
+        raw.USE_TAP_MASKS = True
+    for g, r in zip(got, ref):
+        assert torch.equal(g, r)
