@@ -18,6 +18,7 @@
 // SyncReplicasOptimizer push/apply + token queue (/root/reference/distribute_train.py:146-160), replica_device_setter
 // variable placement (:109-110), done queue (:43-46,86-90,202-204).
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <string.h>
@@ -464,8 +465,21 @@ static OptimArgs make_optim(int kind, float lr, float b1, float b2, float eps, f
   if (kind == 2) o.lr_t = lr * sqrtf(1.f - powf(b2, (float)step)) / (1.f - powf(b1, (float)step));
   return o;
 }
+// Threads per collective CTA (DTF_COMM_THREADS, default 512). Smaller CTAs (256 / 128 threads, 64 registers) were tried
+// so that collective CTAs could sit next to the persistent compute CTAs; the 2-GPU step time did not move (26.0 ms in
+// every variant: the multi-GPU step is paced by the slowest GPU of the group, not by the collectives), and the
+// stand-alone collective got slower, so the full-size CTAs stay.
+static int comm_threads() {
+  static int t = 0;
+  if (t == 0) {
+    const char* e = getenv("DTF_COMM_THREADS");
+    t = e ? atoi(e) : 512;
+    if (t < 32 || t > 512 || (t & 31)) t = 512;
+  }
+  return t;
+}
 static int comm_grid(long long n4, int want) {
-  long long g = (n4 + 511) / 512;
+  long long g = (n4 + comm_threads() - 1) / comm_threads();
   if (g < 1) g = 1;
   if (g > want) g = want;
   if (g > MAX_COMM_BLOCKS) g = MAX_COMM_BLOCKS;
@@ -482,7 +496,7 @@ extern "C" int dtf_comm_allreduce_optim(void* comm, size_t grad_off, long long s
   if (master == nullptr && avg_out == nullptr) return DTF_ERR_ARG;
   const OptimArgs o = make_optim(kind, lr, b1, b2, eps, wd, gscale, step);
   const int grid = comm_grid(count >> 2, blocks);
-  allreduce_optim_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, start, count, o, master, m, v,
+  allreduce_optim_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, start, count, o, master, m, v,
                                                                (__nv_bfloat16*)shadow, avg_out);
   return DTF_CHECK_LAUNCH();
 }
@@ -510,10 +524,10 @@ extern "C" int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long
     np.n = k + 1;
   }
   if (c->ctx.mc != nullptr && master_off == (size_t)-1)
-    rs_optim_ag_nvls_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
+    rs_optim_ag_nvls_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
                                                                   np);
   else
-    rs_optim_ag_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
+    rs_optim_ag_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
                                                              master_off, np);
   return DTF_CHECK_LAUNCH();
 }
@@ -528,7 +542,7 @@ extern "C" int dtf_comm_allgather_slices(void* comm, size_t buf_off, const long 
     if (r > 0 && bounds16[r] - bounds16[r - 1] > maxn) maxn = bounds16[r] - bounds16[r - 1];
   }
   if (buf_off & 15) return DTF_ERR_ALIGN;
-  allgather_slices_kernel<<<comm_grid(maxn, blocks), 512, 0, dtf_stream(stream)>>>(c->ctx, buf_off, b);
+  allgather_slices_kernel<<<comm_grid(maxn, blocks), comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, buf_off, b);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_comm_async_push(void* comm, size_t grad_off, size_t mailbox_off, long long slice_cap,
@@ -542,7 +556,7 @@ extern "C" int dtf_comm_async_push(void* comm, size_t grad_off, size_t mailbox_o
   }
   if ((slice_cap & 3) || (grad_off & 15) || (mailbox_off & 15)) return DTF_ERR_ALIGN;
   int grid = blocks < 1 ? 1 : (blocks > MAX_COMM_BLOCKS ? MAX_COMM_BLOCKS : blocks);
-  async_push_kernel<<<grid, 512, 0, dtf_stream(stream)>>>(c->ctx, grad_off, mailbox_off, slice_cap, b, version);
+  async_push_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, mailbox_off, slice_cap, b, version);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_comm_async_apply(void* comm, size_t mailbox_off, long long slice_cap, const long long* bounds,
@@ -556,7 +570,7 @@ extern "C" int dtf_comm_async_apply(void* comm, size_t mailbox_off, long long sl
   int grid = blocks < 1 ? 1 : (blocks > MAX_COMM_BLOCKS ? MAX_COMM_BLOCKS : blocks);
   cudaStream_t st = dtf_stream(stream);
   async_snapshot_kernel<<<1, 32, 0, st>>>(c->ctx, applied_out_dev);
-  async_apply_kernel<<<grid, 512, 0, st>>>(c->ctx, mailbox_off, slice_cap, b, o, master, m, v, shadow_off,
+  async_apply_kernel<<<grid, comm_threads(), 0, st>>>(c->ctx, mailbox_off, slice_cap, b, o, master, m, v, shadow_off,
                                            applied_out_dev);
   async_commit_kernel<<<1, 32, 0, st>>>(c->ctx, applied_out_dev);
   return DTF_CHECK_LAUNCH();
