@@ -21,7 +21,8 @@ def _str2bool(v):
 
 _DEFS = [
     # name, type, default, help                                         (reference line)
-    ("use_fp16", _str2bool, False, "Train the model using fp16 variables."),  # :10
+    ("use_fp16", _str2bool, False, "Train the model using fp16 variables (accepted for compatibility: the CUDA path "
+     "always computes in bf16 over fp32 master weights, the CPU oracle path stays fp32)."),  # :10
     ("project_name", str, "distribute", "Name of the project."),  # :14
     ("job_name", str, "", "One of 'ps', 'worker'."),  # :16
     ("ps_hosts", str, "", "Comma-separated list of hostname:port pairs."),  # :18
