@@ -252,8 +252,28 @@ def measure_allreduce(trainer, world, device, barrier, iters=10):
     frozen = dtf.GradientDescentOptimizer(0.0)  # lr 0: the owner update leaves the weights unchanged
     t_rs = timed(lambda: eng.comm.rs_optim_ag(goff, st.owner_bounds, frozen, 1, st.master_arena, None, None,
                                               eng.heap.offset_of("shadow"), stream=cur))
+    # B-NCCL-PS: the parameter-server data path on library collectives -- ncclReduceScatter of the fp32 gradients,
+    # owner-shard SGD update (one elementwise kernel), ncclAllGather of the bf16 weights
+    t_ps = None
+    try:
+        shard = (n // world) // 8 * 8
+        if shard > 0:
+            g_in = st.grad_arena[:shard * world].clone()
+            g_out = torch.empty(shard, device=device, dtype=torch.float32)
+            w_master = torch.zeros(shard, device=device, dtype=torch.float32)
+            w_bf16 = torch.empty(shard, device=device, dtype=torch.bfloat16)
+            w_all = torch.empty(shard * world, device=device, dtype=torch.bfloat16)
+
+            def nccl_ps():
+                dist.reduce_scatter_tensor(g_out, g_in)
+                w_master.add_(g_out, alpha=-0.0)
+                w_bf16.copy_(w_master)
+                dist.all_gather_into_tensor(w_all, w_bf16)
+            t_ps = timed(nccl_ps)
+    except Exception as e:  # an older torch without the tensor collectives: leave the entry empty
+        t_ps = None
     f = 2.0 * (world - 1) / world
-    return {"bytes": nbytes, "k_rs_opt_ms": t_rs,
+    return {"bytes": nbytes, "k_rs_opt_ms": t_rs, "nccl_rs_opt_ag_ms": t_ps,
             "k_rs_opt_bus_gbs": (world - 1) / world * (nbytes + nbytes / 2) / t_rs / 1e6, "k_ar_ms": t_ar, "k_ar_bus_gbs": f * nbytes / t_ar / 1e6,
             "nccl_ms": t_nccl, "nccl_bus_gbs": f * nbytes / t_nccl / 1e6,
             "k_ar_frac_of_770": f * nbytes / t_ar / 1e6 / 770.0,
