@@ -9,7 +9,6 @@ optimizer.compute_gradients of /root/reference/distribute_tower.py:26-27).
 import torch
 
 from ..ops import raw
-from . import variables as V
 
 bf16 = torch.bfloat16
 

@@ -9,8 +9,6 @@ CUDA path: the whole step (zero-grad, forward, loss, backward with bucketed fuse
 optimizer, shadow refresh) can be captured ONCE into a CUDA graph and replayed; inputs are copied from pinned host
 memory into static device buffers before every replay, and step-dependent optimizer scalars live in device memory.
 """
-import time
-from typing import Optional
 
 import torch
 

@@ -15,7 +15,7 @@ from __future__ import annotations
 import contextlib
 import math
 import threading
-from typing import Callable, Dict, List, Optional, Sequence
+from typing import Callable, Dict, List, Optional
 
 import torch
 

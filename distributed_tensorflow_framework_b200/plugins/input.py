@@ -12,7 +12,6 @@ the placeholder path builds its queue once and feeds every tower (Q10).
 """
 import abc
 import multiprocessing
-import os
 import queue
 import random
 import threading

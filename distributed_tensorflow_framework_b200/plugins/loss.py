@@ -5,7 +5,6 @@ Built-ins cover the reference's implied workloads: softmax cros
 """
 import abc
 
-import torch
 import torch.nn.functional as F
 
 from ..api import annotations as _ann

@@ -10,7 +10,7 @@ Host strings are whitespace-stripped.
 import datetime
 import os
 import time
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 from ..api import log as logger
 

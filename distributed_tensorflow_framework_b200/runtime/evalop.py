@@ -10,7 +10,6 @@ import os
 
 import torch
 
-from ..api import flags
 from ..api import log as logger
 from ..engine import layers, variables as V
 from ..io import tensorbundle as tb

@@ -7,7 +7,7 @@ ps tasks in creation order). Here a "ps device" is the owner shard of a GPU rank
 variable (or a (op_type, name) pair) to a device string, and `owner_map` gives the parameter -> owner-rank table
 that the K-RS-OPT / async kernels use.
 """
-from typing import Callable, Iterable, List, Optional
+from typing import Iterable, List
 
 PS_OPS = ["Variable", "VariableV2", "VarHandleOp"]
 

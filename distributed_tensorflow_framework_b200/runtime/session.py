@@ -9,7 +9,6 @@ Checkpoints use the TF1 Saver V2 layout (io/tensorbundle.py): model.ckpt-<step>.
 `checkpoint` state file, keys = variable names, `global_step` int64, optimizer slots under TF names.
 """
 import os
-import time
 
 import numpy as np
 import torch

@@ -19,7 +19,7 @@ Two backends share the protocol:
 """
 import queue
 import threading
-from typing import Dict, List, Optional
+from typing import Dict
 
 import torch
 

@@ -15,7 +15,6 @@ import time
 import torch
 
 from ..api import annotations
-from ..api import constants as constant
 from ..api import flags
 from ..api import log as logger
 from ..engine.trainer import Trainer
