@@ -46,6 +46,7 @@ _DEFS = [
     ("comm_algo", str, "auto", "auto | oneshot | twoshot | nccl (gradient collective)."),
     ("placement", str, "bytes", "Owner-shard policy: bytes | round_robin (replica_device_setter order)."),
     ("save_checkpoint_secs", int, 600, "Chief checkpoint cadence in seconds (distribute_train.py:175)."),
+    ("metrics_jsonl", str, "", "Append machine-readable step metrics (JSON lines) to this file; empty = off."),
     ("compute_dtype", str, "bf16", "bf16 | fp32 compute on the CUDA path."),
     ("lrn_compat_noop", _str2bool, False, "Reproduce the reference's `norm` no-op (distribute_tools.py:183-187)."),
 ]

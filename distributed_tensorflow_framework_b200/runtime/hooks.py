@@ -5,6 +5,7 @@ MonitoredTrainingSession installs for the reference (/root/reference/distribute_
 `ExamplesPerSecondHook` is /root/reference/distribute_utils.py:57-116 (average and current examples/sec every N
 steps or seconds; exactly one of the two intervals must be given).
 """
+import json
 import time
 
 from ..api import log as logger
@@ -207,3 +208,49 @@ class HeartbeatHook(SessionRunHook):
             elif now - self._last_change.get(r, now) > self._timeout:
                 from .session import WorkerLostError
                 raise WorkerLostError("rank %d silent for %.0f s" % (r, now - self._last_change[r]))
+
+
+class MetricsJsonlHook(SessionRunHook):
+    """Machine-readable training metrics (extension): one JSON object per line every N steps with the
+    step, the loss (if the step function returned one), wall-clock examples/sec over the interval and -- when a
+    `device_ms_fn` is given (e.g. a CUDA-event timer of the trainer) -- the device-timed milliseconds per step.
+    The file is opened in append mode, so a resumed run continues the same log."""
+
+    def __init__(self, path, batch_size, every_n_steps=10, device_ms_fn=None, extra=None):
+        self._path, self._batch, self._every = path, int(batch_size), int(every_n_steps)
+        self._device_ms_fn, self._extra = device_ms_fn, dict(extra or {})
+        self._t0 = self._step0 = None
+        self._f = None
+
+    def begin(self):
+        self._f = open(self._path, "a", buffering=1)
+
+    def after_create_session(self, session):
+        self._t0, self._step0 = time.time(), session.global_step
+
+    def after_run(self, run_context, run_values):
+        step = run_context.session.global_step
+        if self._f is None or self._t0 is None or step % self._every != 0 or step == self._step0:
+            return
+        now = time.time()
+        rec = {"step": int(step), "time": now,
+               "examples_per_sec": self._batch * (step - self._step0) / max(now - self._t0, 1e-9)}
+        if isinstance(run_values, dict):
+            loss = run_values.get("loss")
+        else:
+            loss = run_values[0] if isinstance(run_values, (tuple, list)) and run_values else run_values
+        try:
+            if loss is not None:
+                rec["loss"] = float(loss)
+        except (TypeError, ValueError):
+            pass
+        if self._device_ms_fn is not None:
+            rec["device_ms_per_step"] = float(self._device_ms_fn())
+        rec.update(self._extra)
+        self._f.write(json.dumps(rec) + "\n")
+        self._t0, self._step0 = now, step
+
+    def end(self, session):
+        if self._f is not None:
+            self._f.close()
+            self._f = None

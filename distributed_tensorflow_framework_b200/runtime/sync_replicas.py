@@ -68,6 +68,40 @@ class ConditionalAccumulator(object):
             return mean
 
 
+class _TokenQueue(object):
+    """The shared token FIFO of SyncReplicasOptimizer with one guard the TF queue does not have: a worker is never
+    handed a second token of the step it already adopted. With a plain FIFO a fast worker can take two tokens of
+    step s, push twice for step s+1 and starve a slow worker; in TF the run continues and the stale push is simply
+    dropped, but with a fixed number of iterations per worker (tests, epoch-bounded jobs) the missing contribution
+    stalls the last aggregation. Seeded tokens (replicas_to_aggregate > total_num_replicas: a worker must contribute
+    more than once per step) are exempt."""
+
+    def __init__(self):
+        self._cv = threading.Condition()
+        self._items = []  # (step, seeded)
+
+    def put(self, step, seeded=False):
+        with self._cv:
+            self._items.append((int(step), bool(seeded)))
+            self._cv.notify_all()
+
+    def qsize(self):
+        with self._cv:
+            return len(self._items)
+
+    def get(self, timeout=None, after_step=None):
+        def pick():
+            for i, (step, seeded) in enumerate(self._items):
+                if seeded or after_step is None or step > after_step:
+                    return i
+            return None
+
+        with self._cv:
+            if not self._cv.wait_for(lambda: pick() is not None, timeout=timeout):
+                raise queue.Empty()
+            return self._items.pop(pick())[0]
+
+
 class InProcessParameterServer(object):
     """Shared "ps" state for worker threads: parameters, accumulators, token queue, done queue, global step."""
 
@@ -79,7 +113,7 @@ class InProcessParameterServer(object):
         self.vars = store.trainable_variables()
         self.accumulators: Dict[str, ConditionalAccumulator] = {
             v.name: ConditionalAccumulator(v.master.shape) for v in self.vars}
-        self.token_queue: "queue.Queue[int]" = queue.Queue()
+        self.token_queue = _TokenQueue()
         self.done_queue: "queue.Queue[int]" = queue.Queue()
         self.global_step = 0
         self._lock = threading.Lock()
@@ -95,7 +129,7 @@ class InProcessParameterServer(object):
             # seeded (replicas_to_aggregate > total_num_replicas), so workers move in lock-step with the global step.
             num_tokens = max(0, self.replicas_to_aggregate - self.total_num_replicas)
         for _ in range(num_tokens):
-            self.token_queue.put(self.global_step)
+            self.token_queue.put(self.global_step, seeded=True)
         if self._runner is None:
             self._runner = threading.Thread(target=self._chief_loop, daemon=True)
             self._runner.start()
@@ -139,8 +173,10 @@ class InProcessParameterServer(object):
                 accepted += 1
         return accepted
 
-    def take_token(self, timeout=None):
-        return self.token_queue.get(timeout=timeout)
+    def take_token(self, timeout=None, after_step=None):
+        """One token = permission to start the next step. `after_step`: the step of the token this worker took last;
+        it will not be handed a second token of that same step (see _TokenQueue)."""
+        return self.token_queue.get(timeout=timeout, after_step=after_step)
 
 
 class SyncReplicasOptimizer(object):
@@ -158,6 +194,7 @@ class SyncReplicasOptimizer(object):
         self._group = group
         self._server = server
         self._local_step = 0
+        self._last_token = None  # step of the last token taken from the fake backend
         self._gradients_applied = False
         if use_locking:
             logger.warn("use_locking=True is ignored: owner-side updates are lock-free by design")
@@ -176,7 +213,8 @@ class SyncReplicasOptimizer(object):
         store = store or V.default_store()
         if self._backend is not None:  # fake backend: worker thread
             self._backend.push(grads_and_vars, self._local_step)
-            self._local_step = self._backend.take_token()
+            self._local_step = self._backend.take_token(after_step=self._last_token)
+            self._last_token = self._local_step
             return self._local_step
         world = self.total_num_replicas
         if self._engine is not None:  # CUDA: fused peer-memory collective (+ optimizer)

@@ -139,6 +139,9 @@ class Train(object):
             session_hooks.append(sync_replicas_hook)
         if trainer.engine is not None and trainer.engine.comm is not None and num_workers > 1:
             session_hooks.append(H.HeartbeatHook(trainer.engine.comm, every_n_steps=50, timeout_s=120.0))
+        if flags.FLAGS.metrics_jsonl:
+            session_hooks.append(H.MetricsJsonlHook(flags.FLAGS.metrics_jsonl, self.batch_size * num_devices * num_workers,
+                                                    every_n_steps=10, extra={"rank": self.task_index}))
         session_hooks += list(getattr(self, "extra_hooks", []))
         if flags.FLAGS.log_device_placement:  # honoured here; the reference hard-codes False (distribute_train.py:176-178)
             for v in store.all_variables():

@@ -45,7 +45,7 @@ def test_sync_replicas_all_workers_mean_and_token_barrier():
             g = torch.full((4,), float(i + 1))
             steps_seen[i].append(opt.apply_gradients([(g, v)]))
 
-    ts = [threading.Thread(target=worker, args=(i,)) for i in range(3)]
+    ts = [threading.Thread(target=worker, args=(i,), daemon=True) for i in range(3)]
     [t.start() for t in ts]
     [t.join(10) for t in ts]
     ps.stop()
@@ -220,15 +220,25 @@ else:
     print("PS_EXIT", flush=True)
 ''' % (ROOT, str(tmp_path), p_ps, p_w0, p_w1))
     env = dict(os.environ, OMP_NUM_THREADS="2")
+    import time as _time
+    logs = [tmp_path / ("out_%d.log" % i) for i in range(3)]
+    files = [open(l, "w") for l in logs]
+    # output goes to files (a full pipe can never block a rank) and the three ranks share ONE deadline
     procs = [subprocess.Popen([sys.executable, str(script), "--job_name=%s" % j, "--task_index=%d" % t],
-                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env)
-             for j, t in (("ps", 0), ("worker", 0), ("worker", 1))]
+                              stdout=f, stderr=subprocess.STDOUT, text=True, env=env)
+             for f, (j, t) in zip(files, (("ps", 0), ("worker", 0), ("worker", 1)))]
     try:
-        outs = [p.communicate(timeout=240)[0] for p in procs]
+        deadline = _time.time() + 240
+        while _time.time() < deadline and any(p.poll() is None for p in procs):
+            _time.sleep(0.2)
     finally:
         for p in procs:
             if p.poll() is None:
                 p.kill()
+                p.wait()
+        for f in files:
+            f.close()
+    outs = [l.read_text() for l in logs]
     assert all(p.returncode == 0 for p in procs), "\\n".join(o[-1500:] for o in outs)
     assert "PS_EXIT" in outs[0]  # the ps left after both workers signalled the done queue
     r0 = [l for l in outs[1].splitlines() if l.startswith("RESULT")][0].split()
@@ -356,3 +366,25 @@ def test_session_recovers_from_lost_worker(tmp_path):
         while not sess.should_stop():
             sess.run(step)
     assert store.global_step == 5 and torch.allclose(v.master, torch.full((2,), 1.0 - 2.5))
+
+
+def test_metrics_jsonl_hook_writes_one_record_per_interval(tmp_path):
+    import json
+    from distributed_tensorflow_framework_b200.runtime import hooks as H
+
+    class FakeSession(object):
+        global_step = 0
+
+    sess, path = FakeSession(), str(tmp_path / "metrics.jsonl")
+    hook = H.MetricsJsonlHook(path, batch_size=32, every_n_steps=5, device_ms_fn=lambda: 1.5, extra={"rank": 0})
+    hook.begin()
+    hook.after_create_session(sess)
+    ctx = H.RunContext(sess)
+    for step in range(1, 21):
+        sess.global_step = step
+        hook.after_run(ctx, {"loss": 2.0 / step, "summaries": None})
+    hook.end(sess)
+    recs = [json.loads(l) for l in open(path)]
+    assert [r["step"] for r in recs] == [5, 10, 15, 20]
+    assert all(r["rank"] == 0 and r["device_ms_per_step"] == 1.5 and r["examples_per_sec"] > 0 for r in recs)
+    assert abs(recs[-1]["loss"] - 0.1) < 1e-9
