@@ -42,13 +42,36 @@ constexpr int MAIL_FLAG_OFF = CTR_OFF + MAX_COMM_BLOCKS;
 constexpr int APPLIED_OFF = MAIL_FLAG_OFF + MAX_RANKS;
 constexpr int DONE_CTR_OFF = APPLIED_OFF + MAX_RANKS;
 constexpr int HEARTBEAT_OFF = DONE_CTR_OFF + 8;
+//   [TICKET_OFF]                              arrival ticket counter of this owner (peers atom.add.sys into it)
+//   [ARRIVE_OFF, +MAX_RANKS)                  arrive[src_rank] = ticket + 1 of that rank's latest arrival (peers)
+//   [BK_CALL_OFF, +MAX_COMM_BLOCKS)           local per-block call counter of backup-worker collectives
+//   [PUSH_VER_OFF]                            local async push version (bumped in-kernel: survives graph replay)
+//   [OWNER_STEP_OFF, +MAX_RANKS)              owner_step[o]: number of updates owner o has applied (written by o)
+//   [BASE_STEP_OFF, +MAX_RANKS)               local snapshot of owner_step[] taken when this step's forward began
+//   [MAIL_BASE_OFF, +MAX_RANKS)               mail_base[src_rank]: owner step the pushed gradient was computed at
+//   [DROPPED_OFF]                             local count of async pushes dropped as too stale
+//   [ERR_OFF, +4)                             local error word: code, block, peer waited for, epoch
+constexpr int TICKET_OFF = HEARTBEAT_OFF + MAX_RANKS;
+constexpr int ARRIVE_OFF = TICKET_OFF + 8;
+constexpr int BK_CALL_OFF = ARRIVE_OFF + MAX_RANKS;
+constexpr int PUSH_VER_OFF = BK_CALL_OFF + MAX_COMM_BLOCKS;
+constexpr int OWNER_STEP_OFF = PUSH_VER_OFF + 8;
+constexpr int BASE_STEP_OFF = OWNER_STEP_OFF + MAX_RANKS;
+constexpr int MAIL_BASE_OFF = BASE_STEP_OFF + MAX_RANKS;
+constexpr int DROPPED_OFF = MAIL_BASE_OFF + MAX_RANKS;
+constexpr int ERR_OFF = DROPPED_OFF + 8;
 constexpr int FLAG_PAGE_BYTES = 8192;
-static_assert((HEARTBEAT_OFF + MAX_RANKS) * 4 <= FLAG_PAGE_BYTES, "flag page too small");
+static_assert((ERR_OFF + 4) * 4 <= FLAG_PAGE_BYTES, "flag page too small");
+
+constexpr uint32_t ERR_BARRIER_TIMEOUT = 1;  // a peer did not reach the barrier within the time bound
+constexpr uint32_t ERR_ARRIVAL_TIMEOUT = 2;  // fewer than replicas_to_aggregate gradients arrived within the bound
 
 struct CommCtx {
   int rank, world;
   uint8_t* peer[MAX_RANKS];  // heap base of every rank as mapped in this process (peer[rank] is local)
   uint8_t* mc;               // NVLS multicast mapping of the heap (nullptr when not available)
+  uint32_t* err_host;        // 4 words of mapped pinned host memory: the host watchdog reads them without a sync
+  unsigned long long timeout_ns;  // bound of every device-side wait (0 = wait forever)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -65,35 +88,76 @@ __device__ __forceinline__ float4 ld_cg_f4(const float4* p) {
   return v;
 }
 
-#ifndef DTF_COMM_SPIN_LIMIT
-#define DTF_COMM_SPIN_LIMIT (1ull << 31)
-#endif
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;\n" : "=l"(t));
+  return t;
+}
+
+// A wait that outlives the time bound records what it was waiting for -- in the local flag page (so that the
+// kernels queued behind this one drain immediately) and in mapped host memory (so that the host watchdog sees it
+// without synchronising) -- and makes the kernel return. No __trap(): the context stays usable, the host raises
+// WorkerLostError and the session reloads the last checkpoint.
+__device__ __noinline__ void report_timeout(const CommCtx& c, uint32_t code, uint32_t peer, uint32_t epoch) {
+  uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
+  if (atomicCAS(flags + ERR_OFF, 0u, code) == 0u) {
+    flags[ERR_OFF + 1] = blockIdx.x;
+    flags[ERR_OFF + 2] = peer;
+    flags[ERR_OFF + 3] = epoch;
+    if (c.err_host != nullptr) {
+      c.err_host[1] = blockIdx.x;
+      c.err_host[2] = peer;
+      c.err_host[3] = epoch;
+      __threadfence_system();
+      st_release_sys(c.err_host, code);
+    }
+  }
+}
+__device__ __forceinline__ bool comm_failed(const CommCtx& c) {
+  return reinterpret_cast<volatile uint32_t*>(c.peer[c.rank])[ERR_OFF] != 0u;
+}
 
 // Barrier among the same-index blocks of all ranks. Also orders memory: everything written (by this GPU) before the
-// barrier is visible to peers after it.
-__device__ void block_barrier(const CommCtx& c) {
+// barrier is visible to peers after it. Returns false (for every thread of the block) when a peer did not show up
+// within c.timeout_ns or an earlier wait on this rank already failed; the caller must then return at once.
+__device__ bool block_barrier(const CommCtx& c) {
   __syncthreads();
   uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
   __shared__ uint32_t epoch_s;
+  __shared__ int ok_s;
   if (threadIdx.x == 0) {
     __threadfence_system();
     const uint32_t e = flags[CTR_OFF + blockIdx.x] + 1;
     flags[CTR_OFF + blockIdx.x] = e;
     epoch_s = e;
+    ok_s = comm_failed(c) ? 0 : 1;
   }
   __syncthreads();
   const uint32_t e = epoch_s;
+  const bool healthy = ok_s != 0;
   if (threadIdx.x < c.world) {
     const int r = threadIdx.x;
     uint32_t* remote = reinterpret_cast<uint32_t*>(c.peer[r]) + blockIdx.x * MAX_RANKS + c.rank;
     st_release_sys(remote, e);
-    const uint32_t* mine = flags + blockIdx.x * MAX_RANKS + r;
-    unsigned long long spins = 0;
-    while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
-      if (++spins > DTF_COMM_SPIN_LIMIT) __trap();
+    if (healthy) {
+      const uint32_t* mine = flags + blockIdx.x * MAX_RANKS + r;
+      unsigned long long t0 = 0;
+      uint32_t spins = 0;
+      while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
+        if ((++spins & 1023u) == 0u && c.timeout_ns != 0ull) {
+          const unsigned long long now = globaltimer_ns();
+          if (t0 == 0) t0 = now;
+          if (now - t0 > c.timeout_ns || comm_failed(c)) {
+            report_timeout(c, ERR_BARRIER_TIMEOUT, (uint32_t)r, e);
+            ok_s = 0;
+            break;
+          }
+        }
+      }
     }
   }
   __syncthreads();
+  return ok_s != 0;
 }
 
 __device__ __forceinline__ uint2 pack4_bf16(float4 v) {
@@ -104,29 +168,18 @@ __device__ __forceinline__ uint2 pack4_bf16(float4 v) {
   return u;
 }
 
-__device__ __forceinline__ float4 reduce_peers(const CommCtx& c, size_t grad_off, long long i4) {
-  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-  for (int r = 0; r < MAX_RANKS; ++r) {
-    if (r < c.world) {
-      const float4 v = ld_cg_f4(reinterpret_cast<const float4*>(c.peer[r] + grad_off) + i4);
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-    }
-  }
-  return s;
-}
-
 // Remote loads cost ~2 us each: keep U independent 16-byte loads per peer in flight per thread. q0 is the first
 // float4 index of this thread, `stride` the distance between its U elements, n4 the range length (indices relative
-// to base4). Sums are formed in rank order, so every rank computes bit-identical results.
+// to base4). Sums are formed in rank order, so every rank computes bit-identical results. `mask` selects the ranks
+// whose gradients enter the sum (all ranks, or the first replicas_to_aggregate arrivals in backup-worker mode).
 constexpr int COMM_U = 4;
 __device__ __forceinline__ void reduce_peers_u(const CommCtx& c, size_t grad_off, long long base4, long long q0,
-                                               long long stride, long long n4, float4 (&s)[COMM_U]) {
+                                               long long stride, long long n4, uint32_t mask, float4 (&s)[COMM_U]) {
 #pragma unroll
   for (int u = 0; u < COMM_U; ++u) s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
   for (int r = 0; r < MAX_RANKS; ++r) {
-    if (r < c.world) {
+    if (r < c.world && ((mask >> r) & 1u)) {
       const float4* g = reinterpret_cast<const float4*>(c.peer[r] + grad_off) + base4;
       float4 v[COMM_U];
 #pragma unroll
@@ -156,14 +209,16 @@ __device__ __forceinline__ float4 optim4(const OptimArgs& o, float* master, floa
 // ---- K-AR: one-shot allreduce (+ optimizer). [start, start+count) in elements, multiples of 4.
 // If master == nullptr the averaged gradient is written to avg_out (plain allreduce-mean).
 __global__ void __launch_bounds__(512)
-allreduce_optim_kernel(CommCtx c, size_t grad_off, long long start, long long count, OptimArgs o, float* master,
-                       float* m, float* v, __nv_bfloat16* shadow, float* avg_out) {
-  block_barrier(c);
+allreduce_optim_kernel(CommCtx c, size_t grad_off, long long start, long long count, OptimArgs o,
+                       const float* __restrict__ hyper, float* master, float* m, float* v, __nv_bfloat16* shadow,
+                       float* avg_out) {
+  optim_load_hyper(o, hyper);
+  if (!block_barrier(c)) return;
   const long long n4 = count >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long q0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * COMM_U) {
     float4 gs[COMM_U];
-    reduce_peers_u(c, grad_off, start >> 2, q0, stride, n4, gs);
+    reduce_peers_u(c, grad_off, start >> 2, q0, stride, n4, 0xffffffffu, gs);
 #pragma unroll
     for (int u = 0; u < COMM_U; ++u) {
       const long long q = q0 + u * stride;
@@ -184,7 +239,9 @@ allreduce_optim_kernel(CommCtx c, size_t grad_off, long long start, long long co
 
 // ---- K-RS-OPT (+ all-gather by peer stores). bounds[r]..bounds[r+1] is rank r's owned element range (multiples
 // of 4). master/m/v are local (owner-side state); shadow_off / master_off are heap offsets of the replicated copies
-// that every peer receives (master_off may be SIZE_MAX to skip the fp32 broadcast).
+// that every peer receives. The fp32 master is broadcast only inside [f32_lo, f32_hi): the region of the arena that
+// holds the variables the forward / backward kernels read in fp32 (biases, batch-norm gamma / beta) -- without it a
+// non-owner would keep computing with the initial values of the parameters it does not own.
 struct Bounds {
   long long b[MAX_RANKS + 1];
 };
@@ -200,16 +257,86 @@ __device__ __forceinline__ bool in_nopush(const NoPush& np, long long i) {
     if (k < np.n && i >= np.lo[k] && i < np.hi[k]) hit = true;
   return hit;
 }
+struct PushF32 {
+  size_t master_off;
+  long long lo, hi;
+};
+
+// Backup workers (SyncReplicasOptimizer(replicas_to_aggregate = R < N), /root/reference/distribute_train.py:146-155):
+// every rank takes a ticket from each owner's arrival counter (a remote atomic in the owner's flag page -- served by
+// the owner's memory system, not its SMs) and publishes it; the owner aggregates the ranks whose ticket of this call
+// is among the first R, drops the rest (their gradient is stale by TF's rule) and the caller scales by 1/R. Each
+// owner decides for itself, exactly like TF's per-variable accumulators. Tickets of call k are k*N .. k*N+N-1: no
+// rank can arrive for call k+1 before every rank has arrived for call k (the exit barrier of call k needs them all).
+// Returns the bit mask of aggregated ranks, or 0 after a time-out.
+__device__ uint32_t backup_arrive_and_select(const CommCtx& c, int R) {
+  uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
+  __shared__ uint32_t mask_s;
+  __shared__ uint32_t call_s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    const uint32_t k = flags[BK_CALL_OFF + blockIdx.x];
+    flags[BK_CALL_OFF + blockIdx.x] = k + 1;
+    call_s = k;
+    mask_s = 0;
+  }
+  __syncthreads();
+  const uint32_t k = call_s;
+  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+    uint32_t* owner = reinterpret_cast<uint32_t*>(c.peer[threadIdx.x]);
+    const uint32_t t = atomicAdd_system(owner + TICKET_OFF, 1u);
+    st_release_sys(owner + ARRIVE_OFF + c.rank, t + 1u);
+  }
+  if (threadIdx.x == 0) {
+    const uint32_t lo = k * (uint32_t)c.world;
+    unsigned long long t0 = 0;
+    uint32_t spins = 0, mask = 0;
+    bool failed = comm_failed(c);
+    while (!failed) {
+      mask = 0;
+      int cnt = 0;
+      for (int r = 0; r < c.world; ++r) {
+        const uint32_t a = ld_acquire_sys(flags + ARRIVE_OFF + r);
+        const uint32_t ord = a - 1u - lo;  // wraps to a huge value for tickets of earlier calls
+        if (a != 0u && ord < (uint32_t)R) {
+          mask |= 1u << r;
+          ++cnt;
+        }
+      }
+      if (cnt >= R) break;
+      if ((++spins & 255u) == 0u && c.timeout_ns != 0ull) {
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        if (now - t0 > c.timeout_ns || comm_failed(c)) {
+          report_timeout(c, ERR_ARRIVAL_TIMEOUT, (uint32_t)cnt, k);
+          failed = true;
+        }
+      }
+    }
+    mask_s = failed ? 0u : mask;
+  }
+  __syncthreads();
+  return mask_s;
+}
+
 __global__ void __launch_bounds__(512)
-rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float* master, float* m, float* v,
-                   size_t shadow_off, size_t master_off, NoPush np) {
-  block_barrier(c);
+rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, const float* __restrict__ hyper,
+                   float* master, float* m, float* v, size_t shadow_off, PushF32 f32, NoPush np, int backup_r) {
+  optim_load_hyper(o, hyper);
+  uint32_t mask = 0xffffffffu;
+  if (backup_r > 0 && backup_r < c.world) {
+    mask = backup_arrive_and_select(c, backup_r);
+    if (mask == 0u) return;
+  } else if (!block_barrier(c)) {
+    return;
+  }
   const long long start = bounds.b[c.rank];
   const long long n4 = (bounds.b[c.rank + 1] - start) >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long q0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * COMM_U) {
     float4 gs[COMM_U];
-    reduce_peers_u(c, grad_off, start >> 2, q0, stride, n4, gs);
+    reduce_peers_u(c, grad_off, start >> 2, q0, stride, n4, mask, gs);
 #pragma unroll
     for (int u = 0; u < COMM_U; ++u) {
       const long long q = q0 + u * stride;
@@ -218,12 +345,13 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float
       const float4 p = optim4(o, master, m, v, i, gs[u]);
       const uint2 pb = pack4_bf16(p);
       const bool local_only = in_nopush(np, i);
+      const bool push_f32 = i >= f32.lo && i < f32.hi;
 #pragma unroll
       for (int r = 0; r < MAX_RANKS; ++r) {
         if (r < c.world && (!local_only || r == c.rank)) {
           *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[r] + shadow_off) + i) = pb;
-          if (master_off != (size_t)-1 && r != c.rank)
-            *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.peer[r] + master_off) + i) = p;
+          if (push_f32 && r != c.rank)
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.peer[r] + f32.master_off) + i) = p;
         }
       }
     }
@@ -248,10 +376,16 @@ __device__ __forceinline__ void multimem_st_b64(void* mc_addr, uint2 v) {
                "f"(__uint_as_float(v.y))
                : "memory");
 }
+__device__ __forceinline__ void multimem_st_f4(void* mc_addr, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};\n" ::"l"(mc_addr), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
 __global__ void __launch_bounds__(512)
-rs_optim_ag_nvls_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, float* master, float* m, float* v,
-                        size_t shadow_off, NoPush np) {
-  block_barrier(c);
+rs_optim_ag_nvls_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, const float* __restrict__ hyper,
+                        float* master, float* m, float* v, size_t shadow_off, PushF32 f32, NoPush np) {
+  optim_load_hyper(o, hyper);
+  if (!block_barrier(c)) return;
   const long long start = bounds.b[c.rank];
   const long long n4 = (bounds.b[c.rank + 1] - start) >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -274,6 +408,8 @@ rs_optim_ag_nvls_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, 
         *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[c.rank] + shadow_off) + i) = pb;
       else
         multimem_st_b64(reinterpret_cast<__nv_bfloat16*>(c.mc + shadow_off) + i, pb);
+      // the owner's own master was written by optim4; the multicast store rewrites it with the same value
+      if (i >= f32.lo && i < f32.hi) multimem_st_f4(reinterpret_cast<float*>(c.mc + f32.master_off) + i, p);
     }
   }
   block_barrier(c);
@@ -282,7 +418,7 @@ rs_optim_ag_nvls_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, 
 // ---- all-gather of owned slices by peer stores (16-byte units): used for checkpoint gathers and weight pulls.
 __global__ void __launch_bounds__(512)
 allgather_slices_kernel(CommCtx c, size_t buf_off, Bounds bounds16) {
-  block_barrier(c);
+  if (!block_barrier(c)) return;
   const long long start = bounds16.b[c.rank];
   const long long n = bounds16.b[c.rank + 1] - start;
   const uint4* src = reinterpret_cast<const uint4*>(c.peer[c.rank] + buf_off) + start;
@@ -295,11 +431,19 @@ allgather_slices_kernel(CommCtx c, size_t buf_off, Bounds bounds16) {
   block_barrier(c);
 }
 
-// ---- K-ASYNC-PUSH: copy my gradient slice for every owner into that owner's mailbox[me], then publish `version`.
-// mailbox layout on each rank: [world][slice_cap] floats at mailbox_off.
+// ---- K-ASYNC. The version stamps and step counters live in the flag page and are advanced by the kernels, so a
+// captured CUDA graph that replays push + apply keeps publishing NEW versions (a by-value version argument would be
+// frozen at capture and the owner would apply once and never again).
+// begin: remember which update of every owner this step's weights correspond to (the push is stamped with it).
+__global__ void async_begin_kernel(CommCtx c) {
+  uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
+  const int o = threadIdx.x;
+  if (o < c.world) flags[BASE_STEP_OFF + o] = ld_acquire_sys(flags + OWNER_STEP_OFF + o);
+}
+// push: copy my gradient slice for every owner into that owner's mailbox[me], then publish the next version together
+// with the owner step the gradient was computed at. mailbox layout on each rank: [world][slice_cap] floats.
 __global__ void __launch_bounds__(512)
-async_push_kernel(CommCtx c, size_t grad_off, size_t mailbox_off, long long slice_cap, Bounds bounds,
-                  uint32_t version) {
+async_push_kernel(CommCtx c, size_t grad_off, size_t mailbox_off, long long slice_cap, Bounds bounds) {
   const float4* grad = reinterpret_cast<const float4*>(c.peer[c.rank] + grad_off);
   for (int o = 0; o < c.world; ++o) {
     const long long s4 = bounds.b[o] >> 2, n4 = (bounds.b[o + 1] - bounds.b[o]) >> 2;
@@ -311,25 +455,34 @@ async_push_kernel(CommCtx c, size_t grad_off, size_t mailbox_off, long long slic
   __threadfence_system();
   __syncthreads();
   __shared__ bool last;
+  __shared__ uint32_t ver_s;
   uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
   if (threadIdx.x == 0) {
     const uint32_t prev = atomicAdd(flags + DONE_CTR_OFF, 1u);
     last = (prev == gridDim.x - 1);
+    if (last) {
+      ver_s = flags[PUSH_VER_OFF] + 1u;
+      flags[PUSH_VER_OFF] = ver_s;
+    }
   }
   __syncthreads();
   if (last) {
     __threadfence_system();
-    if (threadIdx.x < c.world)
-      st_release_sys(reinterpret_cast<uint32_t*>(c.peer[threadIdx.x]) + MAIL_FLAG_OFF + c.rank, version);
+    if (threadIdx.x < c.world) {
+      uint32_t* owner = reinterpret_cast<uint32_t*>(c.peer[threadIdx.x]);
+      owner[MAIL_BASE_OFF + c.rank] = flags[BASE_STEP_OFF + threadIdx.x];
+      st_release_sys(owner + MAIL_FLAG_OFF + c.rank, ver_s);
+    }
     if (threadIdx.x == 0) flags[DONE_CTR_OFF] = 0;
   }
 }
 // ---- owner-side apply: for every worker whose mailbox version is newer than the last applied one, apply its
 // (possibly stale) gradient to the owned shard and push the new bf16 weights to every rank. Never waits.
-// snap[w] (8 words, caller-provided) receives the version applied for worker w (0 = nothing new).
+// snap[w] (8 words, caller-provided) receives the version applied for worker w (0 = nothing new or dropped).
+// A push computed more than max_staleness owner updates ago is dropped (max_staleness < 0: no bound).
 // A worker may overwrite its mailbox while the owner reads it: like use_locking=False in the reference, a torn
 // (mixed-version) gradient is accepted.
-__global__ void async_snapshot_kernel(CommCtx c, uint32_t* snap) {
+__global__ void async_snapshot_kernel(CommCtx c, uint32_t* snap, int max_staleness) {
   // one consistent view of "what has arrived" for the whole apply grid
   uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
   const int w = threadIdx.x;
@@ -337,14 +490,24 @@ __global__ void async_snapshot_kernel(CommCtx c, uint32_t* snap) {
     uint32_t s = 0;
     if (w < c.world) {
       const uint32_t ver = ld_acquire_sys(flags + MAIL_FLAG_OFF + w);
-      if (ver != flags[APPLIED_OFF + w]) s = ver;
+      if (ver != flags[APPLIED_OFF + w]) {
+        s = ver;
+        const uint32_t age = flags[OWNER_STEP_OFF + c.rank] - flags[MAIL_BASE_OFF + w];
+        if (max_staleness >= 0 && (int32_t)age > max_staleness) {
+          s = 0;
+          flags[APPLIED_OFF + w] = ver;  // consumed without applying
+          atomicAdd(flags + DROPPED_OFF, 1u);
+        }
+      }
     }
     snap[w] = s;
   }
 }
 __global__ void __launch_bounds__(512)
-async_apply_kernel(CommCtx c, size_t mailbox_off, long long slice_cap, Bounds bounds, OptimArgs o, float* master,
-                   float* m, float* v, size_t shadow_off, const uint32_t* snap) {
+async_apply_kernel(CommCtx c, size_t mailbox_off, long long slice_cap, Bounds bounds, OptimArgs o,
+                   const float* __restrict__ hyper, float* master, float* m, float* v, size_t shadow_off, PushF32 f32,
+                   const uint32_t* snap) {
+  optim_load_hyper(o, hyper);
   const long long start = bounds.b[c.rank];
   const long long n4 = (bounds.b[c.rank + 1] - start) >> 2;
   for (int w = 0; w < c.world; ++w) {
@@ -355,16 +518,34 @@ async_apply_kernel(CommCtx c, size_t mailbox_off, long long slice_cap, Bounds bo
       const float4 g = ld_cg_f4(mail + q);
       const float4 p = optim4(o, master, m, v, i, g);
       const uint2 pb = pack4_bf16(p);
+      const bool push_f32 = i >= f32.lo && i < f32.hi;
 #pragma unroll
       for (int r = 0; r < MAX_RANKS; ++r)
-        if (r < c.world) *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[r] + shadow_off) + i) = pb;
+        if (r < c.world) {
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(c.peer[r] + shadow_off) + i) = pb;
+          if (push_f32 && r != c.rank)
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.peer[r] + f32.master_off) + i) = p;
+        }
     }
   }
 }
 __global__ void async_commit_kernel(CommCtx c, const uint32_t* snap) {
   uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
   const int w = threadIdx.x;
-  if (w < c.world && snap[w] != 0) flags[APPLIED_OFF + w] = snap[w];
+  __shared__ uint32_t napplied, base;
+  if (w == 0) {
+    napplied = 0;
+    base = flags[OWNER_STEP_OFF + c.rank];
+  }
+  __syncthreads();
+  if (w < c.world && snap[w] != 0) {
+    flags[APPLIED_OFF + w] = snap[w];
+    atomicAdd(&napplied, 1u);
+  }
+  __syncthreads();
+  // publish how many updates this owner has applied so far (the staleness clock of its shard) to every rank
+  if (napplied != 0 && w < c.world)
+    st_release_sys(reinterpret_cast<uint32_t*>(c.peer[w]) + OWNER_STEP_OFF + c.rank, base + napplied);
 }
 
 __global__ void barrier_kernel(CommCtx c) { block_barrier(c); }
@@ -378,6 +559,12 @@ __global__ void heartbeat_kernel(CommCtx c, uint32_t beat, uint32_t* seen_out) {
   }
 }
 
+// test / fault-injection helper: keep the stream busy for `ns` nanoseconds (an injected straggler)
+__global__ void sleep_kernel(unsigned long long ns) {
+  const unsigned long long t0 = globaltimer_ns();
+  while (globaltimer_ns() - t0 < ns) __nanosleep(1000);
+}
+
 }  // namespace dtf
 
 using namespace dtf;
@@ -386,6 +573,7 @@ struct DtfComm {
   CommCtx ctx;
   size_t heap_bytes;
   void* opened[MAX_RANKS];
+  uint32_t* err_host;  // mapped pinned host memory (4 words)
 };
 
 extern "C" int dtf_comm_flag_page_bytes(void) { return FLAG_PAGE_BYTES; }
@@ -395,14 +583,48 @@ extern "C" int dtf_comm_max_blocks(void) { return MAX_COMM_BLOCKS; }
 extern "C" int dtf_comm_heap_alloc(size_t bytes, void** ptr_out, void* handle_out64) {
   void* p = nullptr;
   if (cudaMalloc(&p, bytes) != cudaSuccess) return DTF_ERR_CUDA;
-  if (cudaMemset(p, 0, bytes) != cudaSuccess) return DTF_ERR_CUDA;
+  if (cudaMemset(p, 0, bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) {
+    cudaFree(p);
+    return DTF_ERR_CUDA;
+  }
   cudaIpcMemHandle_t h;
-  if (cudaIpcGetMemHandle(&h, p) != cudaSuccess) return DTF_ERR_CUDA;
+  if (cudaIpcGetMemHandle(&h, p) != cudaSuccess) {
+    cudaFree(p);
+    return DTF_ERR_CUDA;
+  }
   memcpy(handle_out64, &h, sizeof(h));
   *ptr_out = p;
-  return cudaDeviceSynchronize() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+  return DTF_OK;
 }
 extern "C" int dtf_comm_heap_free(void* ptr) { return cudaFree(ptr) == cudaSuccess ? DTF_OK : DTF_ERR_CUDA; }
+
+static unsigned long long default_timeout_ns() {
+  const char* e = getenv("DTF_COMM_TIMEOUT_MS");
+  const long long ms = e ? atoll(e) : 30000;
+  return ms <= 0 ? 0ull : (unsigned long long)ms * 1000000ull;
+}
+static void comm_finish_create(DtfComm* c) {
+  c->ctx.timeout_ns = default_timeout_ns();
+  c->err_host = nullptr;
+  void* h = nullptr;
+  if (cudaHostAlloc(&h, 64, cudaHostAllocMapped) == cudaSuccess) {
+    memset(h, 0, 64);
+    void* d = nullptr;
+    if (cudaHostGetDevicePointer(&d, h, 0) == cudaSuccess) {
+      c->err_host = reinterpret_cast<uint32_t*>(h);
+      c->ctx.err_host = reinterpret_cast<uint32_t*>(d);
+    } else {
+      cudaFreeHost(h);
+    }
+  }
+  (void)cudaGetLastError();
+}
+static void comm_release(DtfComm* c) {
+  for (int r = 0; r < MAX_RANKS; ++r)
+    if (c->opened[r]) cudaIpcCloseMemHandle(c->opened[r]);
+  if (c->err_host) cudaFreeHost(c->err_host);
+  delete c;
+}
 
 // handles: world x 64 bytes (all ranks' IPC handles, rank order). Returns an opaque communicator.
 extern "C" int dtf_comm_create(int rank, int world, void* local_heap, size_t heap_bytes, const void* handles,
@@ -422,12 +644,14 @@ extern "C" int dtf_comm_create(int rank, int world, void* local_heap, size_t hea
     memcpy(&h, reinterpret_cast<const uint8_t*>(handles) + (size_t)r * 64, sizeof(h));
     void* p = nullptr;
     if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
-      delete c;
+      (void)cudaGetLastError();
+      comm_release(c);  // closes the mappings opened so far
       return DTF_ERR_CUDA;
     }
     c->opened[r] = p;
     c->ctx.peer[r] = reinterpret_cast<uint8_t*>(p);
   }
+  comm_finish_create(c);
   *comm_out = c;
   return DTF_OK;
 }
@@ -440,14 +664,12 @@ extern "C" int dtf_comm_create_local(int rank, int world, void* const* heaps, si
   c->ctx.world = world;
   c->heap_bytes = heap_bytes;
   for (int r = 0; r < world; ++r) c->ctx.peer[r] = reinterpret_cast<uint8_t*>(heaps[r]);
+  comm_finish_create(c);
   *comm_out = c;
   return DTF_OK;
 }
 extern "C" int dtf_comm_destroy(void* comm) {
-  DtfComm* c = reinterpret_cast<DtfComm*>(comm);
-  for (int r = 0; r < MAX_RANKS; ++r)
-    if (c->opened[r]) cudaIpcCloseMemHandle(c->opened[r]);
-  delete c;
+  comm_release(reinterpret_cast<DtfComm*>(comm));
   return DTF_OK;
 }
 // Attach the NVLS multicast mapping of the heap (from cuMulticast* / torch symmetric memory); 0 detaches it.
@@ -456,6 +678,30 @@ extern "C" int dtf_comm_set_multicast(void* comm, void* mc_base) {
   return DTF_OK;
 }
 extern "C" void* dtf_comm_peer_ptr(void* comm, int r) { return reinterpret_cast<DtfComm*>(comm)->ctx.peer[r]; }
+// Bound of every device-side wait in milliseconds (0 = wait forever). Default 30 s, or DTF_COMM_TIMEOUT_MS.
+extern "C" int dtf_comm_set_timeout_ms(void* comm, long long ms) {
+  reinterpret_cast<DtfComm*>(comm)->ctx.timeout_ns = ms <= 0 ? 0ull : (unsigned long long)ms * 1000000ull;
+  return DTF_OK;
+}
+// Host watchdog: copies the 4-word error record (code, block, peer / arrivals, epoch) out of mapped host memory.
+// No CUDA call, no synchronisation: safe to poll from any thread while kernels run. Returns the code (0 = healthy).
+extern "C" int dtf_comm_error(void* comm, unsigned int* out4) {
+  DtfComm* c = reinterpret_cast<DtfComm*>(comm);
+  if (c->err_host == nullptr) return 0;
+  const volatile uint32_t* e = c->err_host;
+  const uint32_t code = e[0];
+  if (out4 != nullptr) {
+    out4[0] = code; out4[1] = e[1]; out4[2] = e[2]; out4[3] = e[3];
+  }
+  return (int)code;
+}
+// After a recovery (every rank reloaded the checkpoint and re-synchronised on the control plane) clear the record.
+extern "C" int dtf_comm_clear_error(void* comm, void* stream) {
+  DtfComm* c = reinterpret_cast<DtfComm*>(comm);
+  if (c->err_host) memset(c->err_host, 0, 16);
+  uint32_t* flags = reinterpret_cast<uint32_t*>(c->ctx.peer[c->ctx.rank]);
+  return cudaMemsetAsync(flags + ERR_OFF, 0, 16, dtf_stream(stream)) == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
+}
 
 static OptimArgs make_optim(int kind, float lr, float b1, float b2, float eps, float wd, float gscale,
                             long long step) {
@@ -466,8 +712,7 @@ static OptimArgs make_optim(int kind, float lr, float b1, float b2, float eps, f
   return o;
 }
 // Threads per collective CTA (DTF_COMM_THREADS, default 512). Smaller CTAs (256 / 128 threads, 64 registers) were tried
-// so that collective CTAs could sit next to the persistent compute CTAs; the 2-GPU step time did not move (26.0 ms in
-// every variant: the multi-GPU step is paced by the slowest GPU of the group, not by the collectives), and the
+// so that collective CTAs could sit next to the persistent compute CTAs; the 2-GPU step time did not move, and the
 // stand-alone collective got slower, so the full-size CTAs stay.
 static int comm_threads() {
   static int t = 0;
@@ -485,25 +730,36 @@ static int comm_grid(long long n4, int want) {
   if (g > MAX_COMM_BLOCKS) g = MAX_COMM_BLOCKS;
   return (int)g;
 }
+static int make_push_f32(PushF32* f32, size_t master_off, long long f32_lo, long long f32_hi) {
+  f32->master_off = master_off;
+  f32->lo = f32->hi = 0;
+  if (master_off != (size_t)-1 && f32_hi > f32_lo) {
+    if ((master_off & 15) || (f32_lo & 3) || (f32_hi & 3)) return DTF_ERR_ALIGN;
+    f32->lo = f32_lo;
+    f32->hi = f32_hi;
+  }
+  return DTF_OK;
+}
 
 // The grid must be identical on every rank for a given call, so it is derived from (count, blocks) only.
 extern "C" int dtf_comm_allreduce_optim(void* comm, size_t grad_off, long long start, long long count, int kind,
                                         float lr, float b1, float b2, float eps, float wd, float gscale,
-                                        long long step, float* master, float* m, float* v, void* shadow,
-                                        float* avg_out, int blocks, void* stream) {
+                                        long long step, const float* hyper, float* master, float* m, float* v,
+                                        void* shadow, float* avg_out, int blocks, void* stream) {
   DtfComm* c = reinterpret_cast<DtfComm*>(comm);
   if ((start & 3) || (count & 3) || (grad_off & 15)) return DTF_ERR_ALIGN;
   if (master == nullptr && avg_out == nullptr) return DTF_ERR_ARG;
   const OptimArgs o = make_optim(kind, lr, b1, b2, eps, wd, gscale, step);
   const int grid = comm_grid(count >> 2, blocks);
-  allreduce_optim_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, start, count, o, master, m, v,
-                                                               (__nv_bfloat16*)shadow, avg_out);
+  allreduce_optim_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, start, count, o, hyper,
+                                                                          master, m, v, (__nv_bfloat16*)shadow, avg_out);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long* bounds, int kind, float lr,
                                     float b1, float b2, float eps, float wd, float gscale, long long step,
-                                    float* master, float* m, float* v, size_t shadow_off, size_t master_off,
-                                    int n_nopush, const long long* nopush_ranges, int blocks, void* stream) {
+                                    const float* hyper, float* master, float* m, float* v, size_t shadow_off,
+                                    size_t master_off, long long f32_lo, long long f32_hi, int n_nopush,
+                                    const long long* nopush_ranges, int backup_r, int blocks, void* stream) {
   DtfComm* c = reinterpret_cast<DtfComm*>(comm);
   Bounds b;
   long long maxn = 0;
@@ -513,6 +769,9 @@ extern "C" int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long
     if (r > 0 && bounds[r] - bounds[r - 1] > maxn) maxn = bounds[r] - bounds[r - 1];
   }
   if ((grad_off & 15) || (shadow_off & 15)) return DTF_ERR_ALIGN;
+  PushF32 f32;
+  const int rc = make_push_f32(&f32, master_off, f32_lo, f32_hi);
+  if (rc != DTF_OK) return rc;
   const OptimArgs o = make_optim(kind, lr, b1, b2, eps, wd, gscale, step);
   const int grid = comm_grid(maxn >> 2, blocks);
   NoPush np;
@@ -523,12 +782,15 @@ extern "C" int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long
     np.hi[k] = nopush_ranges[2 * k + 1];
     np.n = k + 1;
   }
-  if (c->ctx.mc != nullptr && master_off == (size_t)-1)
-    rs_optim_ag_nvls_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
-                                                                  np);
+  if (backup_r < 0 || backup_r > c->ctx.world) return DTF_ERR_ARG;
+  const bool backup = backup_r > 0 && backup_r < c->ctx.world;
+  // the in-switch reduction adds ALL ranks: backup-worker mode (a subset of the ranks) needs the peer-load kernel
+  if (c->ctx.mc != nullptr && !backup)
+    rs_optim_ag_nvls_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, hyper, master, m, v,
+                                                                             shadow_off, f32, np);
   else
-    rs_optim_ag_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, master, m, v, shadow_off,
-                                                             master_off, np);
+    rs_optim_ag_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, b, o, hyper, master, m, v,
+                                                                        shadow_off, f32, np, backup_r);
   return DTF_CHECK_LAUNCH();
 }
 // bounds16 in units of 16 bytes relative to buf_off
@@ -545,8 +807,13 @@ extern "C" int dtf_comm_allgather_slices(void* comm, size_t buf_off, const long 
   allgather_slices_kernel<<<comm_grid(maxn, blocks), comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, buf_off, b);
   return DTF_CHECK_LAUNCH();
 }
+extern "C" int dtf_comm_async_begin(void* comm, void* stream) {
+  DtfComm* c = reinterpret_cast<DtfComm*>(comm);
+  async_begin_kernel<<<1, 32, 0, dtf_stream(stream)>>>(c->ctx);
+  return DTF_CHECK_LAUNCH();
+}
 extern "C" int dtf_comm_async_push(void* comm, size_t grad_off, size_t mailbox_off, long long slice_cap,
-                                   const long long* bounds, unsigned int version, int blocks, void* stream) {
+                                   const long long* bounds, int blocks, void* stream) {
   DtfComm* c = reinterpret_cast<DtfComm*>(comm);
   Bounds b;
   for (int r = 0; r <= c->ctx.world; ++r) {
@@ -556,24 +823,40 @@ extern "C" int dtf_comm_async_push(void* comm, size_t grad_off, size_t mailbox_o
   }
   if ((slice_cap & 3) || (grad_off & 15) || (mailbox_off & 15)) return DTF_ERR_ALIGN;
   int grid = blocks < 1 ? 1 : (blocks > MAX_COMM_BLOCKS ? MAX_COMM_BLOCKS : blocks);
-  async_push_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, mailbox_off, slice_cap, b, version);
+  async_push_kernel<<<grid, comm_threads(), 0, dtf_stream(stream)>>>(c->ctx, grad_off, mailbox_off, slice_cap, b);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_comm_async_apply(void* comm, size_t mailbox_off, long long slice_cap, const long long* bounds,
                                     int kind, float lr, float b1, float b2, float eps, float wd, float gscale,
-                                    long long step, float* master, float* m, float* v, size_t shadow_off,
-                                    unsigned int* applied_out_dev, int blocks, void* stream) {
+                                    long long step, const float* hyper, float* master, float* m, float* v,
+                                    size_t shadow_off, size_t master_off, long long f32_lo, long long f32_hi,
+                                    int max_staleness, unsigned int* applied_out_dev, int blocks, void* stream) {
   DtfComm* c = reinterpret_cast<DtfComm*>(comm);
   Bounds b;
   for (int r = 0; r <= c->ctx.world; ++r) b.b[r] = bounds[r];
+  PushF32 f32;
+  const int rc = make_push_f32(&f32, master_off, f32_lo, f32_hi);
+  if (rc != DTF_OK) return rc;
   const OptimArgs o = make_optim(kind, lr, b1, b2, eps, wd, gscale, step);
   int grid = blocks < 1 ? 1 : (blocks > MAX_COMM_BLOCKS ? MAX_COMM_BLOCKS : blocks);
   cudaStream_t st = dtf_stream(stream);
-  async_snapshot_kernel<<<1, 32, 0, st>>>(c->ctx, applied_out_dev);
-  async_apply_kernel<<<grid, comm_threads(), 0, st>>>(c->ctx, mailbox_off, slice_cap, b, o, master, m, v, shadow_off,
-                                           applied_out_dev);
+  async_snapshot_kernel<<<1, 32, 0, st>>>(c->ctx, applied_out_dev, max_staleness);
+  async_apply_kernel<<<grid, comm_threads(), 0, st>>>(c->ctx, mailbox_off, slice_cap, b, o, hyper, master, m, v,
+                                                      shadow_off, f32, applied_out_dev);
   async_commit_kernel<<<1, 32, 0, st>>>(c->ctx, applied_out_dev);
   return DTF_CHECK_LAUNCH();
+}
+// counters of the asynchronous protocol: out[0] = pushes dropped as too stale, out[1] = updates applied by this owner,
+// out[2] = versions pushed by this rank (synchronises the stream)
+extern "C" int dtf_comm_async_stats(void* comm, unsigned int* out3, void* stream) {
+  DtfComm* c = reinterpret_cast<DtfComm*>(comm);
+  const uint32_t* flags = reinterpret_cast<const uint32_t*>(c->ctx.peer[c->ctx.rank]);
+  cudaStream_t st = dtf_stream(stream);
+  if (cudaMemcpyAsync(out3 + 0, flags + DROPPED_OFF, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaMemcpyAsync(out3 + 1, flags + OWNER_STEP_OFF + c->ctx.rank, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaMemcpyAsync(out3 + 2, flags + PUSH_VER_OFF, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess)
+    return DTF_ERR_CUDA;
+  return cudaStreamSynchronize(st) == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 extern "C" int dtf_comm_barrier(void* comm, void* stream) {
   DtfComm* c = reinterpret_cast<DtfComm*>(comm);
@@ -583,5 +866,10 @@ extern "C" int dtf_comm_barrier(void* comm, void* stream) {
 extern "C" int dtf_comm_heartbeat(void* comm, unsigned int beat, unsigned int* seen_out_dev, void* stream) {
   DtfComm* c = reinterpret_cast<DtfComm*>(comm);
   heartbeat_kernel<<<1, 32, 0, dtf_stream(stream)>>>(c->ctx, beat, seen_out_dev);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_debug_sleep(long long ns, void* stream) {
+  if (ns < 0) return DTF_ERR_ARG;
+  sleep_kernel<<<1, 1, 0, dtf_stream(stream)>>>((unsigned long long)ns);
   return DTF_CHECK_LAUNCH();
 }

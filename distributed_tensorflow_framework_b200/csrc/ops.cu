@@ -1112,12 +1112,27 @@ l2_kernel(const float* __restrict__ w, float* __restrict__ out, float* __restric
 // g is pre-scaled by gscale (1/num_replicas); wd adds wd*p to the gradient. Writes the bf16 shadow copy.
 __global__ void optim_kernel(int kind, float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                              float* __restrict__ v, __nv_bfloat16* __restrict__ shadow, long long n, float lr,
-                             float b1, float b2, float eps, float wd, float gscale, float lr_t) {
+                             float b1, float b2, float eps, float wd, float gscale, float lr_t,
+                             const float* __restrict__ hyper) {
+  if (hyper != nullptr) {
+    lr = hyper[0];
+    lr_t = hyper[1];
+  }
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float np = optim_update(kind, p[i], g[i] * gscale, m, v, i, lr, b1, b2, eps, wd, lr_t);
     p[i] = np;
     if (shadow) shadow[i] = __float2bfloat16(np);
   }
+}
+
+// One thread: step += 1; lr_t = lr (SGD / momentum) or lr * sqrt(1 - b2^t) / (1 - b1^t) (Adam). Runs inside the
+// captured step, before the optimizer / collective kernels that read hyper[].
+__global__ void hyper_step_kernel(float* hyper, int kind, float b1, float b2) {
+  int* stepw = reinterpret_cast<int*>(hyper) + 2;
+  const int t = *stepw + 1;
+  *stepw = t;
+  const float lr = hyper[0];
+  hyper[1] = (kind == 2) ? lr * sqrtf(1.f - powf(b2, (float)t)) / (1.f - powf(b1, (float)t)) : lr;
 }
 
 // Batched per-tap transpose of bf16 filters: src [T, Ci, Co] -> dst [T, Co, Ci] for many variables in one launch.
@@ -1526,12 +1541,17 @@ extern "C" int dtf_top1_hits(const void* logits, const long long* labels, unsign
 
 extern "C" int dtf_optim_step(int kind, float* p, const float* g, float* m, float* v, void* shadow, long long n,
                               float lr, float b1, float b2, float eps, float wd, float gscale, long long step,
-                              void* stream) {
+                              const float* hyper, void* stream) {
   if (kind < 0 || kind > 2) return DTF_ERR_ARG;
   float lr_t = lr;
   if (kind == 2) lr_t = lr * sqrtf(1.f - powf(b2, (float)step)) / (1.f - powf(b1, (float)step));
   optim_kernel<<<grid_for(n, 256), 256, 0, ST(stream)>>>(kind, p, g, m, v, (__nv_bfloat16*)shadow, n, lr, b1, b2, eps,
-                                                         wd, gscale, lr_t);
+                                                         wd, gscale, lr_t, hyper);
+  return DTF_CHECK_LAUNCH();
+}
+extern "C" int dtf_optim_hyper_step(float* hyper, int kind, float b1, float b2, void* stream) {
+  if (hyper == nullptr || kind < 0 || kind > 2) return DTF_ERR_ARG;
+  hyper_step_kernel<<<1, 1, 0, ST(stream)>>>(hyper, kind, b1, b2);
   return DTF_CHECK_LAUNCH();
 }
 extern "C" int dtf_tap_transpose(const void* src, void* dst, const void* descs_dev, int ndesc, int total_tiles,

@@ -27,4 +27,16 @@ struct OptimArgs {
   float lr, b1, b2, eps, wd, gscale, lr_t;
 };
 
+// Device-resident hyper-parameters (optional): hyper[0] = learning rate (written by the host whenever the schedule
+// moves it), hyper[1] = Adam's bias-corrected rate lr_t (recomputed on the device every step by hyper_step_kernel),
+// word 2 = the step counter as int32. A kernel launched from a replayed CUDA graph reads them at run time, so a
+// learning-rate schedule (LearningRate handler, /root/reference/distribute_learningrate.py:12-50) and Adam's bias
+// correction follow the real step instead of the values frozen at capture.
+__device__ __forceinline__ void optim_load_hyper(OptimArgs& o, const float* __restrict__ hyper) {
+  if (hyper != nullptr) {
+    o.lr = hyper[0];
+    o.lr_t = hyper[1];
+  }
+}
+
 }  // namespace dtf

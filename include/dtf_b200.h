@@ -180,7 +180,14 @@ int dtf_top1_hits(const void* logits, const long long* labels, unsigned int* hit
 /* Optimizer apply on a flat arena (distribute.py:26,112; distribute_train.py:151-158). kind 0 SGD, 1 momentum,
  * 2 Adam. g is multiplied by gscale; wd*p is added to it; the bf16 shadow (may be NULL) receives the new weights. */
 int dtf_optim_step(int kind, float* p, const float* g, float* m, float* v, void* shadow, long long n, float lr,
-                   float b1, float b2, float eps, float wd, float gscale, long long step, void* stream);
+                   float b1, float b2, float eps, float wd, float gscale, long long step, const float* hyper,
+                   void* stream);
+/* Device-resident hyper-parameters. `hyper` (4 floats of device memory, optional in every optimizer entry point):
+ * [0] learning rate, written by the host when the schedule moves it (LearningRate handler,
+ * distribute_learningrate.py:12-50); [1] Adam's bias-corrected rate, recomputed by dtf_optim_hyper_step; word 2 the
+ * int32 step counter. When `hyper` is non-NULL the kernels read lr / lr_t from it at run time and ignore the by-value
+ * lr / step, so a captured CUDA graph follows the schedule. dtf_optim_hyper_step: step += 1, lr_t refreshed. */
+int dtf_optim_hyper_step(float* hyper, int kind, float b1, float b2, void* stream);
 /* Batched per-tap transpose [T,Ci,Co] -> [T,Co,Ci] of bf16 filters (second shadow used by dgrad / deconv). */
 int dtf_tap_transpose(const void* src, void* dst, const void* descs_dev, int ndesc, int total_tiles, void* stream);
 /* Philox-4x32-10 initialisers: kind 0 constant a, 1 uniform [a,b), 2 normal(a,b), 3 truncated normal(a,b) |z|<=2
@@ -209,27 +216,54 @@ int dtf_comm_set_multicast(void* comm, void* mc_base);
  * update of the local replica. Replaces Tower.average_gradients + apply (distribute_tower.py:78-114). With
  * master == NULL the averaged gradient is written to avg_out instead. */
 int dtf_comm_allreduce_optim(void* comm, size_t grad_off, long long start, long long count, int kind, float lr,
-                             float b1, float b2, float eps, float wd, float gscale, long long step, float* master,
-                             float* m, float* v, void* shadow, float* avg_out, int blocks, void* stream);
+                             float b1, float b2, float eps, float wd, float gscale, long long step,
+                             const float* hyper, float* master, float* m, float* v, void* shadow, float* avg_out,
+                             int blocks, void* stream);
 /* K-RS-OPT: reduce-scatter into the owner shard fused with the owner-side optimizer, then all-gather of the new
- * bf16 weights (except the `nopush_ranges` [lo,hi) element ranges, which consumers pull with dtf_gemm_bf16_ag) (and optionally fp32 masters) by peer stores. Replaces the worker->ps push, ps-side apply and
- * ps->worker pull of SyncReplicasOptimizer / replica_device_setter (distribute_train.py:109-110,146-158). */
+ * bf16 weights by peer stores (except the `nopush_ranges` [lo,hi) element ranges, which consumers pull with
+ * dtf_gemm_bf16_ag). Inside [f32_lo, f32_hi) the owner also broadcasts the fp32 master (heap offset master_off;
+ * (size_t)-1 = never): that region holds the variables which kernels read in fp32 (biases, batch-norm gamma/beta).
+ * Replaces the worker->ps push, ps-side apply and ps->worker pull of SyncReplicasOptimizer /
+ * replica_device_setter (distribute_train.py:109-110,146-158).
+ * backup_r in (0, world): backup workers (replicas_to_aggregate = backup_r, distribute_train.py:146-155,
+ * distribute_flags.py:26-29): each owner aggregates the first backup_r gradients to ARRIVE (ticket counter in its
+ * flag page), drops the late ones; pass gscale = 1/backup_r. 0 or world: every rank is aggregated. */
 int dtf_comm_rs_optim_ag(void* comm, size_t grad_off, const long long* bounds, int kind, float lr, float b1, float b2,
-                         float eps, float wd, float gscale, long long step, float* master, float* m, float* v,
-                         size_t shadow_off, size_t master_off, int n_nopush, const long long* nopush_ranges, int blocks,
+                         float eps, float wd, float gscale, long long step, const float* hyper, float* master,
+                         float* m, float* v, size_t shadow_off, size_t master_off, long long f32_lo,
+                         long long f32_hi, int n_nopush, const long long* nopush_ranges, int backup_r, int blocks,
                          void* stream);
 int dtf_comm_allgather_slices(void* comm, size_t buf_off, const long long* bounds16, int blocks, void* stream);
 /* K-ASYNC-PUSH / owner apply: asynchronous parameter-server mode (extension; the reference is sync-only,
  * distribute_train.py:151). */
+/* Version stamps and staleness clocks live in the flag page and are advanced by the kernels themselves, so a replayed
+ * CUDA graph keeps publishing new versions. async_begin (start of a step): remember which update of every owner the
+ * weights of this step correspond to. async_push: gradient slices into the owners' mailboxes + next version + that
+ * stamp. async_apply: the owner applies every newer mailbox (one optimizer update per push, never waits), drops a
+ * push computed more than max_staleness owner updates ago (< 0: no bound), broadcasts bf16 weights (+ fp32 master in
+ * [f32_lo, f32_hi)). async_stats: {dropped, updates applied by this owner, versions pushed by this rank}. */
+int dtf_comm_async_begin(void* comm, void* stream);
 int dtf_comm_async_push(void* comm, size_t grad_off, size_t mailbox_off, long long slice_cap, const long long* bounds,
-                        unsigned int version, int blocks, void* stream);
+                        int blocks, void* stream);
 int dtf_comm_async_apply(void* comm, size_t mailbox_off, long long slice_cap, const long long* bounds, int kind,
                          float lr, float b1, float b2, float eps, float wd, float gscale, long long step,
-                         float* master, float* m, float* v, size_t shadow_off, unsigned int* applied_out_dev,
+                         const float* hyper, float* master, float* m, float* v, size_t shadow_off, size_t master_off,
+                         long long f32_lo, long long f32_hi, int max_staleness, unsigned int* applied_out_dev,
                          int blocks, void* stream);
+int dtf_comm_async_stats(void* comm, unsigned int* out3, void* stream);
 /* Device-side barrier / liveness (token queue, done queue, init handshake: distribute_train.py:43-46,86-90,160-167). */
 int dtf_comm_barrier(void* comm, void* stream);
 int dtf_comm_heartbeat(void* comm, unsigned int beat, unsigned int* seen_out_dev, void* stream);
+/* Failure detection (the reference hangs forever when a worker dies, distribute_train.py:86-90): every
+ * device-side wait is bounded in TIME (default 30 s, DTF_COMM_TIMEOUT_MS, 0 = unbounded). A wait that expires makes
+ * its kernel return and records {code 1 = barrier / 2 = arrivals, block, peer, epoch} in mapped host memory;
+ * dtf_comm_error copies that record without any CUDA call (a watchdog thread may poll it), dtf_comm_clear_error
+ * re-arms the communicator after the group has recovered. */
+int dtf_comm_set_timeout_ms(void* comm, long long ms);
+int dtf_comm_error(void* comm, unsigned int* out4);
+int dtf_comm_clear_error(void* comm, void* stream);
+/* Fault injection / tests: occupy the stream for `ns` nanoseconds (an artificial straggler). */
+int dtf_debug_sleep(long long ns, void* stream);
 
 #ifdef __cplusplus
 }
