@@ -124,10 +124,12 @@ class DeconvFn(torch.autograd.Function):
         dy = dy.contiguous()
         # dW[kh,kw,co,ci] = sum_p dy[p*s - pad + k, co] * x[p, ci]: the wgrad kernel with (dy, x) in the roles (x, dy)
         raw.conv_wgrad(dy, x, KH, KW, ctx.stride, out=wvar.grad.view(KH * KW * Cout, Cin))
-        _ready(wvar)
+        # dx reads the plain shadow, which the bucket's collective rewrites once the gradient is announced: compute it
+        # BEFORE _ready (conv / linear read `shadow_t`, which is only refreshed in finish_step)
         dx = None
         if ctx.x_needs_grad:
             dx = raw.conv_fprop(dy, wvar.shadow.detach().view(KH * KW * Cout, Cin), None, KH, KW, ctx.stride)
+        _ready(wvar)
         return dx, None, None, None, None
 
 
@@ -357,18 +359,28 @@ def mse(pred, target):
 
 
 class L2Fn(torch.autograd.Function):
-    """wd * sum(w^2)/2 on the fp32 master (tf.nn.l2_loss weight-decay term, distribute_tools.py:63-65)."""
+    """wd * sum(w^2)/2 (tf.nn.l2_loss weight-decay term, distribute_tools.py:63-65).
+
+    The gradient wd * w is added to the gradient arena at FORWARD time (the arena was zeroed by begin_step and the
+    filter-gradient kernels accumulate with red.add): an autograd node of this term would run after the layer's own
+    backward has already announced the gradient to the bucket collective. The term therefore assumes the total loss is
+    the plain sum of the collected losses (coefficient 1), which is what Tower does (distribute_tower.py:133-135).
+    In the owner-sharded modes the fp32 master of a filter is current only on its owner, so w is read from the
+    replicated bf16 shadow there."""
 
     @staticmethod
-    def forward(ctx, w_shadow, wvar, wd):
-        ctx.wvar, ctx.wd = wvar, wd
-        return raw.l2_loss(wvar.master, wd).view(())
+    def forward(ctx, w_shadow, wvar, wd, track):
+        st = getattr(wvar, "_store", None)
+        replicated = st is None or getattr(st, "masters_replicated", True)
+        w = wvar.master if replicated else wvar.shadow.detach().float()
+        if track:
+            wvar.grad.add_(w, alpha=float(wd))
+        return raw.l2_loss(w.contiguous(), wd).view(())
 
     @staticmethod
     def backward(ctx, g):
-        ctx.wvar.grad.add_(ctx.wvar.master * (g.float() * float(ctx.wd)))
-        return None, None, None
+        return None, None, None, None
 
 
 def l2_loss(wvar, wd):
-    return L2Fn.apply(wvar.shadow, wvar, wd)
+    return L2Fn.apply(wvar.shadow, wvar, wd, torch.is_grad_enabled())

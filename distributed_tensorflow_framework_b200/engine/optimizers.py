@@ -67,14 +67,16 @@ class Optimizer(object):
         store.global_step = step
         return step
 
-    def apply_arena(self, store, step, gscale=1.0, start=0, count=None, refresh=True):
+    def apply_arena(self, store, step, gscale=1.0, start=0, count=None, refresh=True, hyper=None):
+        """`hyper`: optional device tensor [lr, lr_t, step, -] read by the kernel instead of the by-value lr / step
+        (learning-rate schedules and Adam under CUDA-graph replay)."""
         from ..ops import raw
         n = store.n_params if count is None else count
         sl = slice(start, start + n)
         raw.optim_step(self.kind, store.master_arena[sl], store.grad_arena[sl],
                        store.slot_m[sl] if store.slot_m is not None else None,
                        store.slot_v[sl] if store.slot_v is not None else None, store.shadow_arena[sl],
-                       self.learning_rate, self.b1, self.b2, self.eps, self.wd, gscale, step)
+                       self.learning_rate, self.b1, self.b2, self.eps, self.wd, gscale, step, hyper=hyper)
         if refresh:
             store.refresh_transposed_shadows()
 

@@ -3,17 +3,19 @@
 This is the per-step body that the reference builds once as a TF graph at /root/reference/distribute_train.py:106-158
 (tower loop, Tower.process, average_gradients, SyncReplicasOptimizer.apply_gradients) and runs with
 `sess.run([train_op, global_step, loss])` at :185. It is the public step API of the framework: the Train operator
-(runtime/train.py) and bench.py both drive it.
+(runtime/train.py), the Estimator (runtime/estimator.py) and bench.py all drive it.
 
 CUDA path: the whole step (zero-grad, forward, loss, backward with bucketed fused collectives on a side stream,
-optimizer, shadow refresh) can be captured ONCE into a CUDA graph and replayed; inputs are copied from pinned host
-memory into static device buffers before every replay, and step-dependent optimizer scalars live in device memory.
+optimizer, shadow refresh) is captured ONCE into a CUDA graph and replayed. Step-dependent optimizer scalars
+(learning rate, Adam's bias-corrected rate, the step counter) live in device memory (`GradientEngine.hyper`), so a
+replayed graph follows a learning-rate schedule and Adam can be captured. Inputs travel host -> device on a copy
+stream into a pair of staging buffers (`prefetch`), one step ahead of the compute stream -- the analogue of the
+reference's queue runners feeding `shuffle_batch` (/root/reference/distribute_input.py:54-69).
 """
 
 import torch
 
 from ..api import constants
-from ..api import log as logger
 from . import layers, variables as V
 from .tower import Tower
 
@@ -21,7 +23,8 @@ from .tower import Tower
 class Trainer(object):
     def __init__(self, net, loss, optimizer, device="cpu", rank=0, world=1, group=None, gpu_num=1, algo="auto",
                  placement="bytes", use_cuda_graph=False, seed=0, sync_optimizer=None, pre_process_fn=None,
-                 post_process_fn=None, pre_train_result=None, bucket_bytes=4 << 20, overlap=True):
+                 post_process_fn=None, pre_train_result=None, bucket_bytes=4 << 20, overlap=True,
+                 replicas_to_aggregate=None, max_staleness=None):
         self.net, self.loss, self.optimizer = net, loss, optimizer
         self.device = torch.device(device)
         self.rank, self.world, self.group = rank, world, group
@@ -33,6 +36,7 @@ class Trainer(object):
         self.pre_process_fn, self.post_process_fn = pre_process_fn, post_process_fn
         self.pre_train_result = pre_train_result
         self.bucket_bytes, self.overlap = bucket_bytes, overlap
+        self.replicas_to_aggregate, self.max_staleness = replicas_to_aggregate, max_staleness
         self.engine = None
         self.built = False
         self._graph = None
@@ -41,6 +45,13 @@ class Trainer(object):
         self._graph_launches = 0
         self.last_summaries = {}
         self.last_logits = None
+        # input staging (CUDA): two device copies of the batch, filled by the copy stream one step ahead
+        self._copy_stream = None
+        self._staging = [None, None]
+        self._staged_src = [None, None]  # host batch objects whose data sits in the slot (identity)
+        self._staged_ready = [None, None]  # event: H2D into the slot has finished (copy stream)
+        self._slot_free = [None, None]  # event: the step that read the slot has finished (compute stream)
+        self._next_slot = 0
 
     # ------------------------------------------------------------------ build (variable discovery + arenas)
     def _to_device(self, t):
@@ -62,7 +73,8 @@ class Trainer(object):
             with torch.cuda.device(self.device):
                 self.engine = GradientEngine(self.store, self.optimizer, self.rank, self.world, self.algo, self.group,
                                              bucket_bytes=self.bucket_bytes, placement=self.placement,
-                                             overlap=self.overlap)
+                                             overlap=self.overlap, replicas_to_aggregate=self.replicas_to_aggregate,
+                                             max_staleness=self.max_staleness, num_towers=self.num_towers)
             self.algo = self.engine.algo
         else:
             self.store.finalize()
@@ -87,15 +99,14 @@ class Trainer(object):
         loss = tower_losses[0] if len(tower_losses) == 1 else torch.stack(tower_losses).mean()
         return loss, tower_grads
 
-    def _step_body(self, batches):
+    def _step_body(self, batches, capturing=False):
         store = self.store
         step = store.global_step + 1
         if self.device.type == "cuda":
-            self.engine.begin_step(step)
+            # in-process towers accumulate into one gradient arena; a bucket's collective starts when the LAST tower
+            # has produced it, and the 1/num_towers factor is part of the collective's scale (engine.num_towers)
+            self.engine.begin_step(step, capturing=capturing)
             loss, _ = self._forward_backward(batches)
-            # in-process towers accumulate into the same arena: their mean is folded into the collective's scale
-            if self.num_towers > 1:
-                store.grad_arena.mul_(1.0 / self.num_towers)
             self.engine.finish_step()
             return loss
         loss, tower_grads = self._forward_backward(batches)
@@ -112,13 +123,77 @@ class Trainer(object):
             return self._step_body(batches)
         return self._graph_step(batches)
 
+    # ------------------------------------------------------------------ host batches: staged H2D on a copy stream
+    def _stage(self, host_batches):
+        """Enqueue the H2D copy of `host_batches` (list of (raw, gt)) into the next staging slot on the copy stream.
+        Returns the slot index."""
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        k = self._next_slot
+        self._next_slot ^= 1
+        cs = self._copy_stream
+        if self._slot_free[k] is not None:
+            cs.wait_event(self._slot_free[k])  # the step that last read this slot must have finished
+        bufs = self._staging[k]
+        ok = bufs is not None and len(bufs) == len(host_batches) and all(
+            b[0].shape == r.shape and b[0].dtype == r.dtype and b[1].shape == g.shape and b[1].dtype == g.dtype
+            for b, (r, g) in zip(bufs, host_batches))
+        if not ok:
+            bufs = [(torch.empty(r.shape, dtype=r.dtype, device=self.device),
+                     torch.empty(g.shape, dtype=g.dtype, device=self.device)) for r, g in host_batches]
+            self._staging[k] = bufs
+            cs.wait_stream(torch.cuda.current_stream(self.device))  # fresh memory: order after its previous users
+        with torch.cuda.stream(cs):
+            for (dr, dg), (r, g) in zip(bufs, host_batches):
+                dr.copy_(r, non_blocking=True)
+                dg.copy_(g, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        self._staged_ready[k] = ev
+        self._staged_src[k] = host_batches
+        return k
+
+    @staticmethod
+    def _same_batches(a, b):
+        return a is not None and len(a) == len(b) and all(x[0] is y[0] and x[1] is y[1] for x, y in zip(a, b))
+
+    def prefetch(self, host_batches):
+        """Start the H2D copy of the NEXT step's (pinned) host batch now, on the copy stream, while the current step
+        is still running; the next `step()` call with the same batch objects finds the data already on the device."""
+        if self.device.type != "cuda":
+            return
+        if isinstance(host_batches, tuple):
+            host_batches = [host_batches]
+        host_batches = list(host_batches)
+        if any(r.device.type == "cuda" for r, _ in host_batches):
+            return
+        for k in (0, 1):
+            if self._same_batches(self._staged_src[k], host_batches):
+                return
+        self._stage(host_batches)
+
     def step(self, host_batches):
-        """Public per-step API: host (pinned) batches -> async H2D -> step -> loss tensor on the device.
+        """Public per-step API: host (pinned) batches -> H2D on the copy stream -> step -> loss tensor on the device.
         `host_batches` is one (raw, gt) pair or a list with one pair per tower."""
         if isinstance(host_batches, tuple):
             host_batches = [host_batches]
-        dev = [(self._to_device(r), self._to_device(g)) for r, g in host_batches]
-        return self.step_device(dev)
+        host_batches = list(host_batches)
+        if self.device.type != "cuda" or any(r.device.type == "cuda" for r, _ in host_batches):
+            return self.step_device([(self._to_device(r), self._to_device(g)) for r, g in host_batches])
+        k = None
+        for j in (0, 1):
+            if self._same_batches(self._staged_src[j], host_batches):
+                k = j
+        if k is None:
+            k = self._stage(host_batches)
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(self._staged_ready[k])
+        self._staged_src[k] = None  # consumed: the same host object may carry new data next time
+        loss = self.step_device(self._staging[k])
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self._slot_free[k] = ev
+        return loss
 
     # ------------------------------------------------------------------ CUDA graph replay
     def _graph_step(self, batches):
@@ -133,16 +208,28 @@ class Trainer(object):
         self._graph.replay()
         self.store.global_step += 1
         self.engine._step = self.store.global_step
+        self.engine.note_replay()
         return self._loss_buf
 
     def _update_hyper(self):
-        pass  # reserved: device-resident lr / bias-correction scalars for schedules under graph replay
+        """Before a replay: push the learning rate to the device if the schedule (a LearningRate handler or a callable
+        given to the optimizer) moved it, and the step counter if it was set from outside (checkpoint restore)."""
+        self.engine.sync_hyper(self.store.global_step)
+
+    def _state_tensors(self):
+        st = self.store
+        ts = [st.master_arena, st.shadow_arena, st.shadow_t_arena, st.slot_m, st.slot_v]
+        ts += [v.master for v in st.all_variables() if not v.trainable]  # batch-norm running statistics
+        return [t for t in ts if t is not None]
+
+    def _quiesce(self):
+        """Every rank's device work (including peer stores into this rank's heap) has finished."""
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)
 
     def _capture(self, batches):
-        if self.optimizer.kind == "adam":
-            logger.warn("CUDA graph replay freezes Adam's bias correction at the capture step; using eager steps")
-            self.use_cuda_graph = False
-            return
         self._static_in = [(r.clone(), g.clone()) for r, g in batches]
         # Autograd ties every parameter leaf to the stream that was current when the leaf was first used and joins
         # that stream at the end of backward; inside a capture this must be the capturing stream itself, otherwise
@@ -150,22 +237,35 @@ class Trainer(object):
         self.store.rebind_shadow_leaves()
         s = self._cap_stream = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
+        # The warm-up steps are real steps on the first batch; their effect is rolled back afterwards (parameters,
+        # optimizer slots, running statistics, step counters), so that the first replay is step global_step + 1 and
+        # the first batch is applied exactly once.
+        step0 = self.store.global_step
         with torch.cuda.stream(s):
+            saved = [t.clone() for t in self._state_tensors()]
             for _ in range(2):
                 self._step_body(self._static_in)
+        self._quiesce()
+        with torch.cuda.stream(s):
+            for t, c in zip(self._state_tensors(), saved):
+                t.copy_(c)
+        self.store.global_step = step0
+        self.engine._step = step0
         torch.cuda.current_stream(self.device).wait_stream(s)
-        torch.cuda.synchronize(self.device)
-        if self.world > 1:
-            import torch.distributed as dist
-            dist.barrier(group=self.group)
+        self._quiesce()
+        del saved
+        self.engine.sync_hyper(step0)
+        self._quiesce()
         self._graph = torch.cuda.CUDAGraph()
         from ..ops import _lib
         n0 = _lib.launch_count
         with torch.cuda.graph(self._graph, stream=s, capture_error_mode="thread_local"):
-            self._loss_buf = self._step_body(self._static_in)
+            self._loss_buf = self._step_body(self._static_in, capturing=True)
         self._graph_launches = _lib.launch_count - n0  # kernels of ours replayed by every graph launch
-        # capture does not execute: undo the step increments of the capture pass
-        self.store.global_step -= 1
+        # capture does not execute: undo the bookkeeping of the capture pass
+        self.store.global_step = step0
+        self.engine._step = step0
+        self.engine._hyper_step = step0
 
     # ------------------------------------------------------------------ evaluation forward
     def forward(self, raw):

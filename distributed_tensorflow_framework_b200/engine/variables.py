@@ -173,6 +173,8 @@ class VariableStore(object):
         self.master_arena = self.grad_arena = self.shadow_arena = self.shadow_t_arena = None
         self.slot_m = self.slot_v = None
         self.n_params = 0
+        self.owner_bounds = [0, 0]
+        self.f32_ranges = [(0, 0)]
         self._tap_table = None
         self.global_step = 0
 
@@ -234,27 +236,42 @@ class VariableStore(object):
             self.finalized = True
             return
         tv = self.trainable_variables()
-        if placement == "round_robin" and world > 1:
+        # Variables that kernels read in fp32 straight from the master arena (biases, batch-norm gamma / beta, user
+        # `weight()` / `bias()` variables) are packed in front of the tensor-core operands (conv / FC / deconv filters,
+        # read through the bf16 shadow), so that in the owner-sharded modes the "fp32 region" an owner must broadcast
+        # after its update is ONE contiguous range per owner (f32_ranges[owner]).
+        small = lambda v: v.kind not in ("conv_w", "fc_w", "deconv_w")  # noqa: E731
+        rr = placement == "round_robin" and world > 1
+        if rr:
             for i, v in enumerate(tv):
                 v.owner = i % world
-            tv = sorted(tv, key=lambda v: (v.owner, v.index))
+            tv = sorted(tv, key=lambda v: (v.owner, 0 if small(v) else 1, v.index))
+        else:
+            tv = sorted(tv, key=lambda v: (0 if small(v) else 1, v.index))
         off = 0
         self.owner_bounds = [0] * (world + 1)
         cur_owner = 0
+        f32_lo, f32_hi = {}, {}
         for v in tv:
-            if placement == "round_robin" and world > 1:
+            if rr:
                 while cur_owner < v.owner:
                     cur_owner += 1
                     self.owner_bounds[cur_owner] = off
             v.offset = off
             off += (v.numel + 7) // 8 * 8  # 16-byte aligned bf16 views, 32-byte aligned fp32 views
+            if small(v):
+                key = v.owner if rr else 0
+                f32_lo.setdefault(key, v.offset)
+                f32_hi[key] = off
         n = off
-        if placement == "round_robin" and world > 1:
+        if rr:
             for o in range(cur_owner + 1, world + 1):
                 self.owner_bounds[o] = n
+            self.f32_ranges = [(f32_lo.get(o, 0), f32_hi.get(o, 0)) for o in range(world)]
         else:
             per = ((n + world - 1) // world + 7) // 8 * 8
             self.owner_bounds = [min(i * per, n) for i in range(world)] + [n]
+            self.f32_ranges = [(f32_lo.get(0, 0), f32_hi.get(0, 0))] * max(world, 1)
         self.n_params = n
         alloc = allocator or (lambda tag, numel, dtype: torch.zeros(numel, device=self.device, dtype=dtype))
         self.master_arena = alloc("master", n, torch.float32)

@@ -526,9 +526,9 @@ def top1_hits(logits, labels):
 OPTIM_KINDS = {"sgd": 0, "momentum": 1, "adam": 2}
 
 
-def optim_step(kind, p, g, m, v, shadow, lr, b1=0.9, b2=0.999, eps=1e-8, wd=0.0, gscale=1.0, step=1):
+def optim_step(kind, p, g, m, v, shadow, lr, b1=0.9, b2=0.999, eps=1e-8, wd=0.0, gscale=1.0, step=1, hyper=None):
     _lib.call("dtf_optim_step", OPTIM_KINDS[kind], p, g, m, v, shadow, p.numel(), lr, b1, b2, eps, wd, gscale, step,
-              _sp())
+              hyper, _sp())
 
 
 def init_(t, kind, a=0.0, b=1.0, seed=0, stream_id=0):

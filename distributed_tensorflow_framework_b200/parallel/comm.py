@@ -91,7 +91,6 @@ class Communicator(object):
         self.handle = ctypes.c_void_p()
         self.stream = torch.cuda.Stream(device=heap.device)
         self.blocks = int(os.environ.get("DTF_COMM_BLOCKS", "64"))  # CTAs per collective kernel
-        self._version = 0
         if heap.peer_ptrs is not None:  # peers already mapped (torch symmetric memory / NVLS backend)
             arr = (ctypes.c_void_p * world)(*heap.peer_ptrs)
             _lib.call("dtf_comm_create_local", rank, world, arr, heap.nbytes, ctypes.byref(self.handle))
@@ -118,31 +117,41 @@ class Communicator(object):
         return _lib.stream_ptr(stream)
 
     @staticmethod
-    def _opt_args(opt, step, gscale):
+    def _opt_args(opt, step, gscale, hyper=None):
         from ..ops.raw import OPTIM_KINDS
-        return (OPTIM_KINDS[opt.kind], opt.learning_rate, opt.b1, opt.b2, opt.eps, opt.wd, gscale, step)
+        return (OPTIM_KINDS[opt.kind], opt.learning_rate, opt.b1, opt.b2, opt.eps, opt.wd, gscale, step, hyper)
 
-    def allreduce_optim(self, grad_off, start, count, opt, step, master, m, v, shadow, gscale=None, stream=None):
+    def allreduce_optim(self, grad_off, start, count, opt, step, master, m, v, shadow, gscale=None, stream=None,
+                        hyper=None):
         """K-AR: grads[start:start+count) of every rank -> mean -> optimizer on the local replica."""
         gscale = 1.0 / self.world if gscale is None else gscale
-        _lib.call("dtf_comm_allreduce_optim", self.handle, grad_off, start, count, *self._opt_args(opt, step, gscale),
-                  master, m, v, shadow, None, self.blocks, self._s(stream))
+        _lib.call("dtf_comm_allreduce_optim", self.handle, grad_off, start, count,
+                  *self._opt_args(opt, step, gscale, hyper), master, m, v, shadow, None, self.blocks, self._s(stream))
 
     def allreduce_mean(self, grad_off, start, count, out, gscale=None, stream=None):
         gscale = 1.0 / self.world if gscale is None else gscale
         _lib.call("dtf_comm_allreduce_optim", self.handle, grad_off, start, count, 0, 0.0, 0.0, 0.0, 0.0, 0.0, gscale,
-                  1, None, None, None, None, out, self.blocks, self._s(stream))
+                  1, None, None, None, None, None, out, self.blocks, self._s(stream))
 
-    def rs_optim_ag(self, grad_off, bounds, opt, step, master, m, v, shadow_off, master_off=None, gscale=None,
-                    stream=None, nopush=()):
+    def rs_optim_ag(self, grad_off, bounds, opt, step, master, m, v, shadow_off, master_off=None, f32_range=None,
+                    gscale=None, stream=None, nopush=(), hyper=None, backup_r=0):
         """K-RS-OPT: reduce-scatter into the owner shard + owner update + all-gather of bf16 weights by stores.
-        `nopush`: up to 8 (lo, hi) element ranges that stay owner-local (pulled later by K-AG-GEMM)."""
-        gscale = 1.0 / self.world if gscale is None else gscale
+        `master_off` + `f32_range` (lo, hi): the owner also broadcasts its fp32 masters inside that element range
+        (default: everywhere when only master_off is given). `nopush`: up to 8 (lo, hi) element ranges that stay
+        owner-local (pulled later by K-AG-GEMM). `backup_r` in (0, world): aggregate the first backup_r arrivals
+        only (backup workers); the default scale is then 1/backup_r."""
+        backup = 0 < backup_r < self.world
+        if gscale is None:
+            gscale = 1.0 / (backup_r if backup else self.world)
         b = (ctypes.c_longlong * (self.world + 1))(*bounds)
         flat = [x for r in nopush for x in r]
         npr = (ctypes.c_longlong * max(len(flat), 1))(*flat) if flat else None
-        _lib.call("dtf_comm_rs_optim_ag", self.handle, grad_off, b, *self._opt_args(opt, step, gscale), master, m, v,
-                  shadow_off, (1 << 64) - 1 if master_off is None else master_off, len(nopush), npr, self.blocks,
+        if master_off is None:
+            master_off, lo, hi = (1 << 64) - 1, 0, 0
+        else:
+            lo, hi = f32_range if f32_range is not None else (0, bounds[-1])
+        _lib.call("dtf_comm_rs_optim_ag", self.handle, grad_off, b, *self._opt_args(opt, step, gscale, hyper), master,
+                  m, v, shadow_off, master_off, lo, hi, len(nopush), npr, backup_r if backup else 0, self.blocks,
                   self._s(stream))
 
     def peer_ptr(self, r):
@@ -152,18 +161,61 @@ class Communicator(object):
         b = (ctypes.c_longlong * (self.world + 1))(*bounds16)
         _lib.call("dtf_comm_allgather_slices", self.handle, buf_off, b, self.blocks, self._s(stream))
 
-    def async_push(self, grad_off, mailbox_off, slice_cap, bounds, stream=None):
-        self._version += 1
-        b = (ctypes.c_longlong * (self.world + 1))(*bounds)
-        _lib.call("dtf_comm_async_push", self.handle, grad_off, mailbox_off, slice_cap, b, self._version, self.blocks,
-                  self._s(stream))
-        return self._version
+    def async_begin(self, stream=None):
+        """Start of an asynchronous step: stamp the owner updates this step's weights correspond to."""
+        _lib.call("dtf_comm_async_begin", self.handle, self._s(stream))
 
-    def async_apply(self, mailbox_off, slice_cap, bounds, opt, step, master, m, v, shadow_off, stream=None):
+    def async_push(self, grad_off, mailbox_off, slice_cap, bounds, stream=None):
+        """The version stamp lives in the flag page and is bumped by the kernel (graph replay publishes new ones)."""
         b = (ctypes.c_longlong * (self.world + 1))(*bounds)
-        _lib.call("dtf_comm_async_apply", self.handle, mailbox_off, slice_cap, b, *self._opt_args(opt, step, 1.0),
-                  master, m, v, shadow_off, self._snap, self.blocks, self._s(stream))
+        _lib.call("dtf_comm_async_push", self.handle, grad_off, mailbox_off, slice_cap, b, self.blocks,
+                  self._s(stream))
+
+    def async_apply(self, mailbox_off, slice_cap, bounds, opt, step, master, m, v, shadow_off, stream=None,
+                    master_off=None, f32_range=None, max_staleness=-1, hyper=None):
+        b = (ctypes.c_longlong * (self.world + 1))(*bounds)
+        if master_off is None:
+            master_off, lo, hi = (1 << 64) - 1, 0, 0
+        else:
+            lo, hi = f32_range if f32_range is not None else (0, bounds[-1])
+        _lib.call("dtf_comm_async_apply", self.handle, mailbox_off, slice_cap, b,
+                  *self._opt_args(opt, step, 1.0, hyper), master, m, v, shadow_off, master_off, lo, hi,
+                  -1 if max_staleness is None else int(max_staleness), self._snap, self.blocks, self._s(stream))
         return self._snap
+
+    def async_stats(self, stream=None):
+        """{'dropped': pushes dropped as too stale, 'applied': updates applied by this owner, 'pushed': versions
+        pushed by this rank}. Synchronises the stream."""
+        out = (ctypes.c_uint * 3)()
+        _lib.call("dtf_comm_async_stats", self.handle, out, self._s(stream))
+        return {"dropped": int(out[0]), "applied": int(out[1]), "pushed": int(out[2])}
+
+    def set_timeout_ms(self, ms):
+        _lib.call("dtf_comm_set_timeout_ms", self.handle, int(ms))
+
+    def error(self):
+        """Host watchdog read (no CUDA call): None when healthy, else a dict describing the wait that timed out."""
+        out = (ctypes.c_uint * 4)()
+        code = _lib.call_raw("dtf_comm_error", self.handle, out)
+        if not code:
+            return None
+        what = {1: "barrier", 2: "gradient arrivals"}.get(int(code), "wait")
+        return {"code": int(code), "what": what, "block": int(out[1]), "peer": int(out[2]), "epoch": int(out[3])}
+
+    def check(self):
+        """Raise WorkerLostError when a device-side wait has expired (a peer is gone or stuck)."""
+        e = self.error()
+        if e is not None:
+            from ..runtime.session import WorkerLostError
+            raise WorkerLostError("rank %d: %s wait timed out (block %d, peer/arrivals %d, epoch %d)"
+                                  % (self.rank, e["what"], e["block"], e["peer"], e["epoch"]))
+
+    def clear_error(self, stream=None):
+        _lib.call("dtf_comm_clear_error", self.handle, self._s(stream))
+
+    def sleep(self, seconds, stream=None):
+        """Fault injection: keep the stream busy (an artificial straggler)."""
+        _lib.call("dtf_debug_sleep", int(seconds * 1e9), self._s(stream))
 
     def barrier(self, stream=None):
         _lib.call("dtf_comm_barrier", self.handle, self._s(stream))
@@ -191,10 +243,21 @@ class GradientEngine(object):
 
     def __init__(self, store, optimizer, rank=0, world=1, algo="auto", group=None,
                  bucket_bytes=int(os.environ.get("DTF_BUCKET_MB", "4")) << 20,
-                 placement="bytes", heap_extra_bytes=0, overlap=True):
+                 placement="bytes", heap_extra_bytes=0, overlap=True, replicas_to_aggregate=None, max_staleness=None,
+                 num_towers=1):
         self.store, self.opt, self.rank, self.world, self.group = store, optimizer, rank, world, group
         dev = store.device
+        self.num_towers = max(int(num_towers), 1)
+        self.max_staleness = max_staleness
+        # backup workers: aggregate the first R arrivals per owner (SyncReplicasOptimizer, distribute_train.py:146-155)
+        r = world if replicas_to_aggregate is None else int(replicas_to_aggregate)
+        self.backup_r = r if 0 < r < world else 0
         n_est = sum((v.numel + 7) // 8 * 8 for v in store.trainable_variables())
+        if self.backup_r:
+            if algo not in ("auto", "twoshot"):
+                raise ValueError("replicas_to_aggregate < num_workers needs the owner-sharded collective "
+                                 "(comm_algo auto or twoshot), not %r" % algo)
+            algo = "twoshot"  # peer-load kernel: the in-switch (NVLS) reduction cannot leave ranks out
         if algo == "auto":
             # small model on a pair of GPUs: one-shot K-AR (one kernel, replicated masters). Otherwise the two-shot
             # K-RS-OPT, over NVLS (in-switch reduce / broadcast) when a multicast mapping can be had.
@@ -236,6 +299,8 @@ class GradientEngine(object):
                 self._setup_pull()
         else:
             store.finalize(placement=placement, world=world, slots=optimizer.num_slots())
+        # fp32 masters of the filters are complete on every rank only when every rank applies the full update
+        store.masters_replicated = self.algo in ("local", "oneshot", "nccl") or world == 1
         self.n = store.n_params
         # buckets: contiguous [start, end) in arena order, flushed from the tail (last layers finish first)
         per_bucket = max(bucket_bytes // 4, 1024)
@@ -261,6 +326,30 @@ class GradientEngine(object):
         if self.overlap:
             store.grad_ready_hook = self._on_grad_ready
         self.kernel_launches = 0
+        # device-resident hyper-parameters: [lr, lr_t (Adam), int32 step, -]; the optimizer kernels read them at run
+        # time, so a replayed CUDA graph follows a learning-rate schedule and Adam's bias correction
+        self.hyper = torch.zeros(4, device=dev, dtype=torch.float32)
+        self._hyper_lr = None
+        self._hyper_step = None
+        self.sync_hyper(store.global_step)
+
+    # ------------------------------------------------------------------ device-resident hyper-parameters
+    def sync_hyper(self, global_step):
+        """Host -> device: the learning rate when the schedule moved it, the step counter when it was set from
+        outside (checkpoint restore). Never called inside a graph capture; cheap when nothing changed."""
+        lr = float(self.opt.learning_rate)
+        if lr != self._hyper_lr:
+            self.hyper[0:1].copy_(torch.tensor([lr], dtype=torch.float32))
+            self._hyper_lr = lr
+        if self._hyper_step != int(global_step):
+            self.hyper[2:3].view(torch.int32).copy_(torch.tensor([int(global_step)], dtype=torch.int32))
+            self._hyper_step = int(global_step)
+
+    def _hyper_advance(self):
+        """In-stream (capturable): step += 1 and lr_t refreshed on the device."""
+        from ..ops.raw import OPTIM_KINDS
+        _lib.call("dtf_optim_hyper_step", self.hyper, OPTIM_KINDS[self.opt.kind], self.opt.b1, self.opt.b2,
+                  _lib.stream_ptr())
 
     def _try_nvls_heap(self, need, dev, group):
         """NVLS heap through torch symmetric memory; every rank must succeed, otherwise all fall back to CUDA IPC."""
@@ -306,13 +395,24 @@ class GradientEngine(object):
             self.nopush.append((v.offset, v.offset + v.numel))
 
     # ------------------------------------------------------------------ per-step protocol
-    def begin_step(self, step):
-        """Call before backward: zero the gradient arena and re-arm the buckets."""
+    def begin_step(self, step, capturing=False):
+        """Call before the forward pass: zero the gradient arena, advance the device-side step / Adam rate, re-arm the
+        buckets (a bucket is complete when every tower has produced every gradient in it)."""
         self._step = step
+        if not capturing:
+            self.sync_hyper(step - 1)
+        self._hyper_advance()
+        self._hyper_step = step
         self.store.zero_grads()
+        if self.algo == "async" and self.comm is not None:
+            self.comm.async_begin()
         for bi, (_, _, vs) in enumerate(self.buckets):
-            self._pending[bi] = len(vs)
+            self._pending[bi] = len(vs) * self.num_towers
             self._launched[bi] = False
+
+    def note_replay(self):
+        """A captured step was replayed: mirror the device-side step counter on the host."""
+        self._hyper_step = (self._hyper_step or 0) + 1
 
     def _on_grad_ready(self, var):
         bi = self._bucket_of.get(var.name)
@@ -333,20 +433,24 @@ class GradientEngine(object):
     def _reduce_and_update(self, start, count):
         st, opt = self.store, self.opt
         step = self._step
+        tw = 1.0 / self.num_towers  # in-process towers summed into one arena: their mean folds into the scale
         if self.algo == "oneshot":
             self.comm.allreduce_optim(self.heap.offset_of("grad"), start, count, opt, step, st.master_arena,
-                                      st.slot_m, st.slot_v, st.shadow_arena, stream=self.comm_stream)
+                                      st.slot_m, st.slot_v, st.shadow_arena, gscale=tw / self.world,
+                                      stream=self.comm_stream, hyper=self.hyper)
         elif self.algo == "nccl":
             import torch.distributed as dist
             dist.all_reduce(st.grad_arena[start:start + count], group=self.group)
-            opt.apply_arena(st, step, 1.0 / self.world, start, count, refresh=False)
+            opt.apply_arena(st, step, tw / self.world, start, count, refresh=False, hyper=self.hyper)
         elif self.algo == "twoshot":
             # the bucket is split among its owners: owner bounds clamped to [start, start + count)
             end = start + count
             bounds = [min(max(b, start), end) for b in st.owner_bounds]
+            n_agg = self.backup_r or self.world
             self.comm.rs_optim_ag(self.heap.offset_of("grad"), bounds, opt, step, st.master_arena, st.slot_m,
-                                  st.slot_v, self.heap.offset_of("shadow"), stream=self.comm_stream,
-                                  nopush=self.nopush)
+                                  st.slot_v, self.heap.offset_of("shadow"), master_off=self.heap.offset_of("master"),
+                                  f32_range=st.f32_ranges[self.rank], gscale=tw / n_agg, stream=self.comm_stream,
+                                  nopush=self.nopush, hyper=self.hyper, backup_r=self.backup_r)
         else:
             raise RuntimeError(self.algo)
 
@@ -356,7 +460,7 @@ class GradientEngine(object):
         step = self._step
         cur = torch.cuda.current_stream(st.device)
         if self.algo == "local":
-            opt.apply_arena(st, step, 1.0)
+            opt.apply_arena(st, step, 1.0 / self.num_towers, hyper=self.hyper)
             st.global_step = step
             return
         self.comm_stream.wait_stream(cur)
@@ -375,7 +479,9 @@ class GradientEngine(object):
                                      st.owner_bounds, stream=self.comm_stream)
                 self.comm.async_apply(self.heap.offset_of("mailbox"), self.slice_cap, st.owner_bounds, opt, step,
                                       st.master_arena, st.slot_m, st.slot_v, self.heap.offset_of("shadow"),
-                                      stream=self.comm_stream)
+                                      stream=self.comm_stream, master_off=self.heap.offset_of("master"),
+                                      f32_range=st.f32_ranges[self.rank], max_staleness=self.max_staleness,
+                                      hyper=self.hyper)
             st.refresh_transposed_shadows()
             if self.algo == "twoshot" and self.nopush:
                 # peers pull the (transposed) shadows of these matrices from their owners: every rank must have
@@ -384,9 +490,35 @@ class GradientEngine(object):
         cur.wait_stream(self.comm_stream)
         st.global_step = step
 
-    def gather_masters(self):
-        """Make every rank's fp32 master arena complete (owner-sharded modes) -- used before checkpointing."""
-        if self.algo in ("twoshot", "async") and self.world > 1:
-            b16 = [b // 4 for b in self.store.owner_bounds]  # fp32 elements -> 16-byte units
-            self.comm.allgather_slices(self.heap.offset_of("master"), b16)
-            torch.cuda.current_stream().synchronize()
+    def needs_gather(self):
+        """True when fp32 masters / optimizer slots are complete only on their owner (owner-sharded modes)."""
+        return self.algo in ("twoshot", "async") and self.world > 1 and self.comm is not None
+
+    def gather_masters(self, slots=True):
+        """Make every rank's fp32 master arena (and optimizer slots) complete in the owner-sharded modes.
+        COLLECTIVE: every rank must call it at the same point of its stream (the session's checkpoint hooks agree on
+        the step through the control plane); a rank calling it alone would pair its barrier with the peers' next
+        gradient collective."""
+        if not self.needs_gather():
+            return
+        b16 = [b // 4 for b in self.store.owner_bounds]  # fp32 elements -> 16-byte units
+        tags = ["master"]
+        if slots:
+            tags += [t for t in ("slot_m", "slot_v") if t in self.heap.allocs]
+        for tag in tags:
+            self.comm.allgather_slices(self.heap.offset_of(tag), b16)
+        torch.cuda.current_stream().synchronize()
+        self.comm.check()
+
+    def replicas_equal(self):
+        """Collective check (every rank calls it): are the bf16 weights bit-identical on all ranks?"""
+        if self.world == 1 or self.group is None:
+            return True
+        import torch.distributed as dist
+        acc = self.store.shadow_arena.view(torch.int16).to(torch.int64)
+        idx = torch.arange(acc.numel(), device=acc.device, dtype=torch.int64) % 65521 + 1
+        sig = torch.stack([acc.sum(), (acc * idx).sum()])  # two checksums: plain and position-weighted
+        lo, hi = sig.clone(), sig.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=self.group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=self.group)
+        return bool(torch.equal(lo, hi))
