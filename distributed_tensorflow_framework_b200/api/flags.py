@@ -47,7 +47,10 @@ _DEFS = [
     ("placement", str, "bytes", "Owner-shard policy: bytes | round_robin (replica_device_setter order)."),
     ("save_checkpoint_secs", int, 600, "Chief checkpoint cadence in seconds (distribute_train.py:175)."),
     ("metrics_jsonl", str, "", "Append machine-readable step metrics (JSON lines) to this file; empty = off."),
-    ("compute_dtype", str, "bf16", "bf16 | fp32 compute on the CUDA path."),
+    ("save_checkpoint_steps", int, 0, "Checkpoint every N global steps instead of every save_checkpoint_secs."),
+    ("max_staleness", int, -1, "Async mode: drop a pushed gradient computed more than this many owner updates ago "
+     "(-1 = no bound)."),
+    ("use_cuda_graph", _str2bool, False, "Capture the training step into a CUDA graph and replay it."),
     ("lrn_compat_noop", _str2bool, False, "Reproduce the reference's `norm` no-op (distribute_tools.py:183-187)."),
 ]
 

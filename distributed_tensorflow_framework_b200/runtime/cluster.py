@@ -106,6 +106,31 @@ class Server(object):
                                     world_size=n, timeout=datetime.timedelta(seconds=self.timeout_s))
         return dist.group.WORLD
 
+    def control_store(self):
+        """Key-value store of the CPU control plane: the Server's own TCPStore, or -- under torchrun -- the store
+        torch.distributed was initialised with. None in a single-process run."""
+        if self.store is not None:
+            return self.store
+        try:
+            import torch.distributed as dist
+            if dist.is_initialized():
+                from torch.distributed import distributed_c10d as c10d
+                return c10d._get_default_store()
+        except Exception:  # pragma: no cover
+            pass
+        return None
+
+    def agree(self, tag, step, chief_value, is_chief):
+        """All workers adopt the chief's boolean for (tag, step): the chief publishes it, the others block on the key."""
+        st = self.control_store()
+        if st is None:
+            return bool(chief_value)
+        key = "agree/%s/%d" % (tag, int(step))
+        if is_chief:
+            st.set(key, b"1" if chief_value else b"0")
+            return bool(chief_value)
+        return st.get(key) == b"1"
+
     def join(self):
         while True:
             time.sleep(3600)

@@ -38,7 +38,8 @@ def build_operator(main, model_module=None, loss_module=None, input_module=None,
     task_index = getattr(main, "task_index", None)
     if task_index is None:
         task_index = flags.FLAGS.task_index or 0
-    if "TORCHELASTIC_RUN_ID" in os.environ or (not hasattr(main, "worker_hosts") and "WORLD_SIZE" in os.environ):
+    if "TORCHELASTIC_RUN_ID" in os.environ or os.environ.get("DTF_SPAWNED") or \
+            (not hasattr(main, "worker_hosts") and "WORLD_SIZE" in os.environ):
         cluster, job_name, task_index = cluster_from_env()
     else:
         ps_hosts = getattr(main, "ps_hosts", "") or flags.FLAGS.ps_hosts
@@ -108,7 +109,26 @@ def build_operator(main, model_module=None, loss_module=None, input_module=None,
         experiment_net = net_mod.Net(model=experiment_model)
         setattr(operator, "net", experiment_net)
     setattr(operator, "loss", loss)
+    if os.environ.get("DTF_SPAWNED"):
+        gpu_num = 1  # this process is ONE of the gpu_num towers spawned by run_main (one rank per GPU)
     setattr(operator, "gpu_num", gpu_num)
+    # learning-rate handler (distribute_learningrate.py:12-50): an instance, or a class name looked up like the other
+    # plugins and constructed from --train_learning_rate / --learning_rate_json. The optimizer reads its current
+    # value every step (on CUDA through the device-resident hyper-parameters), the chief persists it with every
+    # checkpoint, and a restarted run picks the saved value up again.
+    lr_handler = getattr(main, "learning_rate", None)
+    if lr_handler is not None:
+        if isinstance(lr_handler, (str, type)):
+            from ..plugins import learningrate as lr_mod
+            cls = lr_handler if isinstance(lr_handler, type) else \
+                (getattr(lr_mod, lr_handler, None) or annotations.registered(lr_handler))
+            lr_handler = cls(flags.FLAGS.train_learning_rate, flags.FLAGS.learning_rate_json)
+        setattr(operator, "learning_rate", lr_handler)
+        opt = operator.optimizer
+        if optimizer is None or not (callable(opt._lr) or hasattr(opt._lr, "learning_rate")):
+            opt._lr = lr_handler
+    if getattr(main, "sync_mode", None):
+        setattr(operator, "sync_mode", getattr(main, "sync_mode"))
     # advices placed on `main` (in addition to the class-level @get_advice of the reference) are forwarded
     for key in ("pre_fn", "post_fn", "pre_process_fn", "post_process_fn", "init_fn", "parse_data_dir_fn",
                 "pre_eval_fn", "post_eval_fn"):
@@ -117,7 +137,49 @@ def build_operator(main, model_module=None, loss_module=None, input_module=None,
     return operator
 
 
+def _spawn_towers(n):
+    """`@gpu_num(N)` without a launcher: the reference drives N GPUs from one process
+    (`for i in range(num_devices): with tf.device('/gpu:%d')`, distribute_train.py:116-139). Here every tower is its
+    own process on its own GPU (one rank per GPU over the peer-memory collectives): re-run this script N times with
+    the torchrun environment variables set and wait for all of them. Returns the worst exit code."""
+    import socket
+    import subprocess
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    procs = []
+    for r in range(n):
+        env = dict(os.environ, DTF_SPAWNED="1", RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(n),
+                   LOCAL_WORLD_SIZE=str(n), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable] + sys.argv, env=env))
+    rc = 0
+    for p in procs:
+        rc = max(rc, abs(p.wait()))
+    return rc
+
+
+def _should_spawn(main):
+    if os.environ.get("DTF_SPAWNED") or "TORCHELASTIC_RUN_ID" in os.environ or "WORLD_SIZE" in os.environ:
+        return 0
+    n = int(getattr(main, "gpu_num", 0) or 0)
+    job = getattr(main, "job_name", None) or flags.FLAGS.job_name or "worker"
+    workers = getattr(main, "worker_hosts", "") or flags.FLAGS.worker_hosts or ""
+    if n <= 1 or job == "ps" or getattr(main, "mode", None) != "Train" or len([h for h in str(workers).split(",") if h.strip()]) > 1:
+        return 0
+    try:
+        import torch
+        return n if torch.cuda.is_available() and torch.cuda.device_count() >= n else 0
+    except Exception:  # pragma: no cover
+        return 0
+
+
 def run_main(main, **kwargs):
+    n = _should_spawn(main)
+    if n:
+        rc = _spawn_towers(n)
+        if rc:
+            raise RuntimeError("a tower process failed (exit code %d)" % rc)
+        return None
     operator = build_operator(main, **kwargs)
     operator.run()
     return operator

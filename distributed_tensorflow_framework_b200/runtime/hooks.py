@@ -157,11 +157,19 @@ class SummarySaverHook(SessionRunHook):
 
 
 class CheckpointSaverHook(SessionRunHook):
-    """Chief-only periodic save (save_checkpoint_secs=600, distribute_train.py:175) + final save at end."""
+    """Periodic save (save_checkpoint_secs=600, distribute_train.py:175) + final save at end.
 
-    def __init__(self, saver, checkpoint_dir, save_secs=600, save_steps=None):
+    Plain mode (replicated masters): installed on the chief only, local timer. Collective mode (owner-sharded
+    masters: saving needs a gather that every rank must enter): installed on EVERY rank; the ranks save at the same
+    global step -- a step cadence is deterministic, a wall-clock cadence is decided by the chief and agreed through
+    `agree_fn(step, chief_decision)` every `probe_every` steps; `write` is True on the chief only."""
+
+    def __init__(self, saver, checkpoint_dir, save_secs=600, save_steps=None, write=True, collective=False,
+                 agree_fn=None, probe_every=10):
         self._saver, self._dir = saver, checkpoint_dir
         self._timer = SecondOrStepTimer(every_secs=save_secs if save_steps is None else None, every_steps=save_steps)
+        self._by_steps = save_steps is not None
+        self._write, self._collective, self._agree, self._probe = write, collective, agree_fn, max(int(probe_every), 1)
         self._last_saved = None
 
     def after_create_session(self, session):
@@ -169,14 +177,21 @@ class CheckpointSaverHook(SessionRunHook):
 
     def after_run(self, run_context, run_values):
         step = run_context.session.global_step
-        if self._timer.should_trigger_for_step(step):
+        if not self._collective or self._by_steps:
+            trigger = self._timer.should_trigger_for_step(step)
+        elif step % self._probe != 0:
+            trigger = False
+        else:
+            mine = self._timer.should_trigger_for_step(step) if self._write else False
+            trigger = self._agree(step, mine) if self._agree is not None else mine
+        if trigger:
             self._timer.update_last_triggered_step(step)
             self._save(run_context.session, step)
 
     def _save(self, session, step):
         if self._last_saved == step:
             return
-        self._saver.save(self._dir, step)
+        self._saver.save(self._dir, step, write=self._write)
         self._last_saved = step
 
     def end(self, session):
@@ -184,9 +199,12 @@ class CheckpointSaverHook(SessionRunHook):
 
 
 class HeartbeatHook(SessionRunHook):
-    """Failure detection (extension; the reference has none): every N steps each rank bumps a counter in
-    every peer's flag page; a peer whose counter has not moved for `timeout_s` raises WorkerLostError, which the
-    session treats as recoverable (reload the last checkpoint)."""
+    """Failure detection (extension; the reference has none). Two signals:
+    * every step, the communicator's host-mapped error record is read (no CUDA call): a device-side wait that ran
+      into its time bound (a peer that never reached a barrier) raises WorkerLostError at once;
+    * every N steps each rank bumps a counter in every peer's flag page; a peer whose counter has not moved for
+      `timeout_s` raises WorkerLostError too.
+    The session treats WorkerLostError as recoverable (reload the last checkpoint)."""
 
     def __init__(self, comm, every_n_steps=50, timeout_s=120.0):
         self._comm, self._every, self._timeout = comm, every_n_steps, timeout_s
@@ -195,8 +213,11 @@ class HeartbeatHook(SessionRunHook):
         self._last_change = {}
 
     def after_run(self, run_context, run_values):
+        if self._comm is None:
+            return
+        self._comm.check()
         step = run_context.session.global_step
-        if self._comm is None or step % self._every != 0:
+        if step % self._every != 0:
             return
         self._beat += 1
         seen = self._comm.heartbeat(self._beat).tolist()

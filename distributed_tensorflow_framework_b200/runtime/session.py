@@ -30,14 +30,22 @@ class Scaffold(object):
 class Saver(object):
     """tf.train.Saver(sharded=True, max_to_keep=5) over a VariableStore (+ optimizer slots)."""
 
-    def __init__(self, store, optimizer=None, max_to_keep=5, num_shards=1, gather_fn=None):
+    def __init__(self, store, optimizer=None, max_to_keep=5, num_shards=1, gather_fn=None, lr_handler=None):
+        """`gather_fn`: collective that completes the fp32 masters / slots on every rank in the owner-sharded modes
+        (GradientEngine.gather_masters) -- `save` must then be called by EVERY rank at the same step, and only the
+        rank with write=True touches the disk. `num_shards` > 1 writes one data shard per owner rank, the layout the
+        reference's ps sharding produces (one shard per ps device). `lr_handler`: a LearningRate whose JSON file is
+        written next to every checkpoint (/root/reference/distribute_learningrate.py:21-32)."""
         self.store, self.optimizer, self.max_to_keep = store, optimizer, max_to_keep
         self.num_shards = max(int(num_shards), 1)
         self.gather_fn = gather_fn
+        self.lr_handler = lr_handler
 
-    def save(self, model_dir, step, basename="model.ckpt"):
+    def save(self, model_dir, step, basename="model.ckpt", write=True):
         if self.gather_fn is not None:
             self.gather_fn()
+        if not write:
+            return None
         tensors, shard_of = {}, {}
         for v in self.store.all_variables():
             tensors[v.name] = v.logical(v.master.detach()).float().cpu().contiguous().numpy()
@@ -62,6 +70,8 @@ class Saver(object):
                     except OSError:
                         pass
         tb.write_checkpoint_state(model_dir, name, all_paths)
+        if self.lr_handler is not None and getattr(self.lr_handler, "save_path", None):
+            self.lr_handler.save()
         logger.info("Saving checkpoints for %d into %s.", int(step), prefix)
         return prefix
 
@@ -83,7 +93,12 @@ class MonitoredTrainingSession(object):
     def __init__(self, master="", is_chief=True, checkpoint_dir=None, scaffold=None, hooks=None, chief_only_hooks=None,
                  save_checkpoint_secs=600, save_checkpoint_steps=None, save_summaries_steps=100, config=None,
                  stop_grace_period_secs=60, log_step_count_steps=100, store=None, optimizer=None, saver=None,
-                 summary_writer=None, barrier_fn=None, max_recoveries=3):
+                 summary_writer=None, barrier_fn=None, max_recoveries=3, collective_save=False, agree_fn=None,
+                 on_recover=None):
+        """`collective_save`: the checkpoint needs a collective gather (owner-sharded masters), so the saver hook runs
+        on EVERY rank and the ranks agree on the saving step (step cadence, or the chief's wall-clock decision passed
+        through `agree_fn(step, chief_decision) -> bool` on the control plane); only the chief writes.
+        `on_recover`: called after a recoverable failure before the checkpoint is reloaded (re-arm the communicator)."""
         self.master, self.is_chief, self.checkpoint_dir = master, is_chief, checkpoint_dir
         self.scaffold = scaffold or Scaffold()
         self.store = store
@@ -96,11 +111,18 @@ class MonitoredTrainingSession(object):
         self._recoveries = 0
         self._stop = False
         self._writer = summary_writer
+        self._on_recover = on_recover
+        want_ckpt = checkpoint_dir and self.saver is not None and (save_checkpoint_secs or save_checkpoint_steps)
+        if want_ckpt and collective_save and not is_chief:
+            self._hooks.append(H.CheckpointSaverHook(self.saver, checkpoint_dir, save_checkpoint_secs,
+                                                     save_checkpoint_steps, write=False, collective=True,
+                                                     agree_fn=agree_fn))
         if is_chief:
             self._hooks += list(chief_only_hooks or [])
-            if checkpoint_dir and self.saver is not None and (save_checkpoint_secs or save_checkpoint_steps):
+            if want_ckpt:
                 self._hooks.append(H.CheckpointSaverHook(self.saver, checkpoint_dir, save_checkpoint_secs,
-                                                         save_checkpoint_steps))
+                                                         save_checkpoint_steps, write=True,
+                                                         collective=collective_save, agree_fn=agree_fn))
             if checkpoint_dir and log_step_count_steps:
                 self._hooks.append(H.StepCounterHook(every_n_steps=log_step_count_steps, summary_writer=self._writer))
             if self._writer is not None and save_summaries_steps:
@@ -159,6 +181,8 @@ class MonitoredTrainingSession(object):
                 if self._recoveries > self._max_recoveries:
                     raise
                 logger.warn("recoverable failure (%s): restoring from the last checkpoint", e)
+                if self._on_recover is not None:
+                    self._on_recover(e)
                 self._init_or_restore()
         if ctx.stop_requested:
             self._stop = True

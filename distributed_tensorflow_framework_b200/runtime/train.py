@@ -27,8 +27,9 @@ from .session import MonitoredTrainingSession, Saver, Scaffold
 from .sync_replicas import AsyncReplicasOptimizer, SyncReplicasOptimizer
 
 
-def _sync_mode():
-    m = (flags.FLAGS.sync_mode or "").lower()
+def _sync_mode(annotated=None):
+    """sync | backup | async: the --sync_mode flag wins, then the @sync_mode annotation, then --sync_replicas."""
+    m = (flags.FLAGS.sync_mode or annotated or "").lower()
     if m:
         return m
     if not flags.FLAGS.sync_replicas:
@@ -79,22 +80,31 @@ class Train(object):
         group = self.server.init_process_group() if num_workers > 1 else None
         pre_train_result = None if pre_fn is None else pre_fn(args, kwargs)
 
-        mode = _sync_mode()
+        mode = _sync_mode(getattr(self, "sync_mode", None))
         if replicas_to_aggregate is None:
             replicas_to_aggregate = num_workers
+        if mode == "backup" and replicas_to_aggregate >= num_workers:
+            replicas_to_aggregate = max(num_workers - 1, 1)  # "backup" without a count: one backup worker
         if mode == "sync" and replicas_to_aggregate < num_workers:
             mode = "backup"
         algo = flags.FLAGS.comm_algo
         if mode == "async" and device.type == "cuda" and num_workers > 1:
             algo = "async"
-        elif device.type == "cuda" and num_workers > 1 and getattr(self, "ps_equivalent", False) and algo == "auto":
+        elif device.type == "cuda" and num_workers > 1 and self.cluster.num_tasks("ps") > 0 and algo == "auto":
+            # a cluster that declares ps tasks asks for parameter-server semantics: owner-sharded masters, push =
+            # reduce-scatter + owner update, pull = all-gather (distribute_train.py:109-110)
             algo = "twoshot"
         base_opt = self.optimizer
+        use_graph = getattr(self, "use_cuda_graph", None)
+        if use_graph is None:
+            use_graph = flags.FLAGS.use_cuda_graph
         trainer = Trainer(self.net, self.loss, base_opt, device=device, rank=self.task_index, world=num_workers,
                           group=group, gpu_num=num_devices, algo=algo, placement=flags.FLAGS.placement,
-                          use_cuda_graph=getattr(self, "use_cuda_graph", False), pre_process_fn=pre_process_fn,
+                          use_cuda_graph=use_graph, pre_process_fn=pre_process_fn,
                           post_process_fn=post_process_fn, pre_train_result=pre_train_result,
-                          seed=getattr(self, "seed", 0))
+                          seed=getattr(self, "seed", 0),
+                          replicas_to_aggregate=replicas_to_aggregate if mode == "backup" else None,
+                          max_staleness=flags.FLAGS.max_staleness if mode == "async" else None)
         self.trainer = trainer
 
         # input pipeline (one logical pipeline per tower, like distribute_train.py:119-128)
@@ -126,8 +136,25 @@ class Train(object):
             logger.info("Worker %d: Waiting for session to be initialized..." % self.task_index)
 
         writer = EventFileWriter(self.model_dir) if (is_chief and self.model_dir) else None
-        saver = Saver(store, base_opt, num_shards=num_workers if getattr(self, "sharded_checkpoint", False) else 1,
-                      gather_fn=trainer.engine.gather_masters if trainer.engine is not None else None)
+        engine = trainer.engine
+        collective_save = engine is not None and engine.needs_gather()
+        # owner-sharded masters: one data shard per owner rank (what the reference's ps sharding produces) and a
+        # gather that every rank enters at the agreed step; replicated masters: the chief saves alone
+        sharded = getattr(self, "sharded_checkpoint", None)
+        if sharded is None:
+            sharded = collective_save
+        saver = Saver(store, base_opt, num_shards=num_workers if sharded else 1,
+                      gather_fn=engine.gather_masters if collective_save else None,
+                      lr_handler=getattr(self, "learning_rate", None) if is_chief else None)
+
+        def agree(step, chief_decision):
+            return self.server.agree("ckpt", step, chief_decision, is_chief)
+
+        def on_recover(err):
+            if engine is not None and engine.comm is not None:
+                torch.cuda.synchronize(device)
+                engine.comm.clear_error()
+                torch.cuda.synchronize(device)
 
         def barrier():
             if group is not None:
@@ -157,6 +184,11 @@ class Train(object):
             with nvtx.range("train_step"):
                 loss = trainer.step(batches)
             state["loss"] = loss
+            if store.global_step < total_step:
+                # while the device runs this step: load the next host batch and start its H2D copy on the copy stream
+                nxt = [self._next_host_batch(name_queue, placeholder_queue) for _ in range(num_devices)]
+                trainer.prefetch(nxt)
+                pending["batches"] = nxt
             fault.maybe_kill(self.task_index, store.global_step)
             return {"loss": loss, "summaries": trainer.last_summaries}
 
@@ -166,7 +198,9 @@ class Train(object):
                                       config={"allow_soft_placement": True, "log_device_placement": False},
                                       stop_grace_period_secs=60, log_step_count_steps=100, store=store,
                                       optimizer=base_opt, saver=saver, summary_writer=writer,
-                                      barrier_fn=barrier) as sess:
+                                      barrier_fn=barrier, collective_save=collective_save, agree_fn=agree,
+                                      save_checkpoint_steps=flags.FLAGS.save_checkpoint_steps or None,
+                                      on_recover=on_recover) as sess:
             logger.info("Worker %d: Session initialization complete." % self.task_index)
             self.session = sess
             while not sess.should_stop():
