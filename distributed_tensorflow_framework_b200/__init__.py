@@ -27,13 +27,13 @@ from .engine.trainer import Trainer  # noqa: F401
 from .engine.variables import VariableStore, variable_scope  # noqa: F401
 from .runtime.cluster import ClusterSpec, Server, DoneQueue  # noqa: F401
 from .runtime.container import build_operator, run_main  # noqa: F401
-from .runtime.estimator import DistributeEstimator, Estimator, RunConfig  # noqa: F401
+from .runtime.estimator import DistributeEstimator, Estimator, EstimatorSpec, RunConfig  # noqa: F401
 from .runtime.evalop import Eval  # noqa: F401
 from .runtime.experiment import DistributeExperiment  # noqa: F401
 from .runtime.hooks import (ExamplesPerSecondHook, StopAtStepHook, StepCounterHook, CheckpointSaverHook,  # noqa: F401
                             SummarySaverHook, SessionRunHook)
 from .runtime.placement import local_device_setter, replica_device_setter, owner_map  # noqa: F401
-from .runtime.session import MonitoredTrainingSession, Scaffold, Saver  # noqa: F401
+from .runtime.session import MonitoredTrainingSession, Scaffold, Saver, WorkerLostError  # noqa: F401
 from .runtime.sync_replicas import (SyncReplicasOptimizer, AsyncReplicasOptimizer,  # noqa: F401
                                     InProcessParameterServer, ConditionalAccumulator)
 from .runtime.train import Train  # noqa: F401

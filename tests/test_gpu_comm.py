@@ -1,5 +1,7 @@
-"""Peer-memory collectives across real GPUs (needs >= 2 devices; one process per GPU via torchrun)."""
+"""Peer-memory collectives and the Train / Eval operators across real GPUs (one process per GPU via torchrun).
+Parametrised over 2 / 4 / 8 ranks; a world size the box does not have is skipped."""
 import os
+import socket
 import subprocess
 import sys
 
@@ -7,14 +9,58 @@ import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-@pytest.mark.parametrize("world", [2])
-def test_collectives_and_data_parallel_trainer(world):
+def _port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _torchrun(world, script, *args, timeout=900, extra=()):
     if torch.cuda.device_count() < world:
         pytest.skip("needs %d GPUs" % world)
-    here = os.path.dirname(os.path.abspath(__file__))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
-           "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(here, "_comm_worker.py")]
-    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+           "--master-addr", "127.0.0.1", "--master-port", str(_port())] + list(extra) + \
+          [os.path.join(HERE, script)] + [str(a) for a in args]
+    env = dict(os.environ)
+    env.pop("DTF_KILL_RANK_AT_STEP", None)
+    return subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout, env=env)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_collectives_and_data_parallel_trainer(world):
+    p = _torchrun(world, "_comm_worker.py")
     assert p.returncode == 0 and "COMM_WORKER_OK" in p.stdout, p.stdout[-4000:]
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_owner_sharded_fp32_backup_async_graph_and_timeouts(world):
+    p = _torchrun(world, "_comm_worker2.py")
+    assert p.returncode == 0 and "COMM_WORKER2_OK" in p.stdout, p.stdout[-5000:]
+
+
+@pytest.mark.parametrize("sync", ["sync", "backup", "async"])
+def test_train_operator_save_resume_eval_multi_rank(tmp_path, sync):
+    world = 2
+    md = str(tmp_path / sync)
+    os.makedirs(md)
+    p = _torchrun(world, "_train_worker.py", md, sync, 2)
+    assert p.returncode == 0 and "TRAIN_WORKER_OK 20" in p.stdout, p.stdout[-5000:]
+    assert "Saving checkpoints for 5 " in p.stdout or "Saving checkpoints for 5" in p.stdout, p.stdout[-3000:]
+    # resume: a second launch restores step 20 on every rank and continues to 30
+    p = _torchrun(world, "_train_worker.py", md, sync, 3)
+    assert p.returncode == 0 and "TRAIN_WORKER_OK 30" in p.stdout, p.stdout[-5000:]
+    assert "Restoring parameters from" in p.stdout
+
+
+def test_kill_one_rank_and_resume_from_checkpoint(tmp_path):
+    """DTF_KILL_RANK_AT_STEP kills the last rank at step 13 of the first attempt. The survivor's collective runs into
+    its time bound (error record, WorkerLostError) instead of hanging; torchrun restarts the group, which restores
+    the step-10 checkpoint and finishes with global_step continuing to 20."""
+    md = str(tmp_path / "kill")
+    os.makedirs(md)
+    p = _torchrun(2, "_train_worker.py", md, "sync", 2, "kill", extra=("--max-restarts", "1"), timeout=900)
+    assert p.returncode == 0 and "TRAIN_WORKER_OK 20 restart=1" in p.stdout, p.stdout[-6000:]
+    assert "Restoring parameters from" in p.stdout and "model.ckpt-10" in p.stdout
