@@ -19,6 +19,34 @@ from . import variables as V
 from .variables import (ConstantInitializer, TruncatedNormalInitializer, XavierInitializer, variable_scope)
 
 _training = True
+_emulate_bf16 = False
+
+
+class _RoundBF16(torch.autograd.Function):
+    """Oracle helper: rounds a tensor to bf16 precision in the forward pass (optional) and its gradient in the
+    backward pass -- the two places where the CUDA path stores an activation / a data gradient as bf16."""
+
+    @staticmethod
+    def forward(ctx, x, fwd):
+        return x.to(torch.bfloat16).float() if fwd else x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).float(), None
+
+
+def emulate_bf16(flag: bool):
+    """CPU oracle mode: every layer output (and the gradient flowing back into it) is rounded to bf16 exactly where
+    the CUDA kernels store bf16, while all arithmetic stays fp32. With identical (bf16-representable) weights the
+    CPU path then reproduces the CUDA forward pass almost bit for bit, so ReLU / max-pool decisions agree and one
+    training step can be compared per variable with a tight bound (tests/test_gpu_round2.py). Returns the old flag."""
+    global _emulate_bf16
+    old, _emulate_bf16 = _emulate_bf16, bool(flag)
+    return old
+
+
+def _q(x, fwd=True):
+    return _RoundBF16.apply(x, fwd) if _emulate_bf16 else x
 
 
 def set_training(flag: bool):
@@ -115,7 +143,7 @@ def _conv_impl(x, w, b, stride, relu, fork=False, emit_stats=False):
     y = F.conv2d(xn, w.master.permute(3, 2, 0, 1), b.master if b is not None else None, stride=(sh, sw))
     if relu:
         y = F.relu(y)
-    return y.permute(0, 2, 3, 1)
+    return _q(y.permute(0, 2, 3, 1))
 
 
 def conv(layer_name, x, in_channels, out_channels, kernel_size=[3, 3], stride=[1, 1, 1, 1]):
@@ -160,7 +188,7 @@ def acti_layer(x):
     """ReLU -- distribute_tools.py:123-128."""
     if x.is_cuda:
         return Fn.relu(x.contiguous())
-    return F.relu(x)
+    return _q(F.relu(x))
 
 
 def deconv(layer_name, x, in_channels, out_channels, output_shape=[32, 224, 224, 64], kernel_size=[3, 3],
@@ -186,7 +214,7 @@ def deconv(layer_name, x, in_channels, out_channels, output_shape=[32, 224, 224,
         full = F.conv_transpose2d(xn, w.master.permute(3, 2, 0, 1), stride=(sh, sw))
         need_h, need_w = pt + out_hw[0], pl + out_hw[1]
         full = F.pad(full, (0, max(need_w - full.shape[3], 0), 0, max(need_h - full.shape[2], 0)))
-        return full[:, :, pt:need_h, pl:need_w].permute(0, 2, 3, 1)
+        return _q(full[:, :, pt:need_h, pl:need_w].permute(0, 2, 3, 1))
 
 
 def deconv_eval(layer_name, x, in_channels, out_channels, output_shape=[32, 224, 224, 64], kernel_size=[3, 3],
@@ -209,7 +237,7 @@ def pool(layer_name, x, kernel=[1, 2, 2, 1], stride=[1, 2, 2, 1], is_max_pool=Tr
         num = F.avg_pool2d(F.pad(xn, pad), k, s, divisor_override=1)
         cnt = F.avg_pool2d(F.pad(torch.ones_like(xn), pad), k, s, divisor_override=1)
         y = num / cnt
-    return y.permute(0, 2, 3, 1)
+    return _q(y.permute(0, 2, 3, 1))
 
 
 def batch_norm(x):
@@ -221,7 +249,7 @@ def batch_norm(x):
     xf = x.float()
     mean = xf.mean(0, keepdim=True)
     var = xf.var(0, unbiased=False, keepdim=True)
-    return (xf - mean) * torch.rsqrt(var + epsilon)
+    return _q((xf - mean) * torch.rsqrt(var + epsilon))
 
 
 def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momentum=0.1, stats_part=None):
@@ -246,7 +274,7 @@ def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momen
     y = y.reshape(x.shape)
     if residual is not None:
         y = y + residual.float()
-    return F.relu(y) if relu else y
+    return _q(F.relu(y) if relu else y)
 
 
 def norm(name, x, lsize=4):
@@ -258,7 +286,8 @@ def norm(name, x, lsize=4):
     if x.is_cuda:
         return Fn.lrn(x.contiguous(), lsize, bias, alpha, beta)
     n = 2 * lsize + 1
-    return F.local_response_norm(x.float().permute(0, 3, 1, 2), n, alpha=alpha * n, beta=beta, k=bias).permute(0, 2, 3, 1)
+    return _q(F.local_response_norm(x.float().permute(0, 3, 1, 2), n, alpha=alpha * n, beta=beta,
+                                    k=bias).permute(0, 2, 3, 1))
 
 
 def _fc_impl(layer_name, x, out_nodes, relu, out_fp32=False):
@@ -274,7 +303,8 @@ def _fc_impl(layer_name, x, out_nodes, relu, out_fp32=False):
                 flat = flat.to(torch.bfloat16)
             return Fn.linear(flat.contiguous(), w, b, relu=relu, out_fp32=out_fp32)
         y = x.float().reshape(-1, size) @ w.master + b.master
-        return F.relu(y) if relu else y
+        # fp32 logits on CUDA (out_fp32): only the gradient is rounded there
+        return _q(F.relu(y) if relu else y, fwd=not out_fp32)
 
 
 def FC_layer(layer_name, x, out_nodes):
@@ -292,14 +322,14 @@ def global_avg_pool(x):
     H, W = x.shape[1], x.shape[2]
     if x.is_cuda:
         return Fn.pool2d(x.contiguous(), (H, W), (H, W), False).reshape(x.shape[0], x.shape[3])
-    return x.float().mean(dim=(1, 2))
+    return _q(x.float().mean(dim=(1, 2)))
 
 
 def add_relu(a, b, relu=True):
     if a.is_cuda:
         return Fn.add(a.contiguous(), b.contiguous(), relu)
     y = a.float() + b.float()
-    return F.relu(y) if relu else y
+    return _q(F.relu(y) if relu else y)
 
 
 def weight(kernel_shape, is_uniform=True):

@@ -258,7 +258,10 @@ class VariableStore(object):
                     cur_owner += 1
                     self.owner_bounds[cur_owner] = off
             v.offset = off
-            off += (v.numel + 7) // 8 * 8  # 16-byte aligned bf16 views, 32-byte aligned fp32 views
+            # every variable starts on a 128-byte line of the bf16 arenas (256 bytes in the fp32 ones): TMA tiles of a
+            # filter and the red.add rows of its gradient then never straddle lines (an odd-sized variable in front,
+            # e.g. 1000 logits biases, used to shift every later filter by 80 bytes: 1x1-conv GEMMs ran 20 % slower)
+            off += padded_numel(v.numel)
             if small(v):
                 key = v.owner if rr else 0
                 f32_lo.setdefault(key, v.offset)
@@ -368,6 +371,13 @@ class VariableStore(object):
         if strict and missing:
             raise KeyError("missing variables in checkpoint: %s" % missing)
         return missing
+
+
+ARENA_ALIGN = 64  # elements
+
+
+def padded_numel(n):
+    return (n + ARENA_ALIGN - 1) // ARENA_ALIGN * ARENA_ALIGN
 
 
 def _taps(shape):

@@ -19,6 +19,7 @@ from typing import List, Optional
 
 import torch
 
+from ..engine import variables as V
 from ..ops import _lib
 
 _ALIGN = 256
@@ -252,7 +253,7 @@ class GradientEngine(object):
         # backup workers: aggregate the first R arrivals per owner (SyncReplicasOptimizer, distribute_train.py:146-155)
         r = world if replicas_to_aggregate is None else int(replicas_to_aggregate)
         self.backup_r = r if 0 < r < world else 0
-        n_est = sum((v.numel + 7) // 8 * 8 for v in store.trainable_variables())
+        n_est = sum(V.padded_numel(v.numel) for v in store.trainable_variables())
         if self.backup_r:
             if algo not in ("auto", "twoshot"):
                 raise ValueError("replicas_to_aggregate < num_workers needs the owner-sharded collective "
@@ -309,7 +310,7 @@ class GradientEngine(object):
         cur_start, cur_vars = 0, []
         for v in tv:
             cur_vars.append(v)
-            end = v.offset + (v.numel + 7) // 8 * 8
+            end = v.offset + V.padded_numel(v.numel)
             if end - cur_start >= per_bucket:
                 self.buckets.append([cur_start, end, cur_vars])
                 cur_start, cur_vars = end, []

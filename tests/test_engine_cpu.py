@@ -154,3 +154,32 @@ def test_weight_decay_term_joins_the_losses_collection(store):
     (name, term), = store.losses
     assert name == "w/weight_loss"
     assert torch.allclose(term, 0.5 * 0.5 * (store.vars["w"].master ** 2).sum())
+
+
+def test_bf16_emulating_oracle_rounds_activations_and_gradients():
+    """layers.emulate_bf16: layer outputs become bf16-representable, the data gradient entering a layer is rounded,
+    parameter gradients stay fp32, and the mode is off by default."""
+    import torch
+    import distributed_tensorflow_framework_b200 as dtf
+    from distributed_tensorflow_framework_b200 import models
+    from distributed_tensorflow_framework_b200.engine import layers
+    torch.manual_seed(0)
+    x = torch.rand(4, 32, 32, 3)
+    y = torch.randint(0, 10, (4,))
+    tr = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.0))
+    tr.build(x, y)
+    l_plain, g_plain = tr._forward_backward([(x, y)])
+    assert layers.emulate_bf16(True) is False
+    try:
+        with V.using_store(tr.store):
+            h = layers.conv("conv1", x, 3, 64, [5, 5])
+        assert torch.equal(h, h.to(torch.bfloat16).float())
+        l_emu, g_emu = tr._forward_backward([(x, y)])
+    finally:
+        assert layers.emulate_bf16(False) is True
+    assert abs(float(l_plain) - float(l_emu)) < 2e-2
+    for (ga, va), (gb, vb) in zip(g_plain[0], g_emu[0]):
+        assert va is vb and ga.dtype == torch.float32 == gb.dtype
+        if float(ga.norm()) > 1e-6:
+            assert float((ga - gb).norm() / ga.norm()) < 0.25, va.name
+    assert any(not torch.equal(ga, gb) for (ga, _), (gb, _) in zip(g_plain[0], g_emu[0]))

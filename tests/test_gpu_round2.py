@@ -101,11 +101,14 @@ def test_prefetched_steps_equal_plain_steps():
     assert b._copy_stream is not None
 
 
-@pytest.mark.parametrize("name,bound", [("ResNet18", 0.12), ("ResNet50", 0.15)])
+@pytest.mark.parametrize("name,bound", [("ResNet18", 0.05), ("ResNet50", 0.06)])
 def test_resnet_step_gradients_match_cpu_oracle_per_variable(name, bound):
-    """One forward/backward of a small ResNet on the CUDA kernels against the CPU fp32 path with IDENTICAL weights:
+    """One forward/backward of a small ResNet on the CUDA kernels against the CPU oracle with IDENTICAL weights:
     per-variable relative L2 error of the gradient (a wrong batch-norm backward, residual fork or packed filter
-    gradient shows up as an O(1) error in the variables it touches), loss within 1 %."""
+    gradient shows up as an O(1) error in the variables it touches), loss within 0.3 %. The oracle computes in fp32
+    but rounds activations / data gradients to bf16 where the kernels store bf16 (layers.emulate_bf16): against a
+    plain fp32 run the ReLU masks of a deep net differ in ~0.3 % of the positions per layer, which alone puts 30-40 %
+    of noise on the first layers' gradients and would hide real faults."""
     import distributed_tensorflow_framework_b200 as dtf
     from distributed_tensorflow_framework_b200 import models
     torch.manual_seed(4)
@@ -114,7 +117,8 @@ def test_resnet_step_gradients_match_cpu_oracle_per_variable(name, bound):
     class Small(cls):
         num_classes = 16
 
-    x = torch.rand(8, 64, 64, 3)
+    from distributed_tensorflow_framework_b200.engine import layers
+    x = torch.rand(8, 64, 64, 3).to(torch.bfloat16).float()
     y = torch.randint(0, 16, (8,))
     cpu = _trainer(Small, "cpu", dtf.GradientDescentOptimizer(0.0))
     gpu = _trainer(Small, "cuda:0", dtf.GradientDescentOptimizer(0.0))
@@ -128,12 +132,16 @@ def test_resnet_step_gradients_match_cpu_oracle_per_variable(name, bound):
         for v in cpu.store.trainable_variables():
             if v.kind in ("conv_w", "fc_w"):
                 v.master.copy_(v.master.to(torch.bfloat16).float())
-    lc, tower_grads = cpu._forward_backward([(x, y)])
+    old = layers.emulate_bf16(True)
+    try:
+        lc, tower_grads = cpu._forward_backward([(x, y)])
+    finally:
+        layers.emulate_bf16(old)
     cg = {v.name: g for g, v in tower_grads[0]}
     gpu.engine.begin_step(1)
     lg, _ = gpu._forward_backward([(x.cuda(), y.cuda())])
     torch.cuda.synchronize()
-    assert abs(float(lc) - float(lg)) < 1e-2 * max(1.0, abs(float(lc))), (float(lc), float(lg))
+    assert abs(float(lc) - float(lg)) < 3e-3 * max(1.0, abs(float(lc))), (float(lc), float(lg))
     worst = []
     for v in gpu.store.trainable_variables():
         gc = cg[v.name].float()
