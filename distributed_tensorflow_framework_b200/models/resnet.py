@@ -14,7 +14,19 @@ from ..plugins.model import Model
 EPILOGUE_BN_STATS = False
 
 
+_RELU = True
+
+
+def set_relu(flag):
+    """Test hook: build the networks without activations (a linear conv / batch-norm / residual stack), so that a
+    gradient comparison against the CPU oracle is not blurred by ReLU decisions. Returns the previous setting."""
+    global _RELU
+    old, _RELU = _RELU, bool(flag)
+    return old
+
+
 def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None, fork_input=False):
+    relu = relu and _RELU
     y, x_fwd, part = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1],
                                     use_bias=False, fork_input=fork_input, emit_stats=EPILOGUE_BN_STATS) \
         if (fork_input or EPILOGUE_BN_STATS) else \

@@ -26,19 +26,28 @@ def _torchrun(world, script, *args, timeout=900, extra=()):
           [os.path.join(HERE, script)] + [str(a) for a in args]
     env = dict(os.environ)
     env.pop("DTF_KILL_RANK_AT_STEP", None)
-    return subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout, env=env)
+    p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout, env=env)
+    # keep the ranks' own output (torchrun's failure summary hides it at the end of stdout)
+    out_dir = os.path.join(os.path.dirname(HERE), "gpurun_out")
+    if os.path.isdir(out_dir):
+        tag = "_".join([os.path.splitext(script)[0].strip("_"), str(world)] + [os.path.basename(str(a)) for a in args])
+        with open(os.path.join(out_dir, "mr_%s.log" % tag), "a") as f:
+            f.write(p.stdout + "\n==== rc %d\n" % p.returncode)
+    p.worker_tail = "\n".join(l for l in p.stdout.splitlines() if not l.startswith(("E  ", "Traceback", "  File "))
+                              and "torch/distributed" not in l)[-4000:]
+    return p
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_collectives_and_data_parallel_trainer(world):
     p = _torchrun(world, "_comm_worker.py")
-    assert p.returncode == 0 and "COMM_WORKER_OK" in p.stdout, p.stdout[-4000:]
+    assert p.returncode == 0 and "COMM_WORKER_OK" in p.stdout, p.worker_tail
 
 
 @pytest.mark.parametrize("world", [2, 4])
 def test_owner_sharded_fp32_backup_async_graph_and_timeouts(world):
     p = _torchrun(world, "_comm_worker2.py")
-    assert p.returncode == 0 and "COMM_WORKER2_OK" in p.stdout, p.stdout[-5000:]
+    assert p.returncode == 0 and "COMM_WORKER2_OK" in p.stdout, p.worker_tail
 
 
 @pytest.mark.parametrize("sync", ["sync", "backup", "async"])
@@ -47,11 +56,11 @@ def test_train_operator_save_resume_eval_multi_rank(tmp_path, sync):
     md = str(tmp_path / sync)
     os.makedirs(md)
     p = _torchrun(world, "_train_worker.py", md, sync, 2)
-    assert p.returncode == 0 and "TRAIN_WORKER_OK 20" in p.stdout, p.stdout[-5000:]
-    assert "Saving checkpoints for 5 " in p.stdout or "Saving checkpoints for 5" in p.stdout, p.stdout[-3000:]
+    assert p.returncode == 0 and "TRAIN_WORKER_OK 20" in p.stdout, p.worker_tail
+    assert "Saving checkpoints for 5 " in p.stdout or "Saving checkpoints for 5" in p.stdout, p.worker_tail
     # resume: a second launch restores step 20 on every rank and continues to 30
     p = _torchrun(world, "_train_worker.py", md, sync, 3)
-    assert p.returncode == 0 and "TRAIN_WORKER_OK 30" in p.stdout, p.stdout[-5000:]
+    assert p.returncode == 0 and "TRAIN_WORKER_OK 30" in p.stdout, p.worker_tail
     assert "Restoring parameters from" in p.stdout
 
 
@@ -62,5 +71,5 @@ def test_kill_one_rank_and_resume_from_checkpoint(tmp_path):
     md = str(tmp_path / "kill")
     os.makedirs(md)
     p = _torchrun(2, "_train_worker.py", md, "sync", 2, "kill", extra=("--max-restarts", "1"), timeout=900)
-    assert p.returncode == 0 and "TRAIN_WORKER_OK 20 restart=1" in p.stdout, p.stdout[-6000:]
+    assert p.returncode == 0 and "TRAIN_WORKER_OK 20 restart=1" in p.stdout, p.worker_tail
     assert "Restoring parameters from" in p.stdout and "model.ckpt-10" in p.stdout
