@@ -44,7 +44,8 @@ constexpr int DONE_CTR_OFF = APPLIED_OFF + MAX_RANKS;
 constexpr int HEARTBEAT_OFF = DONE_CTR_OFF + 8;
 //   [TICKET_OFF]                              arrival ticket counter of this owner (peers atom.add.sys into it)
 //   [ARRIVE_OFF, +MAX_RANKS)                  arrive[src_rank] = ticket + 1 of that rank's latest arrival (peers)
-//   [BK_CALL_OFF, +MAX_COMM_BLOCKS)           local per-block call counter of backup-worker collectives
+//   [BK_CALL_OFF]                             local call counter of backup-worker collectives (+1 by the last block)
+//   [BK_CALL_OFF + 1]                         blocks of the running backup-worker collective that have finished
 //   [PUSH_VER_OFF]                            local async push version (bumped in-kernel: survives graph replay)
 //   [OWNER_STEP_OFF, +MAX_RANKS)              owner_step[o]: number of updates owner o has applied (written by o)
 //   [BASE_STEP_OFF, +MAX_RANKS)               local snapshot of owner_step[] taken when this step's forward began
@@ -268,7 +269,21 @@ struct PushF32 {
 // is among the first R, drops the rest (their gradient is stale by TF's rule) and the caller scales by 1/R. Each
 // owner decides for itself, exactly like TF's per-variable accumulators. Tickets of call k are k*N .. k*N+N-1: no
 // rank can arrive for call k+1 before every rank has arrived for call k (the exit barrier of call k needs them all).
-// Returns the bit mask of aggregated ranks, or 0 after a time-out.
+// The call index k is one counter per rank, read by every block when the kernel starts and advanced by the block
+// that finishes last (backup_finish): kernels of one communicator are stream-ordered, so every block of call k reads
+// k whatever the grid sizes of the calls were. Returns the bit mask of aggregated ranks, or 0 after a time-out.
+__device__ void backup_finish(const CommCtx& c) {
+  uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(flags + BK_CALL_OFF + 1, 1u) == gridDim.x - 1) {
+      flags[BK_CALL_OFF + 1] = 0;
+      __threadfence();
+      atomicAdd(flags + BK_CALL_OFF, 1u);
+    }
+  }
+}
 __device__ uint32_t backup_arrive_and_select(const CommCtx& c, int R) {
   uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
   __shared__ uint32_t mask_s;
@@ -276,9 +291,7 @@ __device__ uint32_t backup_arrive_and_select(const CommCtx& c, int R) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence_system();
-    const uint32_t k = flags[BK_CALL_OFF + blockIdx.x];
-    flags[BK_CALL_OFF + blockIdx.x] = k + 1;
-    call_s = k;
+    call_s = *reinterpret_cast<volatile uint32_t*>(flags + BK_CALL_OFF);
     mask_s = 0;
   }
   __syncthreads();
@@ -325,9 +338,13 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, const
                    float* master, float* m, float* v, size_t shadow_off, PushF32 f32, NoPush np, int backup_r) {
   optim_load_hyper(o, hyper);
   uint32_t mask = 0xffffffffu;
-  if (backup_r > 0 && backup_r < c.world) {
+  const bool backup = backup_r > 0 && backup_r < c.world;
+  if (backup) {
     mask = backup_arrive_and_select(c, backup_r);
-    if (mask == 0u) return;
+    if (mask == 0u) {
+      backup_finish(c);
+      return;
+    }
   } else if (!block_barrier(c)) {
     return;
   }
@@ -357,6 +374,7 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, const
     }
   }
   block_barrier(c);  // all shards have landed everywhere; gradients may be overwritten
+  if (backup) backup_finish(c);
 }
 
 // ---- K-RS-OPT over NVLS: the owner reduces its slice with ONE multimem.ld_reduce per 16 bytes (the NVSwitch pulls the

@@ -99,7 +99,18 @@ class Server(object):
             return dist.group.WORLD
         backend = backend or ("nccl" if torch.cuda.is_available() else "gloo")
         if "TORCHELASTIC_RUN_ID" in os.environ or self.store is None:
-            dist.init_process_group(backend=backend)
+            restart = os.environ.get("TORCHELASTIC_RESTART_COUNT", "0")
+            if restart != "0" and "MASTER_ADDR" in os.environ and "MASTER_PORT" in os.environ:
+                # a group restarted by the launcher after a lost worker: rendezvous under a fresh key prefix, otherwise
+                # a rank may read the previous attempt's (dead) NCCL bootstrap address from the launcher's store
+                from torch.distributed import PrefixStore, TCPStore
+                base = TCPStore(os.environ["MASTER_ADDR"], int(os.environ["MASTER_PORT"]), world_size=None,
+                                is_master=False, timeout=datetime.timedelta(seconds=self.timeout_s))
+                dist.init_process_group(backend=backend, store=PrefixStore("dtf_attempt_%s" % restart, base),
+                                        rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]),
+                                        timeout=datetime.timedelta(seconds=self.timeout_s))
+            else:
+                dist.init_process_group(backend=backend)
         else:
             from torch.distributed import PrefixStore
             dist.init_process_group(backend=backend, store=PrefixStore("pg", self.store), rank=self.task_index,

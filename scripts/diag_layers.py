@@ -11,9 +11,16 @@ name = sys.argv[1] if len(sys.argv) > 1 else "ResNet18"
 batch = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 size = int(sys.argv[3]) if len(sys.argv) > 3 else 64
 torch.manual_seed(4)
-cls = getattr(models, name)
-class Small(cls):
-    num_classes = 16
+if name.startswith("Shallow"):
+    class Small(resnet_mod._ResNet):
+        num_classes = 16
+        blocks = (1, 2)
+        bottleneck = name.endswith("B")
+else:
+    cls = getattr(models, name)
+    class Small(cls):
+        num_classes = 16
+resnet_mod.set_relu(os.environ.get("RELU", "1") == "1")
 x = torch.rand(batch, size, size, 3).to(torch.bfloat16).float()
 y = torch.randint(0, 16, (batch,))
 mk = lambda d: dtf.Trainer(dtf.Net(Small()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.0), device=d)
@@ -48,7 +55,7 @@ for fn in ("conv_nonacti", "batch_norm_channel", "pool", "global_avg_pool", "fc_
 
 rec = []
 layers.emulate_bf16(True)
-lc, _ = cpu._forward_backward([(x, y)])
+lc, tgc = cpu._forward_backward([(x, y)])
 layers.emulate_bf16(False)
 rc = rec
 rec = []
@@ -65,3 +72,12 @@ def rel(a, b):
     return float((a - b).norm() / (a.norm() + 1e-20))
 for (t1, a1, g1), (t2, a2, g2) in zip(rc, rg):
     print("%-60s act %.5f  grad %.5f" % (t1, rel(a1, a2), rel(g1, g2)))
+
+print("---- per variable")
+cg = {v.name: g for g, v in tgc[0]}
+for v in gpu.store.trainable_variables():
+    gc = cg[v.name].float(); gg = v.logical(v.grad.detach()).float().cpu()
+    if float(gc.norm()) < 1e-9:
+        continue
+    print("%-44s rel %.4f  ratio %.4f  cos %.5f" % (v.name, float((gg - gc).norm() / gc.norm()), float(gg.norm() / gc.norm()),
+          float(torch.dot(gg.flatten(), gc.flatten()) / (gg.norm() * gc.norm() + 1e-20))))

@@ -135,7 +135,15 @@ def _oracle_step(model_cls, batch, size, classes=16):
         gg = v.logical(v.grad.detach()).float().cpu()
         if float(gc.norm()) < 1e-6:
             continue
-        rel = float((gg - gc).norm() / gc.norm())
+        denom = float(gc.norm())
+        if v.name.endswith("/beta") and v.name[:-4] + "gamma" in cg:
+            # the gradient of a batch-norm shift that feeds another batch norm is (nearly) zero by construction -- a
+            # sum of thousands of cancelling terms; measure its error on the scale of the layer's gamma gradient
+            denom = max(denom, float(cg[v.name[:-4] + "gamma"].float().norm()))
+        rel = float((gg - gc).norm() / denom)
+        if denom > float(gc.norm()) * 4:
+            out.append((rel, 1.0, v.name))
+            continue
         cos = float(torch.dot(gg.flatten(), gc.flatten()) / (gg.norm() * gc.norm() + 1e-20))
         out.append((rel, cos, v.name))
     out.sort(reverse=True)
