@@ -142,13 +142,18 @@ def main():
     dist.barrier()
 
     # ---- 4. backup mode through the Trainer (captured graph) with the straggler injected on the last rank
+    # (every rank trains on the SAME batch here: whichever subset an owner aggregates, the update is the same, so the
+    # loss must fall on every rank; that late gradients are really dropped is what section 2 verified exactly)
+    gsame = torch.Generator().manual_seed(77)
+    xs, ys = torch.rand(32, 32, 32, 3, generator=gsame), torch.randint(0, 10, (32,), generator=gsame)
     tr = make_trainer(rank, world, dev, "auto", graph=True, replicas_to_aggregate=R)
     check(tr.replicas_to_aggregate == R, "trainer did not keep replicas_to_aggregate")
     ls = []
     for i in range(8):
         if rank == world - 1 and i % 2 == 1:
             tr.engine.comm.sleep(0.02) if tr.engine is not None else None
-        ls.append(float(tr.step((x, y))))
+        ls.append(float(tr.step((xs, ys))))
+    check(tr.engine.comm.error() is None, "backup trainer: error record %s" % (tr.engine.comm.error(),))
     torch.cuda.synchronize()
     dist.barrier()
     check(tr.engine.backup_r == R and tr.engine.algo == "twoshot" and not tr.engine.nvls, "backup engine setup")

@@ -101,7 +101,7 @@ def test_prefetched_steps_equal_plain_steps():
     assert b._copy_stream is not None
 
 
-def _oracle_step(model_cls, batch, size, classes=16):
+def _oracle_step(model_cls, batch, size, classes=16, damp=None):
     """One forward/backward with IDENTICAL bf16-representable weights on the CUDA kernels and on the CPU oracle (fp32
     arithmetic, activations / data gradients rounded where the kernels store bf16). Returns the two losses and
     [(relative L2 error, cosine, name)] per trainable variable."""
@@ -113,6 +113,13 @@ def _oracle_step(model_cls, batch, size, classes=16):
     gpu = _trainer(model_cls, "cuda:0", dtf.GradientDescentOptimizer(0.0))
     cpu.build(x, y)
     gpu.build(x, y)
+    if damp is not None:  # scale of the last batch norm of every residual branch (see the full-depth test)
+        with torch.no_grad():
+            names = set(cpu.store.vars)
+            for v in cpu.store.trainable_variables():
+                last = "conv3/bn/gamma" if v.name.replace("conv2/bn/gamma", "conv3/bn/gamma") in names else "conv2/bn/gamma"
+                if v.name.startswith("stage") and v.name.endswith(last):
+                    v.master.fill_(damp)
     gpu.store.load_state_dict(cpu.store.state_dict())
     gpu.store.shadow_arena.copy_(gpu.store.master_arena)
     gpu.store.refresh_transposed_shadows()
@@ -185,10 +192,12 @@ def test_residual_stack_gradients_match_cpu_oracle_per_variable(bottleneck, relu
 
 @pytest.mark.parametrize("name", ["ResNet18", "ResNet50"])
 def test_full_depth_resnet_gradients_against_cpu_oracle(name):
-    """Full-depth nets: two CORRECT bf16 implementations already disagree on ~2 % of the ReLU decisions after 20-50
-    roundings (measured: activations drift to 2.5 % by the last stage, which alone moves the first layers' gradients
-    by 25-30 %, cosine 0.95), so the bound here only catches gross faults: every variable's gradient must point the
-    same way (cosine > 0.9) with the right magnitude (+-15 %)."""
+    """Full-depth nets. A randomly initialised batch-norm ResNet amplifies any perturbation by ~1.2x per layer (the
+    known gradient explosion of BN networks at initialisation): measured here, two correct bf16 implementations that
+    agree to 3e-5 after the stem disagree by 35 % in the last stage of ResNet-50, and their gradients are unrelated
+    (cosine 0.3). The comparison is therefore made at the usual "zero-init residual" operating point: the last batch
+    norm of every residual branch gets gamma = 0.2, which makes the blocks near-identity and the network
+    well-conditioned, while every kernel still runs on full-size non-trivial data."""
     from distributed_tensorflow_framework_b200 import models
     torch.manual_seed(4)
     cls = getattr(models, name)
@@ -196,8 +205,9 @@ def test_full_depth_resnet_gradients_against_cpu_oracle(name):
     class Small(cls):
         num_classes = 16
 
-    lc, lg, errs = _oracle_step(Small, 8, 64)
+    lc, lg, errs = _oracle_step(Small, 8, 64, damp=0.2)
     print("%s: loss %.5f / %.5f, worst %s" % (name, lc, lg, [(round(r, 4), round(c, 4), n) for r, c, n in errs[:4]]))
-    assert abs(lc - lg) < 5e-2 * max(1.0, abs(lc)), (lc, lg)
+    assert abs(lc - lg) < 1e-2 * max(1.0, abs(lc)), (lc, lg)
     for rel, cos, vname in errs:
         assert cos > 0.9 and rel < 0.45, (vname, rel, cos)
+    assert sorted(r for r, _, _ in errs)[len(errs) // 2] < 0.25
