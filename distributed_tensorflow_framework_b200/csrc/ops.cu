@@ -352,6 +352,8 @@ __global__ void upsample_zero_kernel(const __nv_bfloat16* __restrict__ dy, __nv_
 //   MODE 2: acc0 += x ; acc1 += x*x                      (BN statistics)
 //   MODE 3: dz = relu? dy*(y>0) : dy -> store (if dz);   (BN backward reduce)
 //           acc0 += dz ; acc1 += dz * (x-mean)*rstd
+//           relu == 3: in1 is the forward's ReLU BITMASK (one byte per 8-channel chunk, [R][N/8]) instead of y --
+//           1/16 of the bytes of the y read it replaces
 template <int MODE>
 __global__ void __launch_bounds__(256)
 colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __restrict__ in1,
@@ -391,6 +393,7 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
     constexpr int U = kBnBwd ? 4 : 8;  // rows in flight per thread (memory-level parallelism)
     for (long long rb = r0 + row_lane; rb < r1; rb += (long long)rpp * U) {
       BF8 b0[U], b1[U], b2[U];
+      uint32_t mb[U];
       bool ok[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
@@ -400,6 +403,7 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
           const long long off = r * N + (long long)col_chunk * 8;
           b0[u] = ld8(in0 + off);
           if (MODE == 1 || (MODE == 3 && relu == 1)) b1[u] = ld8(in1 + off);
+          if (MODE == 3 && relu == 3) mb[u] = reinterpret_cast<const uint8_t*>(in1)[r * cpr + col_chunk];
           if (kBnBwd) b2[u] = ld8(in2 + off);
         }
       }
@@ -420,6 +424,10 @@ colreduce_kernel(const __nv_bfloat16* __restrict__ in0, const __nv_bfloat16* __r
           unpack8(b2[u], xm);
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] = fmaf(xm[j], ksc[j], ksh[j]) > 0.f ? g[j] : 0.f;
+        }
+        if (MODE == 3 && relu == 3) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = ((mb[u] >> j) & 1u) ? g[j] : 0.f;
         }
         if ((MODE == 1 || MODE == 3) && out != nullptr) st8(out + off, pack8(g));
         if (MODE == 2) {
@@ -595,7 +603,7 @@ __global__ void bn_fold_kernel(const float* __restrict__ run_mean, const float* 
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
                 __nv_bfloat16* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
-                long long R, int N, int relu, int rows_per_block) {
+                long long R, int N, int relu, int rows_per_block, uint8_t* __restrict__ mask) {
   const int cpr = N / 8;
   const int cg0 = blockIdx.x * 256;
   const int cprg = min(256, cpr - cg0);
@@ -639,6 +647,12 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
         for (int j = 0; j < 8; ++j) f[j] += q[j];
       }
       if (relu) {
+        if (mask != nullptr) {  // bit j = (pre-activation of channel j > 0): all the backward needs of y
+          uint32_t m = 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
+          mask[r * cpr + col_chunk] = (uint8_t)m;
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
       }
@@ -1416,18 +1430,26 @@ extern "C" int dtf_bn_fold(const float* run_mean, const float* run_var, const fl
   bn_fold_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(run_mean, run_var, gamma, beta, scale, shift, N, eps);
   return DTF_CHECK_LAUNCH();
 }
+extern "C" int dtf_bn_apply_mask(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
+                                 const float* shift, long long R, int N, int relu, void* stream);
 extern "C" int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift,
                             long long R, int N, int relu, void* stream) {
+  return dtf_bn_apply_mask(x, res, y, nullptr, scale, shift, R, N, relu, stream);
+}
+extern "C" int dtf_bn_apply_mask(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
+                                 const float* shift, long long R, int N, int relu, void* stream) {
   if (N % 8) return DTF_ERR_ALIGN;
   int gx, gy, rpb;
   elementwise_geometry(R, N, &gx, &gy, &rpb);
   bn_apply_kernel<<<dim3(gx, gy), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)res,
-                                                        (__nv_bfloat16*)y, scale, shift, R, N, relu, rpb);
+                                                        (__nv_bfloat16*)y, scale, shift, R, N, relu, rpb,
+                                                        (uint8_t*)relu_mask);
   return DTF_CHECK_LAUNCH();
 }
 // part[blocks][2][N] = per-row-block {sum dz, sum dz*xhat}; dz (optional output) = relu ? dy*(y>0) : dy
 // relu: 0 none; 1 mask from y (y > 0); 2 mask recomputed from x with the forward's folded scale / shift
-// (mask_scale / mask_shift, no y read, dz may be NULL and is then never materialised).
+// (mask_scale / mask_shift, no y read, dz may be NULL and is then never materialised); 3: `y` points to the ReLU
+// bitmask written by dtf_bn_apply_mask ([R][N/8] bytes).
 extern "C" int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* part,
                                  const float* mean, const float* rstd, const float* mask_scale,
                                  const float* mask_shift, long long R, int N, int relu, void* stream) {

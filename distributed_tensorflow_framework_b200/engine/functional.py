@@ -279,13 +279,18 @@ class BatchNormFn(torch.autograd.Function):
         beta = bvar.master if bvar is not None else None
         if part is not None and tuple(part.shape[1:]) != (2, x2.shape[1]):
             part = None
-        y2, mean, rstd, scale, shift = raw.bn_train_fwd(x2, gamma, beta, run_mean, run_var, eps, momentum, res2, relu,
-                                                        part=part)
-        ctx.gvar, ctx.bvar, ctx.relu, ctx.rows, ctx.has_res = gvar, bvar, relu, rows, res is not None
-        # without a residual the ReLU mask is a function of x alone: keep the folded coefficients instead of y
+        # without a residual the ReLU mask is a function of x alone: keep the folded coefficients instead of y;
+        # with one, the forward writes the decisions as a bitmask (1 bit per element) and the backward reads that
         ctx.mask_from_x = relu and res is None
+        want_mask = relu and res is not None and x2.shape[1] % 8 == 0
+        out = raw.bn_train_fwd(x2, gamma, beta, run_mean, run_var, eps, momentum, res2, relu, part=part,
+                               want_mask=want_mask)
+        y2, mean, rstd, scale, shift = out[:5]
+        ctx.gvar, ctx.bvar, ctx.relu, ctx.rows, ctx.has_res = gvar, bvar, relu, rows, res is not None
         if ctx.mask_from_x:
             ctx.save_for_backward(x2, None, mean, rstd, scale, shift)
+        elif want_mask:
+            ctx.save_for_backward(x2, out[5], mean, rstd, None, None)
         else:
             ctx.save_for_backward(x2, y2 if relu else None, mean, rstd, None, None)
         return y2.view(shape)

@@ -420,7 +420,8 @@ def _part(R, N, device):
     return torch.empty(nblk, 2, N, device=device, dtype=torch.float32)
 
 
-def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, res=None, relu=False, part=None):
+def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, res=None, relu=False, part=None,
+                 want_mask=False):
     """Training-mode batch norm over rows of x2d [R, N]. Returns (y, mean, rstd, scale, shift). `part` [rows, 2, N]:
     per-tile sums / sums of squares of x2d already produced by the kernel that wrote it (no statistics pass then)."""
     R, N = x2d.shape
@@ -437,6 +438,11 @@ def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, re
         _lib.call("dtf_bn_finalize", part, gamma, beta, mean, rstd, scale, shift, run_mean, run_var, N, R, eps,
                   momentum, _sp())
     y = torch.empty_like(x2d)
+    if want_mask and relu:
+        # the ReLU decisions as one bit per element: what the backward needs of y when a residual went into it
+        mask = torch.empty((R, N // 8), device=dev, dtype=torch.uint8)
+        _lib.call("dtf_bn_apply_mask", x2d, res, y, mask, scale, shift, R, N, 1, _sp())
+        return y, mean, rstd, scale, shift, mask
     _lib.call("dtf_bn_apply", x2d, res, y, scale, shift, R, N, 1 if relu else 0, _sp())
     return y, mean, rstd, scale, shift
 
@@ -465,8 +471,11 @@ def bn_bwd(dy2d, y2d, x2d, mean, rstd, gamma, relu=False, dgamma_acc=None, dbeta
     part = _part(R, N, dev)
     from_x = relu and mask_scale is not None
     mode = 2 if from_x else (1 if relu else 0)
+    if mode == 1 and y2d is not None and y2d.dtype == torch.uint8:
+        mode = 3  # y2d is the forward's ReLU bitmask [R, N/8]
     dz = None if from_x else (torch.empty_like(dy2d) if relu else dy2d)
-    _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if mode == 1 else None, x2d, dz if mode == 1 else None, part, mean, rstd,
+    _lib.call("dtf_bn_bwd_reduce", dy2d, y2d if mode in (1, 3) else None, x2d, dz if mode in (1, 3) else None, part,
+              mean, rstd,
               mask_scale if from_x else None, mask_shift if from_x else None, R, N, mode, _sp())
     dx = torch.empty_like(x2d)
     coef = torch.empty(3, N, device=dev, dtype=torch.float32)

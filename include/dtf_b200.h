@@ -129,7 +129,12 @@ int dtf_bn_fold(const float* run_mean, const float* run_var, const float* gamma,
                 float* shift, int N, float eps, void* stream);
 int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift, long long R, int N,
                  int relu, void* stream);
-/* relu: 0 none, 1 mask from y, 2 mask recomputed from x with the forward's folded scale/shift (no y read, no dz). */
+/* Same, and with relu also writes the ReLU decisions as a bitmask relu_mask[R][N/8] (bit j of a byte = channel 8k+j
+ * is positive): the backward of a batch norm with a residual input reads 1 bit per element instead of y. */
+int dtf_bn_apply_mask(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
+                      const float* shift, long long R, int N, int relu, void* stream);
+/* relu: 0 none, 1 mask from y, 2 mask recomputed from x with the forward's folded scale/shift (no y read, no dz),
+ * 3 `y` is the bitmask of dtf_bn_apply_mask. */
 int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* part, const float* mean,
                       const float* rstd, const float* mask_scale, const float* mask_shift, long long R, int N,
                       int relu, void* stream);

@@ -117,6 +117,14 @@ def test_batch_norm(raw, R, N, relu, with_res):
     close(dbeta, b2.grad, 2e-2)
     if with_res:
         close(dz, resf.grad)
+    if relu and with_res:  # the forward's ReLU bitmask (1 bit per element) replaces y in the backward
+        out = raw.bn_train_fwd(x, gamma, beta, rm.clone(), rv.clone(), 1e-3, 0.1, res, relu, want_mask=True)
+        assert torch.equal(out[0], y) and out[5].dtype == torch.uint8 and tuple(out[5].shape) == (R, N // 8)
+        bits = ((out[5].long().unsqueeze(-1) >> torch.arange(8, device="cuda")) & 1).reshape(R, N).bool()
+        assert torch.equal(bits, y > 0)
+        dx3, dz3, dg3, db3 = raw.bn_bwd(dy, out[5], x, mean, rstd, gamma, relu)
+        assert torch.equal(dz3, dz) and torch.equal(dx3, dx)
+        close(dg3, g2.grad, 2e-2)
     if relu and not with_res:  # mask recomputed from x: same result without reading y / writing dz
         dx2, dz2, dg2, db2 = raw.bn_bwd(dy, None, x, mean, rstd, gamma, relu, mask_scale=scale, mask_shift=shift)
         assert dz2 is None
