@@ -52,6 +52,9 @@ struct IgemmParams {
   // optional bf16 [M, N] (row stride ldc) added to the result before the ReLU: residual inputs, and the second
   // gradient of a tensor with two consumers (so autograd never has to sum them in a separate pass)
   const __nv_bfloat16* addend;
+  // optional batch-norm statistics of the (bf16-rounded) output: per-warp partial rows [grid * 4][2][N] of column
+  // sums and sums of squares, accumulated in shared memory across the tiles of a persistent CTA
+  float* stats;
 };
 
 template <int BN, int STAGES>
@@ -149,9 +152,9 @@ __device__ __forceinline__ void igemm_epilogue(const IgemmParams& p, uint32_t tm
 // (16-byte chunks XOR-swizzled by the row) so that every global store instruction writes complete 32-byte sectors of
 // few rows (COLS = 64: four full 128-byte lines per instruction; COLS = 32: eight 64-byte row segments) instead of
 // 32 scattered 16-byte pieces. `stage` is this warp's private 32 * COLS * 2 bytes.
-template <int BN, int COLS>
+template <int BN, int COLS, bool STATS = false>
 __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint32_t tmem_base, int tile_m,
-                                                      int tile_n, int warp, uint8_t* stage) {
+                                                      int tile_n, int warp, uint8_t* stage, float* acc = nullptr) {
   constexpr int ROWB = COLS * 2;        // bytes per staged row
   constexpr int CPR = ROWB / 16;        // 16-byte chunks per row (8 or 4)
   constexpr int RPI = 32 / CPR;         // rows written per store instruction
@@ -206,12 +209,28 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
       }
     }
     __syncwarp();
+    float cs[8], cq[8];  // STATS: this lane's column sums / sums of squares over its NIT rows of the group
+    if (STATS) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) cs[j] = cq[j] = 0.f;
+    }
 #pragma unroll
     for (int i = 0; i < NIT; ++i) {
       const int r = i * RPI + lane / CPR;
       uint4 q = *reinterpret_cast<const uint4*>(stage + r * ROWB + ((chunk ^ (r & (CPR - 1))) << 4));
       const int m = row0 + r;
       if (m < p.M && n + 8 <= p.N) {
+        if (STATS) {  // statistics of exactly the values that are stored (bf16-rounded)
+          const __nv_bfloat162* qs = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 x = __bfloat1622float2(qs[e]);
+            cs[2 * e] += x.x;
+            cs[2 * e + 1] += x.y;
+            cq[2 * e] = fmaf(x.x, x.x, cq[2 * e]);
+            cq[2 * e + 1] = fmaf(x.y, x.y, cq[2 * e + 1]);
+          }
+        }
         if (has_add) {  // add in fp32, ReLU, round once more
           const __nv_bfloat162* qa = reinterpret_cast<const __nv_bfloat162*>(&q);
           const __nv_bfloat162* aa = reinterpret_cast<const __nv_bfloat162*>(&av[i]);
@@ -229,6 +248,30 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
           q = make_uint4(o[0], o[1], o[2], o[3]);
         }
         *reinterpret_cast<uint4*>(outp + (size_t)m * p.ldc + n) = q;
+      }
+    }
+    if (STATS) {
+      // lanes chunk, chunk + CPR, ... hold the same 8 columns: fold them, then the first CPR lanes add the group's
+      // sums to this warp's private accumulators (fixed order: bitwise reproducible)
+#pragma unroll
+      for (int off = CPR; off < 32; off <<= 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], off);
+          cq[j] += __shfl_xor_sync(0xffffffffu, cq[j], off);
+        }
+      }
+      if (lane < CPR && n + 8 <= p.N) {
+        float4* a0 = reinterpret_cast<float4*>(acc + n);
+        float4* a1 = reinterpret_cast<float4*>(acc + p.N + n);
+        float4 t = a0[0];
+        a0[0] = make_float4(t.x + cs[0], t.y + cs[1], t.z + cs[2], t.w + cs[3]);
+        t = a0[1];
+        a0[1] = make_float4(t.x + cs[4], t.y + cs[5], t.z + cs[6], t.w + cs[7]);
+        t = a1[0];
+        a1[0] = make_float4(t.x + cq[0], t.y + cq[1], t.z + cq[2], t.w + cq[3]);
+        t = a1[1];
+        a1[1] = make_float4(t.x + cq[4], t.y + cq[5], t.z + cq[6], t.w + cq[7]);
       }
     }
     __syncwarp();
@@ -578,6 +621,7 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   constexpr int kStageCols = (BN >= 256) ? 64 : 32;  // wide tiles run one CTA per SM and can afford 4 KB per warp
   uint8_t* stage_base = smem + L::BAR_OFFSET + 256;  // 4 warps x (32 rows x kStageCols x 2 B) epilogue staging
+  float* stats_acc = reinterpret_cast<float*>(stage_base + 4 * 32 * kStageCols * 2);  // [4 warps][2][N] (p.stats)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr bool kAMn = (AMODE == A_TMA_MN);
   // bf16 output with 16-byte aligned rows and whole 8-column groups: use the coalescing epilogue
@@ -681,6 +725,12 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
       if ((buf ^= 1) == 0) acc_par ^= 1;
     }
   } else {
+    const bool want_stats = staged && p.stats != nullptr;
+    float* my_acc = stats_acc + warp * 2 * p.N;
+    if (want_stats) {
+      for (int i = lane; i < 2 * p.N; i += 32) my_acc[i] = 0.f;
+      __syncwarp();
+    }
     int lt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
       int tile_m, tile_n, kb0, kb1;
@@ -697,13 +747,21 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
       }
       mbar_wait(&acc_full[buf], (lt >> 1) & 1);
       tc_fence_after();
-      if (staged)
+      if (want_stats)
+        igemm_epilogue_staged<BN, kStageCols, true>(p, tmem_base + buf * BN, tile_m, tile_n, warp,
+                                                    stage_base + warp * (32 * kStageCols * 2), my_acc);
+      else if (staged)
         igemm_epilogue_staged<BN, kStageCols>(p, tmem_base + buf * BN, tile_m, tile_n, warp,
                                               stage_base + warp * (32 * kStageCols * 2));
       else igemm_epilogue<BN>(p, tmem_base + buf * BN, tile_m, tile_n, warp);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
+    }
+    if (want_stats) {  // one partial row per (CTA, epilogue warp); bn_finalize adds the rows in a fixed order
+      __syncwarp();
+      float* o = p.stats + ((size_t)blockIdx.x * 4 + warp) * 2 * p.N;
+      for (int i = lane; i < 2 * p.N; i += 32) o[i] = my_acc[i];
     }
   }
   tc_fence_before();
@@ -714,25 +772,41 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
   }
 }
 
+constexpr int kMaxSmemOptin = 227 * 1024;
+// Shared memory and grid of the persistent kernel for a problem (the statistics accumulators are 32 N bytes).
+template <int BN, int STAGES>
+static void persistent_plan(int M, int N, int splits, bool with_stats, int* smem_out, int* grid_out) {
+  using L = SmemLayout<BN, STAGES>;
+  constexpr int kStage = 4 * 32 * ((BN >= 256) ? 64 : 32) * 2;  // epilogue staging: 16 KB (wide tiles) or 8 KB
+  const int smem = L::TOTAL + kStage + (with_stats ? 4 * 2 * N * 4 : 0);
+  const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + BLOCK_M - 1) / BLOCK_M;
+  const int total = tiles_n * tiles_m * splits;
+  const int per_sm = (smem <= 112 * 1024) ? 2 : 1;
+  *smem_out = smem;
+  *grid_out = total < 148 * per_sm ? total : 148 * per_sm;
+}
+
 template <int BN, int STAGES, int AMODE>
 static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
                              cudaStream_t stream) {
   using L = SmemLayout<BN, STAGES>;
-  constexpr int kStage = 4 * 32 * ((BN >= 256) ? 64 : 32) * 2;  // epilogue staging: 16 KB (wide tiles) or 8 KB
+  constexpr int kStage = 4 * 32 * ((BN >= 256) ? 64 : 32) * 2;
   static bool attr_set[64] = {};
   auto kern = igemm_persistent_kernel<BN, STAGES, AMODE>;
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL + kStage) != cudaSuccess)
+    const int want = L::TOTAL + kStage + 4 * 2 * 2048 * 4;  // room for the statistics accumulators of N <= 2048
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             want < kMaxSmemOptin ? want : kMaxSmemOptin) != cudaSuccess)
       return DTF_ERR_CUDA;
     attr_set[dev & 63] = true;
   }
+  int smem, grid;
+  persistent_plan<BN, STAGES>(p.M, p.N, splits, p.stats != nullptr, &smem, &grid);
+  if (smem > kMaxSmemOptin) return DTF_ERR_TOO_LARGE;
   const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M;
-  const int total = tiles_n * tiles_m * splits;
-  const int per_sm = (L::TOTAL + kStage <= 112 * 1024) ? 2 : 1;
-  const int grid = total < 148 * per_sm ? total : 148 * per_sm;
-  kern<<<grid, NUM_THREADS, L::TOTAL + kStage, stream>>>(ta, tb, p, tiles_m, tiles_n, splits);
+  kern<<<grid, NUM_THREADS, smem, stream>>>(ta, tb, p, tiles_m, tiles_n, splits);
   return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
@@ -885,23 +959,40 @@ extern "C" int dtf_gemm_bf16(const void* A, const void* B, void* C, const float*
                              int ldb, int ldc, int flags, void* stream_) {
   return dtf_gemm_bf16_ex(A, B, C, bias, nullptr, nullptr, M, N, K, lda, ldb, ldc, flags, stream_);
 }
-// Rows of the batch-norm statistics buffer the GEMM epilogue would fill for this problem. Always 0 in this build:
-// column statistics in the dense GEMM epilogue were implemented and measured (per-CTA register accumulation over the
-// staged tiles) and cost as much as the separate statistics pass they replace, because the bandwidth-bound 1x1
-// layers have their epilogue warps on the critical path. Callers fall back to dtf_bn_stats.
+// Which persistent instantiation dispatch_bn picks for a dense problem (mirrors it): 64, 128 or 256.
+static int persistent_bn(int M, int N, int splits) {
+  if (N <= 64) return 64;
+  const long long tiles256 = (long long)((M + BLOCK_M - 1) / BLOCK_M) * ((N + 255) / 256) * splits;
+  return (g_wide_tiles && N >= 256 && tiles256 >= 148) ? 256 : 128;
+}
+// Rows of the batch-norm statistics buffer [rows][2][N] that dtf_gemm_bf16_ex fills for this problem when given a
+// `stats` pointer, or 0 when the epilogue cannot produce them (then run dtf_bn_stats on the output). The persistent
+// kernel keeps per-warp column sums / sums of squares of the stored bf16 values in shared memory across its tiles and
+// writes one partial row per (CTA, epilogue warp): 4 x grid rows for dtf_bn_finalize_rows.
 extern "C" int dtf_gemm_stats_rows(const void* A, const void* B, const void* C, int M, int N, int K, int lda, int ldb,
                                    int ldc) {
-  (void)A; (void)B; (void)C; (void)M; (void)N; (void)K; (void)lda; (void)ldb; (void)ldc;
-  return 0;
+  (void)K;
+  if (!g_use_persistent || M <= 0 || N <= 0 || N > 2048 || (N % 8) || (ldc % 8)) return 0;
+  if (!aligned16(A) || !aligned16(B) || !aligned16(C) || (lda % 8) || (ldb % 8) || (M * (long long)N < 4096)) return 0;
+  int smem = 0, grid = 0;
+  switch (persistent_bn(M, N, 1)) {
+    case 64: persistent_plan<64, 4>(M, N, 1, true, &smem, &grid); break;
+    case 128: persistent_plan<128, 3>(M, N, 1, true, &smem, &grid); break;
+    default: persistent_plan<256, 3>(M, N, 1, true, &smem, &grid); break;
+  }
+  return smem <= kMaxSmemOptin ? grid * 4 : 0;
 }
 // Same with `addend` (bf16 [M, N], row stride ldc, may be NULL): C = act(A*B + bias + addend); bf16 outputs only.
-// `stats` must be NULL (see dtf_gemm_stats_rows).
+// `stats`: NULL, or a buffer of dtf_gemm_stats_rows(...) x 2 x N floats that receives per-warp partial column sums and
+// sums of squares of the output (plain bf16 outputs without addend / ReLU / split-K only).
 extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const float* bias, const void* addend,
                                 float* stats, int M, int N, int K, int lda, int ldb, int ldc, int flags, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   const int relu = flags & 1, out_fp32 = (flags >> 1) & 1, atomic = (flags >> 2) & 1, a_t = (flags >> 3) & 1;
   if (M <= 0 || N <= 0 || K <= 0) return DTF_ERR_ARG;
-  if (stats != nullptr) return DTF_ERR_UNSUPPORTED;
+  if (stats != nullptr && (relu || out_fp32 || atomic || a_t || addend != nullptr ||
+                           dtf_gemm_stats_rows(A, B, C, M, N, K, lda, ldb, ldc) == 0))
+    return DTF_ERR_UNSUPPORTED;
   if (addend != nullptr && (out_fp32 || atomic)) return DTF_ERR_UNSUPPORTED;
   const bool tc_ok = aligned16(A) && aligned16(B) && (lda % 8 == 0) && (ldb % 8 == 0) && (M * (long long)N >= 4096);
   if (!tc_ok) {
@@ -923,6 +1014,7 @@ extern "C" int dtf_gemm_bf16_ex(const void* A, const void* B, void* C, const flo
   p.M = M; p.N = N; p.K = K;
   p.out = C; p.ldc = ldc; p.bias = bias; p.relu = relu; p.out_fp32 = out_fp32; p.atomic = atomic;
   p.addend = reinterpret_cast<const __nv_bfloat16*>(addend);
+  p.stats = stats;
   const int total_kb = (K + BLOCK_K - 1) / BLOCK_K;
   const int splits = pick_splits(M, N, total_kb, atomic);
   p.kb_per_split = (total_kb + splits - 1) / splits;

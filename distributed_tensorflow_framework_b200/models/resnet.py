@@ -7,11 +7,13 @@ from ..plugins.input import SyntheticDataLoader
 from ..plugins.model import Model
 
 
-# Batch-norm statistics can be produced by the convolution epilogues (conv_nonacti(emit_stats=True)) instead of a
-# separate pass over the output. Measured on ResNet-50 b256 it does not pay: the 1x1 layers are bandwidth bound with
-# the epilogue warps on the critical path, and the extra column reduction there costs what the saved pass gained
-# (25.8 ms/step with, 25.3 without), so it is off by default.
-EPILOGUE_BN_STATS = False
+# Batch-norm statistics can be produced by the epilogue of the kernel that writes the tensor instead of a separate
+# pass over it. 1 (default): the 1x1 convolutions (dense persistent GEMM: per-warp column sums kept in shared memory
+# across the CTA's tiles, accumulated while the staged tile is written out). 2: also the KxK halo convolutions, whose
+# epilogue statistics were measured NOT to pay on ResNet-50 (25.8 ms/step with, 25.3 without). 0: never.
+import os as _os
+
+EPILOGUE_BN_STATS = int(_os.environ.get("DTF_EPILOGUE_STATS", "1"))
 
 
 _RELU = True
@@ -27,11 +29,13 @@ def set_relu(flag):
 
 def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None, fork_input=False):
     relu = relu and _RELU
-    y, x_fwd, part = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1],
-                                    use_bias=False, fork_input=fork_input, emit_stats=EPILOGUE_BN_STATS) \
-        if (fork_input or EPILOGUE_BN_STATS) else \
-        (L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1], use_bias=False), None,
-         None)
+    emit = EPILOGUE_BN_STATS >= 2 or (EPILOGUE_BN_STATS == 1 and k == 1)
+    if fork_input or emit:
+        y, x_fwd, part = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1],
+                                        use_bias=False, fork_input=fork_input, emit_stats=emit)
+    else:
+        y, x_fwd, part = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1],
+                                        use_bias=False), None, None
     out = L.batch_norm_channel(name + "/bn", y, relu=relu, residual=residual, stats_part=part)
     return (out, x_fwd) if fork_input else out  # x_fwd: x forwarded for the shortcut branch
 

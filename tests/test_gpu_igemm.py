@@ -181,6 +181,43 @@ def test_conv_epilogue_statistics(raw, n, H, C, Co, k, s):
     assert torch.allclose(tot[1], (yf * yf).sum(0), rtol=2e-2, atol=0.5)
 
 
+@pytest.mark.parametrize("M,N,K", [(802816 // 8, 256, 64), (50176, 1024, 256), (12544, 2048, 512), (3136, 64, 256),
+                                   (1000, 128, 64), (200704 // 4, 512, 128)])
+def test_gemm_epilogue_statistics(raw, M, N, K):
+    """Batch-norm statistics from the dense GEMM epilogue (1x1 convolutions): the per-warp partial rows add up to the
+    column sums / sums of squares of the stored bf16 output, the output itself is unchanged, and the 1x1 convolution
+    entry point (plain and strided) hands them to batch norm."""
+    a = rnd(M, K)
+    b = (torch.randn(K, N, device="cuda") * 0.1).to(torch.bfloat16)
+    st = {}
+    y = raw.gemm(a, b, stats=st)
+    assert "part" in st and st["part"].shape[1:] == (2, N) and st["part"].shape[0] % 4 == 0
+    assert torch.equal(y, raw.gemm(a, b))
+    tot = st["part"].double().sum(0)
+    yf = y.double()
+    assert torch.allclose(tot[0], yf.sum(0), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(tot[1], (yf * yf).sum(0), rtol=1e-4, atol=1e-2)
+    st2 = {}
+    raw.gemm(a, b, relu=True, stats=st2)  # a fused ReLU changes what is stored: no statistics offered
+    assert "part" not in st2
+
+
+def test_conv1x1_statistics_feed_batch_norm(raw):
+    x = rnd(8, 28, 28, 128)
+    w = (torch.randn(1, 1, 128, 256, device="cuda") * 0.05).to(torch.bfloat16).reshape(128, 256)
+    for stride in (1, 2):
+        st = {}
+        y = raw.conv_fprop(x, w, None, 1, 1, stride, stats=st)
+        assert "part" in st
+        y2 = y.reshape(-1, 256)
+        gamma, beta = torch.rand(256, device="cuda") + 0.5, torch.randn(256, device="cuda")
+        o1 = raw.bn_train_fwd(y2, gamma, beta, None, None, 1e-3, 0.1, part=st["part"])
+        o2 = raw.bn_train_fwd(y2, gamma, beta, None, None, 1e-3, 0.1)
+        close(o1[1], o2[1], 1e-3)  # mean
+        close(o1[2], o2[2], 1e-3)  # rstd
+        close(o1[0], o2[0], 1e-2)
+
+
 def test_gather_conv_with_more_than_65535_row_tiles(raw):
     """8.5 M output pixels = 66 k row tiles: tiles are linearised in grid.x (grid.y would overflow)."""
     n, H, W, C, Co = 170, 224, 224, 8, 8
