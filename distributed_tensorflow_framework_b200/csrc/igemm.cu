@@ -73,14 +73,16 @@ struct PixelCoord {
 
 // Fused epilogue of one 128 x BN accumulator tile: TMEM -> registers -> (bias, ReLU) -> bf16 / fp32 store or
 // split-K red.add. Called by the four epilogue warps (warp index == TMEM lane quarter).
+// `warp` = TMEM lane quarter of the calling warp (warp index % 4); with two warps per quarter (persistent kernel, wide
+// tiles) each takes every second 32-column group (cc0 / cstep).
 template <int BN>
 __device__ __forceinline__ void igemm_epilogue(const IgemmParams& p, uint32_t tmem_base, int tile_m, int tile_n,
-                                               int warp) {
-  const int r = threadIdx.x;  // accumulator row == TMEM lane
+                                               int warp, int cc0 = 0, int cstep = 1) {
+  const int r = warp * 32 + (threadIdx.x & 31);  // accumulator row == TMEM lane
   const int m = tile_m * BLOCK_M + r;
   const uint32_t lane_addr = tmem_base + ((uint32_t)(warp * 32) << 16);
 #pragma unroll 1
-  for (int cc = 0; cc < BN / 32; ++cc) {
+  for (int cc = cc0; cc < BN / 32; cc += cstep) {
     uint32_t v[32];
     tmem_ld32(lane_addr + cc * 32, v);
     tmem_ld_wait();
@@ -154,7 +156,8 @@ __device__ __forceinline__ void igemm_epilogue(const IgemmParams& p, uint32_t tm
 // 32 scattered 16-byte pieces. `stage` is this warp's private 32 * COLS * 2 bytes.
 template <int BN, int COLS, bool STATS = false>
 __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint32_t tmem_base, int tile_m,
-                                                      int tile_n, int warp, uint8_t* stage, float* acc = nullptr) {
+                                                      int tile_n, int warp, uint8_t* stage, float* acc = nullptr,
+                                                      int cg0 = 0, int cgstep = 1) {
   constexpr int ROWB = COLS * 2;        // bytes per staged row
   constexpr int CPR = ROWB / 16;        // 16-byte chunks per row (8 or 4)
   constexpr int RPI = 32 / CPR;         // rows written per store instruction
@@ -166,7 +169,7 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
   const int chunk = lane & (CPR - 1);
   const bool has_add = p.addend != nullptr;
 #pragma unroll 1
-  for (int cg = 0; cg < BN / COLS; ++cg) {
+  for (int cg = cg0; cg < BN / COLS; cg += cgstep) {
     const int n0 = tile_n * BN + cg * COLS;
     const int n = n0 + chunk * 8;
     // the addend pieces of this group are requested first, all at once, so their latency overlaps the TMEM load
@@ -280,8 +283,8 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
 
 // Pull the addend rows of a tile towards L2 ahead of the epilogue that will read them (one 128-byte line per call).
 template <int BN>
-__device__ __forceinline__ void prefetch_addend_tile(const IgemmParams& p, int tile_m, int tile_n) {
-  const int m = tile_m * BLOCK_M + threadIdx.x;  // epilogue threads 0..127 = tile rows
+__device__ __forceinline__ void prefetch_addend_tile(const IgemmParams& p, int tile_m, int tile_n, int tile_row) {
+  const int m = tile_m * BLOCK_M + tile_row;  // one epilogue thread per tile row
   if (m >= p.M) return;
   const char* row = reinterpret_cast<const char*>(p.addend + (size_t)m * p.ldc + (size_t)tile_n * BN);
   const int bytes = min(BN, p.N - tile_n * BN) * 2;
@@ -606,8 +609,20 @@ __device__ __forceinline__ void igemm_body(const CUtensorMap& tma_a, const CUten
 // The TMA producer keeps the smem ring full ACROSS tiles, the accumulator is double buffered in TMEM (2 x BN
 // columns), so the epilogue of tile i (tcgen05.ld + stores) overlaps the loads and MMAs of tile i+1, and the
 // per-tile costs of the one-shot kernel (launch, TMEM alloc, barrier init, exposed first-load latency) are paid once.
+// Wide tiles (BN = 256) run one CTA per SM; four epilogue warps then cannot keep up with the bandwidth-bound 1x1 layers
+// (each warp walks ~1500 dependent instructions per tile: measured, every instruction added to the epilogue showed up
+// 1:1 in the kernel time). Those instances therefore get EIGHT epilogue warps -- warps 6..9 join warps 0..3, two warps
+// per TMEM lane quarter, each taking every second column group.
+template <int BN>
+struct PersistCfg {
+  static constexpr int EW = (BN >= 256) ? 8 : 4;
+  static constexpr int THREADS = NUM_THREADS + (EW - 4) * 32;
+  static constexpr int STAGE_COLS = (BN >= 256) ? 64 : 32;
+  static constexpr int STAGING_BYTES = EW * 32 * STAGE_COLS * 2;
+};
+
 template <int BN, int STAGES, int AMODE>
-__global__ void __launch_bounds__(NUM_THREADS)
+__global__ void __launch_bounds__(PersistCfg<BN>::THREADS)
 igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                         const IgemmParams p, int tiles_m, int tiles_n, int splits) {
   static_assert(AMODE == A_TMA_K || AMODE == A_TMA_MN, "persistent kernel is for the TMA-fed modes");
@@ -619,9 +634,10 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
   uint64_t* acc_full = empty_bar + STAGES;   // [2]
   uint64_t* acc_empty = acc_full + 2;        // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  constexpr int kStageCols = (BN >= 256) ? 64 : 32;  // wide tiles run one CTA per SM and can afford 4 KB per warp
-  uint8_t* stage_base = smem + L::BAR_OFFSET + 256;  // 4 warps x (32 rows x kStageCols x 2 B) epilogue staging
-  float* stats_acc = reinterpret_cast<float*>(stage_base + 4 * 32 * kStageCols * 2);  // [4 warps][2][N] (p.stats)
+  constexpr int kStageCols = PersistCfg<BN>::STAGE_COLS;  // wide tiles run one CTA per SM: 4 KB per warp
+  constexpr int EW = PersistCfg<BN>::EW;
+  uint8_t* stage_base = smem + L::BAR_OFFSET + 256;  // EW warps x (32 rows x kStageCols x 2 B) epilogue staging
+  float* stats_acc = reinterpret_cast<float*>(stage_base + PersistCfg<BN>::STAGING_BYTES);  // [4 quarters][2][N]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr bool kAMn = (AMODE == A_TMA_MN);
   // bf16 output with 16-byte aligned rows and whole 8-column groups: use the coalescing epilogue
@@ -638,7 +654,7 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&acc_full[b], 1);
-      mbar_init(&acc_empty[b], 4);  // one arrival per epilogue warp
+      mbar_init(&acc_empty[b], EW);  // one arrival per epilogue warp
     }
     mbar_fence_init();
   }
@@ -725,43 +741,49 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
       if ((buf ^= 1) == 0) acc_par ^= 1;
     }
   } else {
+    const int q = warp & 3;                // TMEM lane quarter this warp may read
+    const int half = (warp < 4) ? 0 : 1;   // which column groups of a tile (second epilogue warp set: warps 6..9)
+    constexpr int kSplit = EW / 4;
+    uint8_t* my_stage = stage_base + (half * 4 + q) * (32 * kStageCols * 2);
     const bool want_stats = staged && p.stats != nullptr;
-    float* my_acc = stats_acc + warp * 2 * p.N;
+    float* my_acc = stats_acc + q * 2 * p.N;  // shared by the two warps of a quarter (disjoint columns)
     if (want_stats) {
-      for (int i = lane; i < 2 * p.N; i += 32) my_acc[i] = 0.f;
-      __syncwarp();
+      for (int i = (half * 4 + q) * 32 + lane; i < 4 * 2 * p.N; i += EW * 32) stats_acc[i] = 0.f;
+      asm volatile("bar.sync 1, %0;\n" ::"r"(EW * 32) : "memory");
     }
     int lt = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++lt) {
       int tile_m, tile_n, kb0, kb1;
       decode(t, tile_m, tile_n, kb0, kb1);
       const int buf = lt & 1;
-      if (p.addend != nullptr) {  // this tile's rows (first tile only) and the next tile's, one tile period ahead
-        if (lt == 0) prefetch_addend_tile<BN>(p, tile_m, tile_n);
+      if (p.addend != nullptr && half == 0) {  // this tile's rows (first tile only) and the next tile's, a tile ahead
+        if (lt == 0) prefetch_addend_tile<BN>(p, tile_m, tile_n, q * 32 + lane);
         const int tn = t + gridDim.x;
         if (tn < total_tiles) {
           int m2, n2, k0, k1;
           decode(tn, m2, n2, k0, k1);
-          prefetch_addend_tile<BN>(p, m2, n2);
+          prefetch_addend_tile<BN>(p, m2, n2, q * 32 + lane);
         }
       }
       mbar_wait(&acc_full[buf], (lt >> 1) & 1);
       tc_fence_after();
       if (want_stats)
-        igemm_epilogue_staged<BN, kStageCols, true>(p, tmem_base + buf * BN, tile_m, tile_n, warp,
-                                                    stage_base + warp * (32 * kStageCols * 2), my_acc);
+        igemm_epilogue_staged<BN, kStageCols, true>(p, tmem_base + buf * BN, tile_m, tile_n, q, my_stage, my_acc, half,
+                                                    kSplit);
       else if (staged)
-        igemm_epilogue_staged<BN, kStageCols>(p, tmem_base + buf * BN, tile_m, tile_n, warp,
-                                              stage_base + warp * (32 * kStageCols * 2));
-      else igemm_epilogue<BN>(p, tmem_base + buf * BN, tile_m, tile_n, warp);
+        igemm_epilogue_staged<BN, kStageCols>(p, tmem_base + buf * BN, tile_m, tile_n, q, my_stage, nullptr, half,
+                                              kSplit);
+      else igemm_epilogue<BN>(p, tmem_base + buf * BN, tile_m, tile_n, q, half, kSplit);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
-    if (want_stats) {  // one partial row per (CTA, epilogue warp); bn_finalize adds the rows in a fixed order
-      __syncwarp();
-      float* o = p.stats + ((size_t)blockIdx.x * 4 + warp) * 2 * p.N;
-      for (int i = lane; i < 2 * p.N; i += 32) o[i] = my_acc[i];
+    if (want_stats) {  // one partial row per (CTA, lane quarter); bn_finalize adds the rows in a fixed order
+      asm volatile("bar.sync 1, %0;\n" ::"r"(EW * 32) : "memory");
+      if (half == 0) {
+        float* o = p.stats + ((size_t)blockIdx.x * 4 + q) * 2 * p.N;
+        for (int i = lane; i < 2 * p.N; i += 32) o[i] = my_acc[i];
+      }
     }
   }
   tc_fence_before();
@@ -777,7 +799,7 @@ constexpr int kMaxSmemOptin = 227 * 1024;
 template <int BN, int STAGES>
 static void persistent_plan(int M, int N, int splits, bool with_stats, int* smem_out, int* grid_out) {
   using L = SmemLayout<BN, STAGES>;
-  constexpr int kStage = 4 * 32 * ((BN >= 256) ? 64 : 32) * 2;  // epilogue staging: 16 KB (wide tiles) or 8 KB
+  constexpr int kStage = PersistCfg<BN>::STAGING_BYTES;  // epilogue staging: 32 KB (wide tiles) or 8 KB
   const int smem = L::TOTAL + kStage + (with_stats ? 4 * 2 * N * 4 : 0);
   const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + BLOCK_M - 1) / BLOCK_M;
   const int total = tiles_n * tiles_m * splits;
@@ -790,7 +812,7 @@ template <int BN, int STAGES, int AMODE>
 static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& p, int splits,
                              cudaStream_t stream) {
   using L = SmemLayout<BN, STAGES>;
-  constexpr int kStage = 4 * 32 * ((BN >= 256) ? 64 : 32) * 2;
+  constexpr int kStage = PersistCfg<BN>::STAGING_BYTES;
   static bool attr_set[64] = {};
   auto kern = igemm_persistent_kernel<BN, STAGES, AMODE>;
   int dev = 0;
@@ -806,7 +828,7 @@ static int launch_persistent(const CUtensorMap& ta, const CUtensorMap& tb, const
   persistent_plan<BN, STAGES>(p.M, p.N, splits, p.stats != nullptr, &smem, &grid);
   if (smem > kMaxSmemOptin) return DTF_ERR_TOO_LARGE;
   const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + BLOCK_M - 1) / BLOCK_M;
-  kern<<<grid, NUM_THREADS, smem, stream>>>(ta, tb, p, tiles_m, tiles_n, splits);
+  kern<<<grid, PersistCfg<BN>::THREADS, smem, stream>>>(ta, tb, p, tiles_m, tiles_n, splits);
   return cudaGetLastError() == cudaSuccess ? DTF_OK : DTF_ERR_CUDA;
 }
 
