@@ -662,8 +662,10 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
     }
   } else {
     // epilogue warp w owns channels [32w, 32w+32) of the item: TMEM lane = channel, column = padded-linear pixel
-    uint8_t* stage = stage_base + warp * (32 * 64);
-    int* tab = tab_base + warp * PN_PIX;
+    // staging tile and pixel table are addressed by 32-bit shared addresses (explicit st.shared / ld.shared: the
+    // pointers lose their address space in the carve-up arithmetic and would compile to generic LD.E / ST.E)
+    const uint32_t stage = smem_u32(stage_base) + warp * (32 * 64);
+    const uint32_t tab = smem_u32(tab_base) + warp * PN_PIX * 4;
     const uint32_t lane_addr = ((uint32_t)(warp * 32) << 16);
     const int m_limit = (pp.G - 1) * pp.img_rows + p.R * p.Wp;  // columns beyond carry no output pixel
     int buf = 0;
@@ -684,7 +686,7 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
           const int xx = rem - ry * p.Wp;
           const int x = x0 + xx, y = y0 + ry, im = img + g;
           const bool valid = (g < pp.G) && (im < p.n_img) && (ry < p.R) && (xx < p.Wt) && (x < p.W) && (y < p.H);
-          tab[m] = valid ? (int)(((long long)im * p.H + y) * p.W + x) : -1;
+          st_shared_b32(tab + m * 4, valid ? (uint32_t)(int)(((long long)im * p.H + y) * p.W + x) : 0xffffffffu);
           if (STATS) vmask[STATS ? q : 0] = __ballot_sync(0xffffffffu, valid);
         }
         __syncwarp();
@@ -700,7 +702,7 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
           uint32_t v[32];
           tmem_ld32(tmem_base + buf * PN_PIX + lane_addr + cc * 32, v);
           tmem_ld_wait();
-          __nv_bfloat16* st = reinterpret_cast<__nv_bfloat16*>(stage) + lane;
+          const uint32_t st = stage + lane * 2;
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             float f = __uint_as_float(v[j]) + bias;
@@ -709,7 +711,7 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
               st_sq = fmaf(f, f, st_sq);
             }
             if (p.relu) f = fmaxf(f, 0.f);
-            st[j * 32] = __float2bfloat16(f);  // stage[pixel j][channel lane]
+            st_shared_b16(st + j * 64, __bfloat16_as_ushort(__float2bfloat16(f)));  // stage[pixel j][channel lane]
           }
           __syncwarp();
           const int c8 = (lane & 3) * 8;
@@ -717,8 +719,8 @@ conv_halo_pn_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_cons
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const int r = i * 8 + (lane >> 2);
-            const int pr = tab[cc * 32 + r];
-            const uint4 q = *reinterpret_cast<const uint4*>(stage + r * 64 + c8 * 2);
+            const int pr = (int)ld_shared_b32(tab + (cc * 32 + r) * 4);
+            const uint4 q = ld_shared_v4(stage + r * 64 + c8 * 2);
             if (pr >= 0 && n + 8 <= p.n_out)
               *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)pr * p.n_out + n) = q;
           }

@@ -156,8 +156,9 @@ __device__ __forceinline__ void igemm_epilogue(const IgemmParams& p, uint32_t tm
 // 32 scattered 16-byte pieces. `stage` is this warp's private 32 * COLS * 2 bytes.
 template <int BN, int COLS, bool STATS = false>
 __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint32_t tmem_base, int tile_m,
-                                                      int tile_n, int warp, uint8_t* stage, float* acc = nullptr,
+                                                      int tile_n, int warp, uint32_t stage, uint32_t acc = 0,
                                                       int cg0 = 0, int cgstep = 1) {
+  // `stage` / `acc`: 32-bit shared-memory addresses (explicit st.shared / ld.shared, see ptx.cuh)
   constexpr int ROWB = COLS * 2;        // bytes per staged row
   constexpr int CPR = ROWB / 16;        // 16-byte chunks per row (8 or 4)
   constexpr int RPI = 32 / CPR;         // rows written per store instruction
@@ -208,7 +209,7 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
         q.z = pack_bf16x2(f[c * 8 + 4], f[c * 8 + 5]);
         q.w = pack_bf16x2(f[c * 8 + 6], f[c * 8 + 7]);
         const int ch = h * 4 + c;
-        *reinterpret_cast<uint4*>(stage + lane * ROWB + ((ch ^ (lane & (CPR - 1))) << 4)) = q;
+        st_shared_v4(stage + lane * ROWB + ((ch ^ (lane & (CPR - 1))) << 4), q);
       }
     }
     __syncwarp();
@@ -220,7 +221,7 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
 #pragma unroll
     for (int i = 0; i < NIT; ++i) {
       const int r = i * RPI + lane / CPR;
-      uint4 q = *reinterpret_cast<const uint4*>(stage + r * ROWB + ((chunk ^ (r & (CPR - 1))) << 4));
+      uint4 q = ld_shared_v4(stage + r * ROWB + ((chunk ^ (r & (CPR - 1))) << 4));
       const int m = row0 + r;
       if (m < p.M && n + 8 <= p.N) {
         if (STATS) {  // statistics of exactly the values that are stored (bf16-rounded)
@@ -265,16 +266,15 @@ __device__ __forceinline__ void igemm_epilogue_staged(const IgemmParams& p, uint
         }
       }
       if (lane < CPR && n + 8 <= p.N) {
-        float4* a0 = reinterpret_cast<float4*>(acc + n);
-        float4* a1 = reinterpret_cast<float4*>(acc + p.N + n);
-        float4 t = a0[0];
-        a0[0] = make_float4(t.x + cs[0], t.y + cs[1], t.z + cs[2], t.w + cs[3]);
-        t = a0[1];
-        a0[1] = make_float4(t.x + cs[4], t.y + cs[5], t.z + cs[6], t.w + cs[7]);
-        t = a1[0];
-        a1[0] = make_float4(t.x + cq[0], t.y + cq[1], t.z + cq[2], t.w + cq[3]);
-        t = a1[1];
-        a1[1] = make_float4(t.x + cq[4], t.y + cq[5], t.z + cq[6], t.w + cq[7]);
+        const uint32_t a0 = acc + (uint32_t)n * 4u, a1 = acc + (uint32_t)(p.N + n) * 4u;
+        float4 t = ld_shared_f4(a0);
+        st_shared_f4(a0, make_float4(t.x + cs[0], t.y + cs[1], t.z + cs[2], t.w + cs[3]));
+        t = ld_shared_f4(a0 + 16);
+        st_shared_f4(a0 + 16, make_float4(t.x + cs[4], t.y + cs[5], t.z + cs[6], t.w + cs[7]));
+        t = ld_shared_f4(a1);
+        st_shared_f4(a1, make_float4(t.x + cq[0], t.y + cq[1], t.z + cq[2], t.w + cq[3]));
+        t = ld_shared_f4(a1 + 16);
+        st_shared_f4(a1 + 16, make_float4(t.x + cq[4], t.y + cq[5], t.z + cq[6], t.w + cq[7]));
       }
     }
     __syncwarp();
@@ -744,11 +744,12 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
     const int q = warp & 3;                // TMEM lane quarter this warp may read
     const int half = (warp < 4) ? 0 : 1;   // which column groups of a tile (second epilogue warp set: warps 6..9)
     constexpr int kSplit = EW / 4;
-    uint8_t* my_stage = stage_base + (half * 4 + q) * (32 * kStageCols * 2);
+    const uint32_t my_stage = smem_u32(stage_base) + (half * 4 + q) * (32 * kStageCols * 2);
     const bool want_stats = staged && p.stats != nullptr;
-    float* my_acc = stats_acc + q * 2 * p.N;  // shared by the two warps of a quarter (disjoint columns)
+    const uint32_t acc_u32 = smem_u32(stats_acc);
+    const uint32_t my_acc = acc_u32 + (uint32_t)(q * 2 * p.N) * 4u;  // shared by the two warps of a quarter
     if (want_stats) {
-      for (int i = (half * 4 + q) * 32 + lane; i < 4 * 2 * p.N; i += EW * 32) stats_acc[i] = 0.f;
+      for (int i = (half * 4 + q) * 32 + lane; i < 4 * 2 * p.N; i += EW * 32) st_shared_f32(acc_u32 + i * 4, 0.f);
       asm volatile("bar.sync 1, %0;\n" ::"r"(EW * 32) : "memory");
     }
     int lt = 0;
@@ -771,7 +772,7 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
         igemm_epilogue_staged<BN, kStageCols, true>(p, tmem_base + buf * BN, tile_m, tile_n, q, my_stage, my_acc, half,
                                                     kSplit);
       else if (staged)
-        igemm_epilogue_staged<BN, kStageCols>(p, tmem_base + buf * BN, tile_m, tile_n, q, my_stage, nullptr, half,
+        igemm_epilogue_staged<BN, kStageCols>(p, tmem_base + buf * BN, tile_m, tile_n, q, my_stage, 0u, half,
                                               kSplit);
       else igemm_epilogue<BN>(p, tmem_base + buf * BN, tile_m, tile_n, q, half, kSplit);
       tc_fence_before();
@@ -782,7 +783,7 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
       asm volatile("bar.sync 1, %0;\n" ::"r"(EW * 32) : "memory");
       if (half == 0) {
         float* o = p.stats + ((size_t)blockIdx.x * 4 + q) * 2 * p.N;
-        for (int i = lane; i < 2 * p.N; i += 32) o[i] = my_acc[i];
+        for (int i = lane; i < 2 * p.N; i += 32) o[i] = ld_shared_f32(my_acc + i * 4);
       }
     }
   }
