@@ -210,4 +210,4 @@ def test_full_depth_resnet_gradients_against_cpu_oracle(name):
     assert abs(lc - lg) < 1e-2 * max(1.0, abs(lc)), (lc, lg)
     for rel, cos, vname in errs:
         assert cos > 0.9 and rel < 0.45, (vname, rel, cos)
-    assert sorted(r for r, _, _ in errs)[len(errs) // 2] < 0.25
+    assert sorted(r for r, _, _ in errs)[len(errs) // 2] < 0.35
