@@ -1,7 +1,17 @@
 """B-NCCL-AR stand-in baseline: the same model / config in stock PyTorch -- cuDNN convolutions and
-cuBLAS GEMMs under bf16 autocast, channels_last, ncclAllReduce of the flat gradient, torch.optim.SGD(momentum). This
-is NOT the reference (which is TF1-only and cannot run here); it is the "library path" the hand-written kernels are
-compared against. None of this repo's kernels are used on this path."""
+cuBLAS GEMMs, channels_last, NCCL gradient all-reduce, torch.optim.SGD(momentum). This is NOT the reference (which is
+TF1-only and cannot run here); it is the "library path" the hand-written kernels are compared against. None of this
+repo's kernels are used on this path.
+
+Modes (DTF_BASELINE_MODE or --baseline-mode):
+  eager    round-1 stand-in: bf16 autocast over fp32 parameters, eager launches, flat ncclAllReduce after backward.
+  graph    (default) the strongest plain-library configuration: parameters and activations in bf16 channels_last (no
+           autocast casts, no fp32 master copy -- less work than this repo's fp32-master path does), the whole step
+           (forward, backward, fused SGD) captured in ONE CUDA graph at N = 1; at N > 1 DistributedDataParallel
+           (bucketed NCCL all-reduce overlapped with backward), eager.
+  compile  as graph, with the model compiled by torch.compile (inductor fuses batch norm / ReLU / residual adds into
+           Triton kernels; mode="max-autotune-no-cudagraphs" + our own graph capture at N = 1)."""
+import os
 import json
 import time
 
@@ -104,25 +114,40 @@ def run(args, cfg, dist_setup, max_over_ranks, make_batch, ClockSampler):
     rank, world, local, group = dist_setup(args.gpus)
     device = torch.device("cuda", local)
     torch.backends.cudnn.benchmark = True
+    mode = getattr(args, "baseline_mode", None) or os.environ.get("DTF_BASELINE_MODE", "graph")
+    pure_bf16 = mode in ("graph", "compile")
     model = build(cfg["model"]).to(device).to(memory_format=torch.channels_last)
+    if pure_bf16:
+        model = model.to(torch.bfloat16)
     params = [p for p in model.parameters()]
-    opt = torch.optim.SGD(params, lr=0.01, momentum=0.9)
+    try:
+        opt = torch.optim.SGD(params, lr=0.01, momentum=0.9, fused=pure_bf16)
+    except (TypeError, RuntimeError):
+        opt = torch.optim.SGD(params, lr=0.01, momentum=0.9)
     batch = args.batch or cfg["batch"]
     pool = [make_batch(cfg, batch, 100 + rank * 10 + i) for i in range(2)]
+    fwd = model
+    if world > 1 and pure_bf16:
+        from torch.nn.parallel import DistributedDataParallel as DDP
+        fwd = DDP(model, device_ids=[local], gradient_as_bucket_view=True, bucket_cap_mb=25)
+    if mode == "compile":
+        fwd = torch.compile(fwd, mode="max-autotune-no-cudagraphs")
+    act_dtype = torch.bfloat16 if pure_bf16 else torch.float32
 
-    def step(xh, yh):
-        x = xh.to(device, non_blocking=True).permute(0, 3, 1, 2).float().div_(255.).contiguous(
-            memory_format=torch.channels_last)
-        y = yh.to(device, non_blocking=True)
-        with torch.autocast("cuda", dtype=torch.bfloat16):
-            out = model(x)
-            if cfg["classes"]:
-                loss = F.cross_entropy(out.float(), y)
-            else:
-                loss = F.mse_loss(out.float(), y.permute(0, 3, 1, 2))
+    def compute(x_u8, y):
+        x = x_u8.permute(0, 3, 1, 2).to(act_dtype).div_(255.).contiguous(memory_format=torch.channels_last)
+        if pure_bf16:
+            out = fwd(x)
+        else:
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out = fwd(x)
+        if cfg["classes"]:
+            loss = F.cross_entropy(out.float(), y)
+        else:
+            loss = F.mse_loss(out.float(), y.permute(0, 3, 1, 2))
         opt.zero_grad(set_to_none=False)
         loss.backward()
-        if world > 1:
+        if world > 1 and not pure_bf16:
             import torch.distributed as dist
             flat = torch.cat([p.grad.reshape(-1) for p in params])
             dist.all_reduce(flat)
@@ -135,6 +160,32 @@ def run(args, cfg, dist_setup, max_over_ranks, make_batch, ClockSampler):
         opt.step()
         return loss
 
+    graph = {"g": None}
+    static = {}
+
+    def step(xh, yh):
+        if graph["g"] is not None:  # replay: copy the inputs into the captured step's static buffers
+            static["x"].copy_(xh, non_blocking=True)
+            static["y"].copy_(yh, non_blocking=True)
+            graph["g"].replay()
+            return static["loss"]
+        return compute(xh.to(device, non_blocking=True), yh.to(device, non_blocking=True))
+
+    def capture():
+        x0, y0 = pool[0]
+        static["x"], static["y"] = x0.to(device), y0.to(device)
+        s = torch.cuda.Stream(device=device)
+        s.wait_stream(torch.cuda.current_stream(device))
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                compute(static["x"], static["y"])
+        torch.cuda.current_stream(device).wait_stream(s)
+        torch.cuda.synchronize(device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            static["loss"] = compute(static["x"], static["y"])
+        graph["g"] = g
+
     def barrier():
         torch.cuda.synchronize(device)
         if world > 1:
@@ -144,6 +195,16 @@ def run(args, cfg, dist_setup, max_over_ranks, make_batch, ClockSampler):
     dev_pool = [(x.to(device), y.to(device)) for x, y in pool]
     for i in range(max(args.warmup, 3)):
         step(*dev_pool[i % 2])
+    graphed = False
+    if pure_bf16 and world == 1:
+        try:
+            capture()
+            graphed = True
+            for i in range(2):
+                step(*dev_pool[i % 2])
+        except Exception as e:  # capture is an optimisation of the stand-in, never a reason to lose the number
+            graph["g"] = None
+            print("baseline: CUDA graph capture failed (%s); running eagerly" % str(e)[:200], flush=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)
     sampler = ClockSampler(local)
     if rank == 0:
@@ -171,8 +232,10 @@ def run(args, cfg, dist_setup, max_over_ranks, make_batch, ClockSampler):
             "metric": "images/sec (device-timed, max over ranks)", "value": gb * args.steps / (dev_ms / 1e3),
             "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16 autocast", "data": "synthetic", "impl": "torch_nccl (cuDNN/cuBLAS + ncclAllReduce stand-in)",
-            "config": {"model": cfg["model"], "global_batch": gb, "parallelism": "dp%d" % world},
+            "dtype": "bf16" if pure_bf16 else "bf16 autocast", "data": "synthetic",
+            "impl": "torch_nccl (cuDNN/cuBLAS + NCCL stand-in, mode %s)" % mode,
+            "config": {"model": cfg["model"], "global_batch": gb, "parallelism": "dp%d" % world, "mode": mode,
+                       "cuda_graph": graphed, "ddp_overlap": bool(world > 1 and pure_bf16)},
             "e2e": {"value": gb * args.steps / e2e_s, "unit": "images/s",
                     "h2d_bytes_per_step": x0.numel() * x0.element_size() + y0.numel() * y0.element_size(),
                     "d2h_bytes_per_step": 4},

@@ -319,6 +319,8 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the config's)")
     ap.add_argument("--algo", default="auto")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--baseline-mode", default=None, choices=[None, "eager", "graph", "compile"],
+                    help="--impl torch_nccl only: see baseline/torch_baseline.py")
     args = ap.parse_args()
     cfg = CONFIGS[args.config]
     if args.impl == "reference":
