@@ -142,6 +142,8 @@ def run_ours(args, cfg):
     algo = args.algo
     if args.config == "resnet18_async" and world > 1 and algo == "auto":
         algo = "async"
+    if algo == "auto_sync":  # the async config's model with the synchronous collective (for comparison)
+        algo = "auto"
     trainer = dtf.Trainer(dtf.Net(getattr(models, cfg["model"])()), loss, opt, device=device, rank=rank, world=world,
                           group=group, algo=algo, use_cuda_graph=not args.no_graph, seed=0)
     pool = [make_batch(cfg, batch, 100 + rank * 10 + i) for i in range(2)]
@@ -214,7 +216,8 @@ def run_ours(args, cfg):
         "impl": "ours",
         "config": {"model": cfg["model"], "desc": cfg["desc"], "global_batch": gb, "per_gpu_batch": batch,
                    "image": list(cfg["shape"]), "parallelism": "dp%d" % world,
-                   "collective": trainer.algo + ("_nvls" if getattr(trainer.engine, "nvls", False) else ""),
+                   "collective": trainer.algo + ("_nvls" if getattr(trainer.engine, "nvls", False) else "") +
+                   ("_pull" if getattr(trainer.engine, "nopush", None) else ""),
                    "optimizer": "momentum", "cuda_graph": bool(trainer._graph is not None),
                    "l2": "256 MiB write between timed steps (outside the event pairs)"},
         "e2e": {"value": gb * args.steps / e2e_s, "unit": "images/s",

@@ -270,14 +270,18 @@ class GradientEngine(object):
                 import os
                 algo = "twoshot_nvls" if os.environ.get("DTF_NVLS", "1") != "0" else "twoshot"
         self.algo = algo
-        self.overlap = overlap and algo in ("oneshot", "nccl", "twoshot", "twoshot_pull", "twoshot_nvls")
+        self.overlap = overlap and algo in ("oneshot", "nccl", "twoshot", "twoshot_pull", "twoshot_nvls",
+                                            "twoshot_nvls_pull")
         self.comm = None
         self.heap = None
+        # "twoshot_nvls_pull": reduce-scatter / push over NVLS multimem, large FC matrices pulled by K-AG-GEMM
+        self.pull = algo in ("twoshot_pull", "twoshot_nvls_pull")
+        if algo == "twoshot_nvls_pull":
+            algo = "twoshot_nvls"
         self.nvls = algo == "twoshot_nvls"
         if self.nvls:
             algo = self.algo = "twoshot"
-        self.pull = algo == "twoshot_pull"
-        if self.pull:
+        if algo == "twoshot_pull":
             algo = self.algo = "twoshot"
         use_heap = algo in ("oneshot", "twoshot", "async")
         if use_heap:
@@ -361,8 +365,12 @@ class GradientEngine(object):
             if not heap.multicast_ptr:
                 ok = 0
         except Exception as e:  # no multicast support, old driver, fabric not configured ...
+            if os.environ.get("DTF_NVLS", "1") == "require":
+                raise  # a misconfigured fabric must not silently halve the collective's speed
             from ..api import log as logger
-            logger.warn("NVLS heap unavailable (%s); using CUDA IPC peer mappings", str(e)[:120])
+            self.nvls_fallback_reason = str(e)[:200]
+            logger.warn("NVLS heap unavailable (%s); using CUDA IPC peer mappings (DTF_NVLS=require makes this an "
+                        "error)", self.nvls_fallback_reason)
             ok = 0
         flag = torch.tensor([ok], device=dev, dtype=torch.int32)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)

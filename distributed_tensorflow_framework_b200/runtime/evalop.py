@@ -29,6 +29,16 @@ class Eval(object):
         pre_result = pre_eval_fn(args, kwargs) if pre_eval_fn is not None else None
         total_loss, n_batches, hits, seen = 0.0, 0, 0, 0
         restored_step = None
+        # launched on several ranks (torchrun): every rank restores the checkpoint and evaluates every world-th batch
+        # of the stream; the sums are combined at the end, so the result is that of one pass over the data
+        rank, world = 0, 1
+        try:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                rank, world = dist.get_rank(), dist.get_world_size()
+        except Exception:  # pragma: no cover
+            pass
+        seq = -1
         layers.set_training(False)
         try:
             with V.using_store(store), torch.no_grad():
@@ -36,6 +46,9 @@ class Eval(object):
                     batch = self.data_loader.load_eval_batch()
                     if batch is None:
                         break
+                    seq += 1
+                    if world > 1 and seq % world != rank and restored_step is not None:
+                        continue
                     raw, gt = batch
                     raw = raw.to(device, non_blocking=True)
                     gt = gt.to(device, non_blocking=True) if isinstance(gt, torch.Tensor) else gt
@@ -46,6 +59,8 @@ class Eval(object):
                         # variables exist after the first forward: now restore them (init_or_restore semantics)
                         restored_step = self._restore(store)
                         logits = self.net.process(raw)
+                    if world > 1 and seq % world != rank:
+                        continue  # (the first batch is run by every rank only to create and restore the variables)
                     if post_process_fn is not None:
                         logits = post_process_fn(logits)
                     if getattr(self, "loss", None) is not None and gt is not None:
@@ -60,6 +75,12 @@ class Eval(object):
                     n_batches += 1
         finally:
             layers.set_training(True)
+        if world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([total_loss, float(n_batches), float(hits), float(seen)], dtype=torch.float64,
+                             device=device if device.type == "cuda" else "cpu")
+            dist.all_reduce(t)
+            total_loss, n_batches, hits, seen = float(t[0]), int(t[1]), int(t[2]), int(t[3])
         results = {"global_step": restored_step or 0, "batches": n_batches,
                    "loss": total_loss / max(n_batches, 1)}
         if seen:

@@ -81,9 +81,13 @@ def main():
                 assert torch.equal(saved, v.logical(v.master.detach()).cpu()), name
                 if sync != "async":  # the bf16 weights every rank computes with are the rounded masters
                     assert torch.equal(saved.to(torch.bfloat16), v.logical(v.shadow.detach()).cpu()), name
-        ev = dtf.run_main(build_main(model_dir, "Eval", epochs, sync))
-        assert ev.results["global_step"] == total and ev.results["loss"] > 0
-        print("TRAIN_WORKER_OK %d restart=%d loss=%.4f" % (step, restart, op.final_loss), flush=True)
+    dist.barrier()
+    # the Eval operator on every rank: each evaluates its share of the batches, the sums are combined
+    ev = dtf.run_main(build_main(model_dir, "Eval", epochs, sync))
+    assert ev.results["global_step"] == total and ev.results["loss"] > 0 and ev.results["batches"] >= world
+    if rank == 0:
+        print("TRAIN_WORKER_OK %d restart=%d loss=%.4f eval_batches=%d" % (step, restart, op.final_loss,
+                                                                          ev.results["batches"]), flush=True)
     dist.barrier()
 
 
