@@ -233,6 +233,12 @@ def run_ours(args, cfg):
         print(json.dumps(res), flush=True)
     if world > 1:
         import torch.distributed as dist
+        dist.barrier()
+        if trainer.algo == "nccl":
+            # NCCL collectives captured in the step's CUDA graph leave ProcessGroupNCCL's watchdog waiting at
+            # teardown (observed: destroy_process_group never returns); the result is out, leave without it
+            sys.stdout.flush()
+            os._exit(0)
         dist.destroy_process_group()
 
 
