@@ -61,11 +61,17 @@ constexpr int BASE_STEP_OFF = OWNER_STEP_OFF + MAX_RANKS;
 constexpr int MAIL_BASE_OFF = BASE_STEP_OFF + MAX_RANKS;
 constexpr int DROPPED_OFF = MAIL_BASE_OFF + MAX_RANKS;
 constexpr int ERR_OFF = DROPPED_OFF + 8;
-constexpr int FLAG_PAGE_BYTES = 8192;
-static_assert((ERR_OFF + 4) * 4 <= FLAG_PAGE_BYTES, "flag page too small");
+//   [KIND_OFF, +MAX_COMM_BLOCKS*MAX_RANKS)    kind[block][src_rank]: which collective the peer entered with the epoch
+//                                             it published in sig[block][src_rank] (protocol check, see block_barrier)
+constexpr int KIND_OFF = ERR_OFF + 8;
+constexpr int FLAG_PAGE_BYTES = 16384;
+static_assert((KIND_OFF + SIG_WORDS) * 4 <= FLAG_PAGE_BYTES, "flag page too small");
 
 constexpr uint32_t ERR_BARRIER_TIMEOUT = 1;  // a peer did not reach the barrier within the time bound
 constexpr uint32_t ERR_ARRIVAL_TIMEOUT = 2;  // fewer than replicas_to_aggregate gradients arrived within the bound
+constexpr uint32_t ERR_KIND_MISMATCH = 3;    // a peer entered a DIFFERENT collective at this barrier epoch
+// collective kinds carried through the barriers
+constexpr uint32_t KIND_AR = 1, KIND_RS = 2, KIND_AG = 3, KIND_BARRIER = 4;
 
 struct CommCtx {
   int rank, world;
@@ -121,7 +127,12 @@ __device__ __forceinline__ bool comm_failed(const CommCtx& c) {
 // Barrier among the same-index blocks of all ranks. Also orders memory: everything written (by this GPU) before the
 // barrier is visible to peers after it. Returns false (for every thread of the block) when a peer did not show up
 // within c.timeout_ns or an earlier wait on this rank already failed; the caller must then return at once.
-__device__ bool block_barrier(const CommCtx& c) {
+// `kind` names the collective that is calling: every rank publishes it next to its epoch, and a rank that finds a
+// peer at the SAME epoch with a different kind records ERR_KIND_MISMATCH -- the ranks did not issue the same sequence
+// of collectives (for example a checkpoint gather launched by the chief alone pairs with the peers' next gradient
+// collective: the failure mode is silent data corruption otherwise). SURVEY 5.2: epoch-stamped barriers that make
+// peer-memory protocol faults detectable.
+__device__ bool block_barrier(const CommCtx& c, uint32_t kind) {
   __syncthreads();
   uint32_t* flags = reinterpret_cast<uint32_t*>(c.peer[c.rank]);
   __shared__ uint32_t epoch_s;
@@ -139,12 +150,13 @@ __device__ bool block_barrier(const CommCtx& c) {
   if (threadIdx.x < c.world) {
     const int r = threadIdx.x;
     uint32_t* remote = reinterpret_cast<uint32_t*>(c.peer[r]) + blockIdx.x * MAX_RANKS + c.rank;
+    remote[KIND_OFF] = kind;  // ordered before the epoch by the release store below
     st_release_sys(remote, e);
     if (healthy) {
       const uint32_t* mine = flags + blockIdx.x * MAX_RANKS + r;
       unsigned long long t0 = 0;
-      uint32_t spins = 0;
-      while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
+      uint32_t spins = 0, seen;
+      while ((int32_t)((seen = ld_acquire_sys(mine)) - e) < 0) {
         if ((++spins & 1023u) == 0u && c.timeout_ns != 0ull) {
           const unsigned long long now = globaltimer_ns();
           if (t0 == 0) t0 = now;
@@ -154,6 +166,11 @@ __device__ bool block_barrier(const CommCtx& c) {
             break;
           }
         }
+      }
+      // the peer is at exactly this epoch (not already one ahead): its kind word belongs to this barrier
+      if (ok_s && seen == e && ld_acquire_sys(mine + KIND_OFF) != kind) {
+        report_timeout(c, ERR_KIND_MISMATCH, (uint32_t)r, e);
+        ok_s = 0;
       }
     }
   }
@@ -214,7 +231,7 @@ allreduce_optim_kernel(CommCtx c, size_t grad_off, long long start, long long co
                        const float* __restrict__ hyper, float* master, float* m, float* v, __nv_bfloat16* shadow,
                        float* avg_out) {
   optim_load_hyper(o, hyper);
-  if (!block_barrier(c)) return;
+  if (!block_barrier(c, KIND_AR)) return;
   const long long n4 = count >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long q0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; q0 < n4; q0 += stride * COMM_U) {
@@ -235,7 +252,7 @@ allreduce_optim_kernel(CommCtx c, size_t grad_off, long long start, long long co
       }
     }
   }
-  block_barrier(c);  // nobody may overwrite its gradient bucket while a peer still reads it
+  block_barrier(c, KIND_AR);  // nobody may overwrite its gradient bucket while a peer still reads it
 }
 
 // ---- K-RS-OPT (+ all-gather by peer stores). bounds[r]..bounds[r+1] is rank r's owned element range (multiples
@@ -345,7 +362,7 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, const
       backup_finish(c);
       return;
     }
-  } else if (!block_barrier(c)) {
+  } else if (!block_barrier(c, KIND_RS)) {
     return;
   }
   const long long start = bounds.b[c.rank];
@@ -373,7 +390,7 @@ rs_optim_ag_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, const
       }
     }
   }
-  block_barrier(c);  // all shards have landed everywhere; gradients may be overwritten
+  block_barrier(c, KIND_RS);  // all shards have landed everywhere; gradients may be overwritten
   if (backup) backup_finish(c);
 }
 
@@ -403,7 +420,7 @@ __global__ void __launch_bounds__(512)
 rs_optim_ag_nvls_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, const float* __restrict__ hyper,
                         float* master, float* m, float* v, size_t shadow_off, PushF32 f32, NoPush np) {
   optim_load_hyper(o, hyper);
-  if (!block_barrier(c)) return;
+  if (!block_barrier(c, KIND_RS)) return;
   const long long start = bounds.b[c.rank];
   const long long n4 = (bounds.b[c.rank + 1] - start) >> 2;
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -430,13 +447,13 @@ rs_optim_ag_nvls_kernel(CommCtx c, size_t grad_off, Bounds bounds, OptimArgs o, 
       if (i >= f32.lo && i < f32.hi) multimem_st_f4(reinterpret_cast<float*>(c.mc + f32.master_off) + i, p);
     }
   }
-  block_barrier(c);
+  block_barrier(c, KIND_RS);
 }
 
 // ---- all-gather of owned slices by peer stores (16-byte units): used for checkpoint gathers and weight pulls.
 __global__ void __launch_bounds__(512)
 allgather_slices_kernel(CommCtx c, size_t buf_off, Bounds bounds16) {
-  if (!block_barrier(c)) return;
+  if (!block_barrier(c, KIND_AG)) return;
   const long long start = bounds16.b[c.rank];
   const long long n = bounds16.b[c.rank + 1] - start;
   const uint4* src = reinterpret_cast<const uint4*>(c.peer[c.rank] + buf_off) + start;
@@ -446,7 +463,7 @@ allgather_slices_kernel(CommCtx c, size_t buf_off, Bounds bounds16) {
     for (int r = 0; r < MAX_RANKS; ++r)
       if (r < c.world && r != c.rank) reinterpret_cast<uint4*>(c.peer[r] + buf_off)[start + q] = val;
   }
-  block_barrier(c);
+  block_barrier(c, KIND_AG);
 }
 
 // ---- K-ASYNC. The version stamps and step counters live in the flag page and are advanced by the kernels, so a
@@ -566,7 +583,7 @@ __global__ void async_commit_kernel(CommCtx c, const uint32_t* snap) {
     st_release_sys(reinterpret_cast<uint32_t*>(c.peer[w]) + OWNER_STEP_OFF + c.rank, base + napplied);
 }
 
-__global__ void barrier_kernel(CommCtx c) { block_barrier(c); }
+__global__ void barrier_kernel(CommCtx c) { block_barrier(c, KIND_BARRIER); }
 
 // heartbeat: bump my counter in every peer's flag page; read what peers wrote into mine
 __global__ void heartbeat_kernel(CommCtx c, uint32_t beat, uint32_t* seen_out) {

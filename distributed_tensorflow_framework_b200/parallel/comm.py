@@ -200,7 +200,8 @@ class Communicator(object):
         code = _lib.call_raw("dtf_comm_error", self.handle, out)
         if not code:
             return None
-        what = {1: "barrier", 2: "gradient arrivals"}.get(int(code), "wait")
+        what = {1: "barrier", 2: "gradient arrivals", 3: "collective mismatch (a peer entered a different collective)"
+                }.get(int(code), "wait")
         return {"code": int(code), "what": what, "block": int(out[1]), "peer": int(out[2]), "epoch": int(out[3])}
 
     def check(self):
@@ -208,7 +209,7 @@ class Communicator(object):
         e = self.error()
         if e is not None:
             from ..runtime.session import WorkerLostError
-            raise WorkerLostError("rank %d: %s wait timed out (block %d, peer/arrivals %d, epoch %d)"
+            raise WorkerLostError("rank %d: %s: device-side wait failed (block %d, peer/arrivals %d, epoch %d)"
                                   % (self.rank, e["what"], e["block"], e["peer"], e["epoch"]))
 
     def clear_error(self, stream=None):

@@ -267,6 +267,8 @@ int dtf_comm_heartbeat(void* comm, unsigned int beat, unsigned int* seen_out_dev
 int dtf_comm_set_timeout_ms(void* comm, long long ms);
 int dtf_comm_error(void* comm, unsigned int* out4);
 int dtf_comm_clear_error(void* comm, void* stream);
+/* Error code 3 (collective mismatch): every barrier carries the kind of collective that entered it; a rank that meets a
+ * peer at the same epoch inside a different collective records it instead of silently exchanging the wrong data. */
 /* Fault injection / tests: occupy the stream for `ns` nanoseconds (an artificial straggler). */
 int dtf_debug_sleep(long long ns, void* stream);
 

@@ -141,6 +141,27 @@ def main():
         print("barrier time-out -> error record -> recovery ok", flush=True)
     dist.barrier()
 
+    # ---- 3b. protocol check: ranks that enter DIFFERENT collectives at the same barrier epoch are told so (this is
+    # what a chief-only checkpoint gather used to do silently: pair with the peers' next gradient collective)
+    dist.barrier()
+    if rank == 0:
+        comm.allgather_slices(heap.offset_of("shadow"), [0] + [8] * world)  # 128 bytes from rank 0: one block
+    else:
+        comm.barrier()
+    torch.cuda.synchronize()
+    e = comm.error()
+    check(e is not None and e["code"] == 3, "expected a collective-mismatch record, got %s" % (e,))
+    dist.barrier()
+    comm.clear_error()
+    torch.cuda.synchronize()
+    dist.barrier()
+    comm.barrier()
+    torch.cuda.synchronize()
+    check(comm.error() is None, "communicator unusable after the mismatch was cleared: %s" % (comm.error(),))
+    if rank == 0:
+        print("collective-kind mismatch detected and cleared ok", flush=True)
+    dist.barrier()
+
     # ---- 4. backup mode through the Trainer (captured graph) with the straggler injected on the last rank
     # (every rank trains on the SAME batch here: whichever subset an owner aggregates, the update is the same, so the
     # loss must fall on every rank; that late gradients are really dropped is what section 2 verified exactly)
