@@ -73,3 +73,22 @@ def test_kill_one_rank_and_resume_from_checkpoint(tmp_path):
     p = _torchrun(2, "_train_worker.py", md, "sync", 2, "kill", extra=("--max-restarts", "1"), timeout=900)
     assert p.returncode == 0 and "TRAIN_WORKER_OK 20 restart=1" in p.stdout, p.worker_tail
     assert "Restoring parameters from" in p.stdout and "model.ckpt-10" in p.stdout
+
+
+def test_gpu_num_two_without_a_launcher_spawns_one_rank_per_gpu(tmp_path):
+    """`@gpu_num(2)` and no torchrun: the container starts one process per GPU; both train (global batch =
+    batch_size x gpu_num as in the reference), the chief writes the checkpoint."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    md = str(tmp_path / "spawn")
+    os.makedirs(md)
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "TORCHELASTIC_RUN_ID",
+                                                            "MASTER_ADDR", "MASTER_PORT", "DTF_SPAWNED")}
+    p = subprocess.run([sys.executable, os.path.join(HERE, "_spawn_main.py"), md], stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=600, env=env)
+    out = p.stdout
+    assert p.returncode == 0 and "SPAWN_PARENT_OK" in out, out[-3000:]
+    assert "SPAWN_RANK_OK rank=0 world=2 device=cuda:0 step=10 towers=1" in out, out[-3000:]
+    assert "SPAWN_RANK_OK rank=1 world=2 device=cuda:1 step=10 towers=1" in out, out[-3000:]
+    from distributed_tensorflow_framework_b200.io import tensorbundle as tb
+    assert tb.latest_checkpoint(md).endswith("model.ckpt-10")
