@@ -603,7 +603,8 @@ __global__ void bn_fold_kernel(const float* __restrict__ run_mean, const float* 
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
                 __nv_bfloat16* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
-                long long R, int N, int relu, int rows_per_block, uint8_t* __restrict__ mask) {
+                long long R, int N, int relu, int rows_per_block, uint8_t* __restrict__ mask,
+                const float* __restrict__ rscale, const float* __restrict__ rshift) {
   const int cpr = N / 8;
   const int cg0 = blockIdx.x * 256;
   const int cprg = min(256, cpr - cg0);
@@ -612,11 +613,16 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   if (tid >= rpp * cprg) return;
   const int col_chunk = cg0 + (tid % cprg);
   const int row_lane = tid / cprg;
-  float sc[8], sh[8];
+  float sc[8], sh[8], rsc[8], rsh[8];
+  // rscale / rshift: the residual is itself the raw input of a batch norm (a projection shortcut) whose folded
+  // coefficients are applied here, so that branch's normalised tensor is never written or read
+  const bool res_affine = res != nullptr && rscale != nullptr;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     sc[j] = scale[col_chunk * 8 + j];
     sh[j] = shift[col_chunk * 8 + j];
+    rsc[j] = res_affine ? rscale[col_chunk * 8 + j] : 1.f;
+    rsh[j] = res_affine ? rshift[col_chunk * 8 + j] : 0.f;
   }
   const long long r0 = (long long)blockIdx.y * rows_per_block;
   const long long r1 = min(R, r0 + rows_per_block);
@@ -644,7 +650,7 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
         float q[8];
         unpack8(rbuf[u], q);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] += q[j];
+        for (int j = 0; j < 8; ++j) f[j] += fmaf(q[j], rsc[j], rsh[j]);
       }
       if (relu) {
         if (mask != nullptr) {  // bit j = (pre-activation of channel j > 0): all the backward needs of y
@@ -1430,6 +1436,9 @@ extern "C" int dtf_bn_fold(const float* run_mean, const float* run_var, const fl
   bn_fold_kernel<<<(N + 127) / 128, 128, 0, ST(stream)>>>(run_mean, run_var, gamma, beta, scale, shift, N, eps);
   return DTF_CHECK_LAUNCH();
 }
+extern "C" int dtf_bn_apply_dual(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
+                                 const float* shift, const float* res_scale, const float* res_shift, long long R,
+                                 int N, int relu, void* stream);
 extern "C" int dtf_bn_apply_mask(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
                                  const float* shift, long long R, int N, int relu, void* stream);
 extern "C" int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, const float* shift,
@@ -1438,12 +1447,17 @@ extern "C" int dtf_bn_apply(const void* x, const void* res, void* y, const float
 }
 extern "C" int dtf_bn_apply_mask(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
                                  const float* shift, long long R, int N, int relu, void* stream) {
+  return dtf_bn_apply_dual(x, res, y, relu_mask, scale, shift, nullptr, nullptr, R, N, relu, stream);
+}
+extern "C" int dtf_bn_apply_dual(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
+                                 const float* shift, const float* res_scale, const float* res_shift, long long R,
+                                 int N, int relu, void* stream) {
   if (N % 8) return DTF_ERR_ALIGN;
   int gx, gy, rpb;
   elementwise_geometry(R, N, &gx, &gy, &rpb);
   bn_apply_kernel<<<dim3(gx, gy), 256, 0, ST(stream)>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)res,
                                                         (__nv_bfloat16*)y, scale, shift, R, N, relu, rpb,
-                                                        (uint8_t*)relu_mask);
+                                                        (uint8_t*)relu_mask, res_scale, res_shift);
   return DTF_CHECK_LAUNCH();
 }
 // part[blocks][2][N] = per-row-block {sum dz, sum dz*xhat}; dz (optional output) = relu ? dy*(y>0) : dy

@@ -319,6 +319,48 @@ def batch_norm_train(x, rows, gvar=None, bvar=None, run_mean=None, run_var=None,
                              eps, momentum, relu, part)
 
 
+class DualBatchNormFn(torch.autograd.Function):
+    """y = relu(bn_a(x) + bn_b(xs)): the closing batch norm of a residual block whose shortcut is a projection
+    (convolution + batch norm). One apply pass reads both raw convolution outputs; the shortcut's normalised tensor is
+    never written. Backward: dz = dy * mask (bitmask from the forward), then each batch norm's own reduce + apply."""
+
+    @staticmethod
+    def forward(ctx, x, xs, ga_shadow, gs_shadow, gvar, bvar, rm, rv, gvar_s, bvar_s, rm_s, rv_s, rows, eps, momentum,
+                relu, part, part_s):
+        shape = x.shape
+        x2, xs2 = x.reshape(rows, -1), xs.reshape(rows, -1)
+        mean, rstd, scale, shift = raw.bn_stats_coeffs(x2, gvar.master, bvar.master, rm, rv, eps, momentum, part)
+        mean_s, rstd_s, scale_s, shift_s = raw.bn_stats_coeffs(xs2, gvar_s.master, bvar_s.master, rm_s, rv_s, eps,
+                                                               momentum, part_s)
+        y2, mask = raw.bn_apply_dual(x2, xs2, scale, shift, scale_s, shift_s, relu)
+        ctx.vars = (gvar, bvar, gvar_s, bvar_s)
+        ctx.relu, ctx.rows = relu, rows
+        ctx.save_for_backward(x2, xs2, mask, mean, rstd, mean_s, rstd_s)
+        return y2.view(shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, xs2, mask, mean, rstd, mean_s, rstd_s = ctx.saved_tensors
+        gvar, bvar, gvar_s, bvar_s = ctx.vars
+        shape = dy.shape
+        dy2 = dy.contiguous().view(ctx.rows, -1)
+        dx2, dz2, _, _ = raw.bn_bwd(dy2, mask if ctx.relu else None, x2, mean, rstd, gvar.master, ctx.relu,
+                                    dgamma_acc=gvar.grad, dbeta_acc=bvar.grad)
+        _ready(gvar)
+        _ready(bvar)
+        dxs2, _, _, _ = raw.bn_bwd(dz2, None, xs2, mean_s, rstd_s, gvar_s.master, False, dgamma_acc=gvar_s.grad,
+                                   dbeta_acc=bvar_s.grad)
+        _ready(gvar_s)
+        _ready(bvar_s)
+        return (dx2.view(shape), dxs2.view(shape)) + (None,) * 16
+
+
+def batch_norm_dual_train(x, xs, rows, gvar, bvar, rm, rv, gvar_s, bvar_s, rm_s, rv_s, eps=1e-3, momentum=0.1,
+                          relu=True, part=None, part_s=None):
+    return DualBatchNormFn.apply(x, xs, gvar.shadow, gvar_s.shadow, gvar, bvar, rm, rv, gvar_s, bvar_s, rm_s, rv_s, rows,
+                                 eps, momentum, relu, part, part_s)
+
+
 def batch_norm_eval(x, rows, gvar, bvar, run_mean, run_var, eps=1e-3, res=None, relu=False):
     shape = x.shape
     y = raw.bn_eval_fwd(x.reshape(rows, -1), gvar.master if gvar is not None else None,

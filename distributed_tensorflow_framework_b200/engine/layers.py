@@ -252,17 +252,36 @@ def batch_norm(x):
     return _q((xf - mean) * torch.rsqrt(var + epsilon))
 
 
-def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momentum=0.1, stats_part=None):
-    """Standard per-channel batch norm with affine parameters and running statistics (needed by the ResNet
-    configs of BASELINE.json; optionally fused with a residual add and ReLU). `stats_part`: per-tile statistics of x
-    from the convolution that produced it (conv_nonacti(..., emit_stats=True)); saves the statistics pass."""
-    C = x.shape[-1]
+def _bn_vars(layer_name, C):
     with variable_scope(layer_name):
-        beta = _get("beta", [C], ConstantInitializer(0.0), kind="bias")  # beta first: [beta | gamma] are adjacent in
-        gamma = _get("gamma", [C], ConstantInitializer(1.0), kind="bias")  # the arenas (see BatchNormFn.backward)
+        beta = _get("beta", [C], ConstantInitializer(0.0), kind="bias")
+        gamma = _get("gamma", [C], ConstantInitializer(1.0), kind="bias")
         rm = _get("moving_mean", [C], ConstantInitializer(0.0), trainable=False)
         rv = _get("moving_variance", [C], ConstantInitializer(1.0), trainable=False)
+    return gamma, beta, rm, rv
+
+
+def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momentum=0.1, stats_part=None,
+                       residual_bn=None, residual_part=None):
+    """Standard per-channel batch norm with affine parameters and running statistics (needed by the ResNet
+    configs of BASELINE.json; optionally fused with a residual add and ReLU). `stats_part`: per-tile statistics of x
+    from the convolution that produced it (conv_nonacti(..., emit_stats=True)); saves the statistics pass.
+    `residual_bn` (a layer name): the residual is the RAW output of a projection shortcut's convolution and goes
+    through its own batch norm (variables under that name) inside the same pass -- y = act(bn(x) + bn_r(residual));
+    `residual_part`: that convolution's epilogue statistics."""
+    C = x.shape[-1]
+    gamma, beta, rm, rv = _bn_vars(layer_name, C)
     rows = x.numel() // C
+    if residual_bn is not None:
+        assert residual is not None
+        gamma_r, beta_r, rm_r, rv_r = _bn_vars(residual_bn, C)
+        if x.is_cuda and _training and C % 8 == 0:
+            return Fn.batch_norm_dual_train(x.contiguous(), residual.contiguous(), rows, gamma, beta, rm.master,
+                                            rv.master, gamma_r, beta_r, rm_r.master, rv_r.master, eps, momentum, relu,
+                                            stats_part, residual_part)
+        # eval / CPU: normalise the shortcut on its own, then the plain fused path
+        residual = batch_norm_channel(residual_bn, residual, relu=False, eps=eps, momentum=momentum,
+                                      stats_part=residual_part)
     if x.is_cuda:
         x = x.contiguous()
         if _training:

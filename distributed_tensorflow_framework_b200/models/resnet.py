@@ -27,7 +27,18 @@ def set_relu(flag):
     return old
 
 
-def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None, fork_input=False):
+def _conv_only(name, x, cin, cout, k, stride):
+    """A convolution whose batch norm is applied by its consumer (projection shortcut): (raw output, statistics)."""
+    emit = EPILOGUE_BN_STATS >= 2 or (EPILOGUE_BN_STATS == 1 and k == 1)
+    if emit:
+        y, _, part = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1],
+                                    use_bias=False, emit_stats=True)
+        return y, part
+    return L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1], use_bias=False), None
+
+
+def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None, fork_input=False, residual_bn=None,
+             residual_part=None):
     relu = relu and _RELU
     emit = EPILOGUE_BN_STATS >= 2 or (EPILOGUE_BN_STATS == 1 and k == 1)
     if fork_input or emit:
@@ -36,7 +47,8 @@ def _conv_bn(name, x, cin, cout, k, stride, relu=True, residual=None, fork_input
     else:
         y, x_fwd, part = L.conv_nonacti(name, x, cin, cout, kernel_size=[k, k], stride=[1, stride, stride, 1],
                                         use_bias=False), None, None
-    out = L.batch_norm_channel(name + "/bn", y, relu=relu, residual=residual, stats_part=part)
+    out = L.batch_norm_channel(name + "/bn", y, relu=relu, residual=residual, stats_part=part,
+                               residual_bn=residual_bn, residual_part=residual_part)
     return (out, x_fwd) if fork_input else out  # x_fwd: x forwarded for the shortcut branch
 
 
@@ -45,7 +57,10 @@ def _basic_block(name, x, cin, cout, stride):
         # conv1 forwards x to the shortcut branch so that both gradients of x meet inside conv1's backward
         y, shortcut = _conv_bn("conv1", x, cin, cout, 3, stride, fork_input=True)
         if stride != 1 or cin != cout:
-            shortcut = _conv_bn("shortcut", shortcut, cin, cout, 1, stride, relu=False)
+            # projection shortcut: its batch norm is applied inside conv2's closing batch norm (one pass over both)
+            raw_s, part_s = _conv_only("shortcut", shortcut, cin, cout, 1, stride)
+            return _conv_bn("conv2", y, cout, cout, 3, 1, relu=True, residual=raw_s, residual_bn="shortcut/bn",
+                            residual_part=part_s)
         return _conv_bn("conv2", y, cout, cout, 3, 1, relu=True, residual=shortcut)
 
 
@@ -53,9 +68,11 @@ def _bottleneck(name, x, cin, mid, stride):
     cout = mid * 4
     with variable_scope(name):
         y, shortcut = _conv_bn("conv1", x, cin, mid, 1, 1, fork_input=True)
-        if stride != 1 or cin != cout:
-            shortcut = _conv_bn("shortcut", shortcut, cin, cout, 1, stride, relu=False)
         y = _conv_bn("conv2", y, mid, mid, 3, stride)
+        if stride != 1 or cin != cout:
+            raw_s, part_s = _conv_only("shortcut", shortcut, cin, cout, 1, stride)
+            return _conv_bn("conv3", y, mid, cout, 1, 1, relu=True, residual=raw_s, residual_bn="shortcut/bn",
+                            residual_part=part_s)
         return _conv_bn("conv3", y, mid, cout, 1, 1, relu=True, residual=shortcut)
 
 

@@ -447,6 +447,34 @@ def bn_train_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, re
     return y, mean, rstd, scale, shift
 
 
+def bn_stats_coeffs(x2d, gamma, beta, run_mean, run_var, eps=1e-3, momentum=0.1, part=None):
+    """Training-mode statistics of x2d [R, N] folded into (mean, rstd, scale, shift); updates the running statistics.
+    `part`: per-tile partial sums already produced by the kernel that wrote x2d (no statistics pass then)."""
+    R, N = x2d.shape
+    stat = torch.empty(4, N, device=x2d.device, dtype=torch.float32)
+    mean, rstd, scale, shift = stat[0], stat[1], stat[2], stat[3]
+    if part is not None and tuple(part.shape[1:]) == (2, N):
+        _lib.call("dtf_bn_finalize_rows", part, part.shape[0], gamma, beta, mean, rstd, scale, shift, run_mean, run_var,
+                  N, R, eps, momentum, _sp())
+    else:
+        part = _part(R, N, x2d.device)
+        _lib.call("dtf_bn_stats", x2d, part, R, N, _sp())
+        _lib.call("dtf_bn_finalize", part, gamma, beta, mean, rstd, scale, shift, run_mean, run_var, N, R, eps,
+                  momentum, _sp())
+    return mean, rstd, scale, shift
+
+
+def bn_apply_dual(x2d, res2d, scale, shift, res_scale, res_shift, relu=True):
+    """y = act(x*scale + shift + res*res_scale + res_shift) (+ the ReLU bitmask): two batch norms joined by a residual
+    add in one pass; the normalised residual branch is never written."""
+    R, N = x2d.shape
+    y = torch.empty_like(x2d)
+    mask = torch.empty((R, N // 8), device=x2d.device, dtype=torch.uint8) if relu else None
+    _lib.call("dtf_bn_apply_dual", x2d, res2d, y, mask, scale, shift, res_scale, res_shift, R, N, 1 if relu else 0,
+              _sp())
+    return y, mask
+
+
 def bn_eval_fwd(x2d, gamma, beta, run_mean, run_var, eps=1e-3, res=None, relu=False):
     R, N = x2d.shape
     scale = torch.empty(N, device=x2d.device, dtype=torch.float32)

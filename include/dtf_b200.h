@@ -133,6 +133,10 @@ int dtf_bn_apply(const void* x, const void* res, void* y, const float* scale, co
  * is positive): the backward of a batch norm with a residual input reads 1 bit per element instead of y. */
 int dtf_bn_apply_mask(const void* x, const void* res, void* y, void* relu_mask, const float* scale,
                       const float* shift, long long R, int N, int relu, void* stream);
+/* Same, with the residual itself passing through a batch norm: y = act(x*scale + shift + res*res_scale + res_shift).
+ * A projection shortcut's normalised tensor is then never materialised (res = the shortcut convolution's raw output). */
+int dtf_bn_apply_dual(const void* x, const void* res, void* y, void* relu_mask, const float* scale, const float* shift,
+                      const float* res_scale, const float* res_shift, long long R, int N, int relu, void* stream);
 /* relu: 0 none, 1 mask from y, 2 mask recomputed from x with the forward's folded scale/shift (no y read, no dz),
  * 3 `y` is the bitmask of dtf_bn_apply_mask. */
 int dtf_bn_bwd_reduce(const void* dy, const void* y, const void* x, void* dz, float* part, const float* mean,
