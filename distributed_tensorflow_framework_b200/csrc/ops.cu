@@ -749,7 +749,11 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* _
 template <int TKH, int TKW>
 __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                 uint8_t* __restrict__ idx, int n_img, int H, int W, int C, int OH, int OW, int kh_,
-                                int kw_, int sh, int sw, int pt, int pl, int is_max) {
+                                int kw_, int sh, int sw, int pt, int pl, int is_max,
+                                const float* __restrict__ pre_scale = nullptr,
+                                const float* __restrict__ pre_shift = nullptr) {
+  // pre_scale / pre_shift (compile-time windows only): every window element first goes through
+  // relu(x * scale[c] + shift[c]) -- a batch norm + ReLU applied while pooling, whose output is never stored
   const int kh = TKH > 0 ? TKH : kh_, kw = TKW > 0 ? TKW : kw_;
   const int cpr = C / 8;
   const long long total = (long long)n_img * OH * OW * cpr;
@@ -779,10 +783,23 @@ __global__ void pool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
           if (ok[dy * TKW + dx]) win[dy * TKW + dx] = ld8(x + (((long long)n * H + ih) * W + iw) * C + c0);
         }
 #pragma unroll
+      float psc[8], psh[8];
+      if (pre_scale != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          psc[j] = pre_scale[c0 + j];
+          psh[j] = pre_shift[c0 + j];
+        }
+      }
+#pragma unroll
       for (int t = 0; t < TKH * TKW; ++t) {
         if (!ok[t]) continue;
         float f[8];
         unpack8(win[t], f);
+        if (pre_scale != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = fmaxf(fmaf(f[j], psc[j], psh[j]), 0.f);
+        }
         if (is_max) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -1488,14 +1505,26 @@ extern "C" int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const f
                                                             mask_shift);
   return DTF_CHECK_LAUNCH();
 }
+extern "C" int dtf_pool_fwd_affine(const void* x, void* y, void* idx, const float* pre_scale, const float* pre_shift,
+                                   int n_img, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
+                                   int pt, int pl, int is_max, void* stream);
 extern "C" int dtf_pool_fwd(const void* x, void* y, void* idx, int n_img, int H, int W, int C, int OH, int OW, int kh,
                             int kw, int sh, int sw, int pt, int pl, int is_max, void* stream) {
+  return dtf_pool_fwd_affine(x, y, idx, nullptr, nullptr, n_img, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl, is_max,
+                             stream);
+}
+extern "C" int dtf_pool_fwd_affine(const void* x, void* y, void* idx, const float* pre_scale, const float* pre_shift,
+                                   int n_img, int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw,
+                                   int pt, int pl, int is_max, void* stream) {
   if (C % 8) return DTF_ERR_ALIGN;
   if (kh * kw > 255) return DTF_ERR_UNSUPPORTED;
+  if (pre_scale != nullptr && !((kh == 3 && kw == 3) || (kh == 2 && kw == 2))) return DTF_ERR_UNSUPPORTED;
+  if ((pre_scale == nullptr) != (pre_shift == nullptr)) return DTF_ERR_ARG;
   const long long total = (long long)n_img * OH * OW * (C / 8);
 #define DTF_POOL_FWD(KH_, KW_)                                                                                 \
   pool_fwd_kernel<KH_, KW_><<<grid_for(total, 256), 256, 0, ST(stream)>>>(                                     \
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (uint8_t*)idx, n_img, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl, is_max)
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, (uint8_t*)idx, n_img, H, W, C, OH, OW, kh, kw, sh, sw, pt, pl, is_max, \
+      pre_scale, pre_shift)
   if (kh == 3 && kw == 3) DTF_POOL_FWD(3, 3);
   else if (kh == 2 && kw == 2) DTF_POOL_FWD(2, 2);
   else DTF_POOL_FWD(0, 0);

@@ -319,6 +319,36 @@ def batch_norm_train(x, rows, gvar=None, bvar=None, run_mean=None, run_var=None,
                              eps, momentum, relu, part)
 
 
+class BnReluPoolFn(torch.autograd.Function):
+    """max_pool(relu(batch_norm(x))): the normalised tensor is produced inside the pooling kernel's window loads and
+    never stored (ResNet stem: saves a write and a read of the largest activation of the network)."""
+
+    @staticmethod
+    def forward(ctx, x, g_shadow, gvar, bvar, rm, rv, rows, eps, momentum, k, s, part):
+        x = x.contiguous()
+        x2 = x.reshape(rows, -1)
+        mean, rstd, scale, shift = raw.bn_stats_coeffs(x2, gvar.master, bvar.master, rm, rv, eps, momentum, part)
+        y, idx = raw.pool_fwd(x, k, s, True, want_idx=True, pre_scale=scale, pre_shift=shift)
+        ctx.gvar, ctx.bvar, ctx.rows, ctx.k, ctx.s, ctx.in_shape = gvar, bvar, rows, k, s, tuple(x.shape)
+        ctx.save_for_backward(x2, idx, mean, rstd, scale, shift)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, idx, mean, rstd, scale, shift = ctx.saved_tensors
+        gvar, bvar = ctx.gvar, ctx.bvar
+        d_bn = raw.pool_bwd(idx, dy.contiguous(), ctx.in_shape, ctx.k, ctx.s, True)
+        dx2, _, _, _ = raw.bn_bwd(d_bn.view(ctx.rows, -1), None, x2, mean, rstd, gvar.master, True,
+                                  dgamma_acc=gvar.grad, dbeta_acc=bvar.grad, mask_scale=scale, mask_shift=shift)
+        _ready(gvar)
+        _ready(bvar)
+        return (dx2.view(ctx.in_shape),) + (None,) * 11
+
+
+def batch_norm_relu_pool_train(x, rows, gvar, bvar, rm, rv, k, s, eps=1e-3, momentum=0.1, part=None):
+    return BnReluPoolFn.apply(x, gvar.shadow, gvar, bvar, rm, rv, rows, eps, momentum, tuple(k), tuple(s), part)
+
+
 class DualBatchNormFn(torch.autograd.Function):
     """y = relu(bn_a(x) + bn_b(xs)): the closing batch norm of a residual block whose shortcut is a projection
     (convolution + batch norm). One apply pass reads both raw convolution outputs; the shortcut's normalised tensor is

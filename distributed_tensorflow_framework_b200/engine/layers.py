@@ -296,6 +296,22 @@ def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momen
     return _q(F.relu(y) if relu else y)
 
 
+def batch_norm_relu_pool(bn_name, pool_name, x, kernel=[1, 3, 3, 1], stride=[1, 2, 2, 1], eps=1e-3, momentum=0.1,
+                         stats_part=None):
+    """max_pool(relu(batch_norm_channel(x))) -- the ResNet stem. On CUDA in training mode one kernel pools over the
+    normalised values computed on the fly (3x3 / 2x2 windows); elsewhere it is the composition of the three layers.
+    Variables are those of batch_norm_channel(bn_name)."""
+    C = x.shape[-1]
+    k = (int(kernel[1]), int(kernel[2])) if len(kernel) == 4 else tuple(kernel)
+    s = _stride_hw(stride)
+    if x.is_cuda and _training and C % 8 == 0 and k in ((3, 3), (2, 2)):
+        gamma, beta, rm, rv = _bn_vars(bn_name, C)
+        return Fn.batch_norm_relu_pool_train(x, x.numel() // C, gamma, beta, rm.master, rv.master, k, s, eps, momentum,
+                                             stats_part)
+    y = batch_norm_channel(bn_name, x, relu=True, eps=eps, momentum=momentum, stats_part=stats_part)
+    return pool(pool_name, y, kernel=kernel, stride=stride)
+
+
 def norm(name, x, lsize=4):
     """tf.nn.lrn(depth_radius=lsize, bias=1, alpha=0.001/9, beta=0.75) -- distribute_tools.py:183-187. The reference
     discards the result and returns x unchanged; that behaviour is kept behind --lrn_compat_noop."""

@@ -82,8 +82,13 @@ class _ResNet(Model):
     bottleneck = False
 
     def inference(self, images, *args, **kwargs):
-        x = _conv_bn("conv1", images, 3, 64, 7, 2)
-        x = L.pool("pool1", x, kernel=[1, 3, 3, 1], stride=[1, 2, 2, 1])
+        if _RELU:  # stem: batch norm + ReLU are applied inside the max-pool kernel
+            y, part = _conv_only("conv1", images, 3, 64, 7, 2)
+            x = L.batch_norm_relu_pool("conv1/bn", "pool1", y, kernel=[1, 3, 3, 1], stride=[1, 2, 2, 1],
+                                       stats_part=part)
+        else:
+            x = _conv_bn("conv1", images, 3, 64, 7, 2)
+            x = L.pool("pool1", x, kernel=[1, 3, 3, 1], stride=[1, 2, 2, 1])
         cin = 64
         for stage, n in enumerate(self.blocks):
             width = 64 * (2 ** stage)

@@ -383,13 +383,15 @@ def pool_geometry(H, W, k, s):
     return OH, OW, pt, pl
 
 
-def pool_fwd(x, k=(2, 2), s=(2, 2), is_max=True, want_idx=True):
-    """Returns (y, idx); idx (uint8 argmax positions) is None for average pooling."""
+def pool_fwd(x, k=(2, 2), s=(2, 2), is_max=True, want_idx=True, pre_scale=None, pre_shift=None):
+    """Returns (y, idx); idx (uint8 argmax positions) is None for average pooling. With pre_scale / pre_shift the
+    pooled quantity is relu(x * scale + shift) (batch norm + ReLU applied on the fly)."""
     n, H, W, C = x.shape
     OH, OW, pt, pl = pool_geometry(H, W, k, s)
     y = torch.empty((n, OH, OW, C), device=x.device, dtype=bf16)
     idx = torch.empty((n, OH, OW, C), device=x.device, dtype=torch.uint8) if (is_max and want_idx) else None
-    _lib.call("dtf_pool_fwd", x, y, idx, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl, 1 if is_max else 0, _sp())
+    _lib.call("dtf_pool_fwd_affine", x, y, idx, pre_scale, pre_shift, n, H, W, C, OH, OW, k[0], k[1], s[0], s[1], pt, pl,
+              1 if is_max else 0, _sp())
     return y, idx
 
 

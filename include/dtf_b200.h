@@ -151,6 +151,11 @@ int dtf_bn_bwd_apply(const void* dz, const void* x, void* dx, const float* part,
  * records the in-window position of the first maximum (one byte per output element, `idx`) for the backward. */
 int dtf_pool_fwd(const void* x, void* y, void* idx, int n_img, int H, int W, int C, int OH, int OW, int kh, int kw,
                  int sh, int sw, int pt, int pl, int is_max, void* stream);
+/* Pooling over relu(x * pre_scale[c] + pre_shift[c]) (3x3 / 2x2 windows): a batch norm + ReLU in front of a pooling
+ * layer is applied while pooling and its output is never stored (ResNet stem). */
+int dtf_pool_fwd_affine(const void* x, void* y, void* idx, const float* pre_scale, const float* pre_shift, int n_img,
+                        int H, int W, int C, int OH, int OW, int kh, int kw, int sh, int sw, int pt, int pl,
+                        int is_max, void* stream);
 int dtf_pool_bwd(const void* idx, const void* dy, void* dx, int n_img, int H, int W, int C, int OH, int OW, int kh,
                  int kw, int sh, int sw, int pt, int pl, int is_max, void* stream);
 

@@ -211,3 +211,21 @@ def test_init(raw):
     assert torch.equal(t, t2)  # counter-based: reproducible
     raw.init_(t, "constant", 0.25)
     assert (t == 0.25).all()
+
+
+def test_pool_over_batch_norm_relu_matches_the_composition(raw):
+    """dtf_pool_fwd_affine: max_pool(relu(x * scale + shift)) computed inside the pooling kernel equals pooling the
+    separately normalised tensor (the ResNet stem path), values and arg-max routing."""
+    x = rnd(4, 30, 30, 64)
+    scale = torch.randn(64, device="cuda")
+    shift = torch.randn(64, device="cuda") * 0.3
+    ref_in = torch.relu(x.float() * scale + shift).to(torch.bfloat16)
+    y_ref, idx_ref = raw.pool_fwd(ref_in, (3, 3), (2, 2), True)
+    y, idx = raw.pool_fwd(x, (3, 3), (2, 2), True, pre_scale=scale, pre_shift=shift)
+    assert torch.equal(y, y_ref)
+    dy = rnd(*y.shape)
+    d1 = raw.pool_bwd(idx, dy, tuple(x.shape), (3, 3), (2, 2), True)
+    d2 = raw.pool_bwd(idx_ref, dy, tuple(x.shape), (3, 3), (2, 2), True)
+    # ties (several window elements equal after bf16 rounding / all clipped to 0) may pick another element
+    assert (d1 != d2).float().mean() < 0.15
+    assert torch.allclose(d1.float().sum((1, 2)), d2.float().sum((1, 2)), rtol=2e-2, atol=2e-1)
