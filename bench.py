@@ -138,12 +138,13 @@ def run_ours(args, cfg):
     _lib.lib()
     batch = args.batch or cfg["batch"]
     loss = dtf.SoftmaxCrossEntropyLoss() if cfg["loss"] == "xent" else dtf.MSELoss()
-    opt = dtf.MomentumOptimizer(0.01, 0.9)
     algo = args.algo
     if args.config == "resnet18_async" and world > 1 and algo == "auto":
         algo = "async"
     if algo == "auto_sync":  # the async config's model with the synchronous collective (for comparison)
         algo = "auto"
+    # asynchronous parameter server: every rank's push is its own update, so the rate is scaled by 1/N as usual
+    opt = dtf.MomentumOptimizer(0.01 / world if algo == "async" else 0.01, 0.9)
     trainer = dtf.Trainer(dtf.Net(getattr(models, cfg["model"])()), loss, opt, device=device, rank=rank, world=world,
                           group=group, algo=algo, use_cuda_graph=not args.no_graph, seed=0)
     pool = [make_batch(cfg, batch, 100 + rank * 10 + i) for i in range(2)]

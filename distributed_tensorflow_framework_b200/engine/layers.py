@@ -118,7 +118,8 @@ def _prep_cuda_input(x, cin_store):
         if x.dtype == torch.bfloat16:
             x = F.pad(x, (0, cin_store - x.shape[-1]))
         else:
-            x = Fn.convert_input(x, cin_store)
+            # uint8 images are mapped to [0, 1] (tf.image.convert_image_dtype semantics); floats pass unchanged
+            x = Fn.convert_input(x, cin_store, scale=(1.0 / 255.0) if x.dtype == torch.uint8 else 1.0)
     return x.contiguous()
 
 
@@ -139,6 +140,8 @@ def _conv_impl(x, w, b, stride, relu, fork=False, emit_stats=False):
     if fork or emit_stats:
         return _conv_impl(x, w, b, stride, relu), (x if fork else None), None
     xn = x.float().permute(0, 3, 1, 2)
+    if x.dtype == torch.uint8:
+        xn = xn / 255.0
     xn = F.pad(xn, _same_pad_nchw(xn, (KH, KW), (sh, sw)))
     y = F.conv2d(xn, w.master.permute(3, 2, 0, 1), b.master if b is not None else None, stride=(sh, sw))
     if relu:

@@ -118,7 +118,9 @@ def main():
         torch.manual_seed(100 + rank)
         x = torch.rand(32, 32, 32, 3)
         y = torch.randint(0, 10, (32,))
-        tr = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.MomentumOptimizer(0.01, 0.9),
+        # asynchronous mode applies every rank's push as its own update: the usual 1/N learning-rate scaling
+        lr = 0.01 / world if algo == "async" else 0.01
+        tr = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.MomentumOptimizer(lr, 0.9),
                          device=dev, rank=rank, world=world, group=dist.group.WORLD, algo=algo, seed=5,
                          use_cuda_graph=(algo == "oneshot"))
         losses = [float(tr.step((x, y))) for _ in range(12)]
