@@ -13,10 +13,9 @@ for line in out.splitlines():
         fn = m.group(1)
         counts[fn] = collections.Counter()
         continue
-    m = re.search(r"/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d\s+)?([A-Z][A-Z0-9_.]+)", line)
-    if m and fn:
-        op = m.group(1)
-        if KEEP.match(op):
+    if fn:
+        for op in re.findall(r"\b((?:LDGMC|STGMC|REDGMC|UTCHMMA|UTCQMMA|UTCBAR|UTCATOMSWS|LDTM|STTM|UTMALDG|UTMASTG|UTMAPF|"
+                             r"SYNCS|LDGSTS|UBLKCP|ELECT|LDS|STS|RED|ATOMG?)(?:\.[A-Za-z0-9_]+)*)\b", line):
             op = re.sub(r"^(LDTM)\..*", r"\1.", op)
             counts[fn][op] += 1
 with open(sys.argv[1] if len(sys.argv) > 1 else os.path.join(root, "profiles", "r2", "sass_evidence_r2.txt"), "w") as f:
