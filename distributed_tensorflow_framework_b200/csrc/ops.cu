@@ -1085,9 +1085,13 @@ softmax_xent_kernel(const T* __restrict__ logits, const long long* __restrict__ 
     float se = 0.f;
     for (int c = lane; c < C; c += 32) se += __expf(ldf(x, c) - mx);
     se = warp_sum(se);
-    const int lab = (int)labels[row];
+    // a label outside [0, C) never indexes the row: its loss term is NaN (what TF's GPU kernel of
+    // sparse_softmax_cross_entropy_with_logits returns) and its gradient is the plain softmax
+    const long long lab64 = labels[row];
+    const bool lab_ok = lab64 >= 0 && lab64 < (long long)C;
+    const int lab = lab_ok ? (int)lab64 : -1;
     const float lse = mx + __logf(se);
-    if (lane == 0) scratch[1 + row] = lse - ldf(x, lab);
+    if (lane == 0) scratch[1 + row] = lab_ok ? lse - ldf(x, lab) : __int_as_float(0x7fc00000);
     if (dlogits != nullptr) {
       const float inv = 1.f / se;
       const float gs = gscale / (float)B;

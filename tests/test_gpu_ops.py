@@ -229,3 +229,22 @@ def test_pool_over_batch_norm_relu_matches_the_composition(raw):
     # ties (several window elements equal after bf16 rounding / all clipped to 0) may pick another element
     assert (d1 != d2).float().mean() < 0.15
     assert torch.allclose(d1.float().sum((1, 2)), d2.float().sum((1, 2)), rtol=2e-2, atol=2e-1)
+
+
+def test_softmax_xent_out_of_range_label_is_nan_not_a_wild_read(raw):
+    logits = torch.randn(16, 10, device="cuda")
+    labels = torch.randint(0, 10, (16,), device="cuda")
+    labels[3] = 10 ** 12  # far outside the row: must not be used as an index
+    labels[5] = -7
+    loss, dl = raw.softmax_xent(logits, labels)
+    torch.cuda.synchronize()
+    assert bool(torch.isnan(loss).all())
+    sm = torch.softmax(logits, 1) / 16
+    assert torch.allclose(dl[3], sm[3], atol=1e-6) and torch.allclose(dl[5], sm[5], atol=1e-6)
+    good = torch.ones(16, dtype=torch.bool, device="cuda")
+    good[3] = good[5] = False
+    ref = torch.softmax(logits, 1)
+    ref[torch.arange(16), labels.clamp(0, 9)] -= 1
+    assert torch.allclose(dl[good], (ref / 16)[good], atol=1e-6)
+    loss2, _ = raw.softmax_xent(logits, labels.clamp(0, 9))  # the scratch counter was left clean
+    assert bool(torch.isfinite(loss2).all())
