@@ -52,8 +52,8 @@ struct IgemmParams {
   // optional bf16 [M, N] (row stride ldc) added to the result before the ReLU: residual inputs, and the second
   // gradient of a tensor with two consumers (so autograd never has to sum them in a separate pass)
   const __nv_bfloat16* addend;
-  // optional batch-norm statistics of the (bf16-rounded) output: per-warp partial rows [grid * 4][2][N] of column
-  // sums and sums of squares, accumulated in shared memory across the tiles of a persistent CTA
+  // optional batch-norm statistics of the (bf16-rounded) output: per-CTA partial rows [grid][2][N] of column sums
+  // and sums of squares, accumulated in shared memory across the tiles of a persistent CTA
   float* stats;
 };
 
@@ -779,11 +779,13 @@ igemm_persistent_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
-    if (want_stats) {  // one partial row per (CTA, lane quarter); bn_finalize adds the rows in a fixed order
+    if (want_stats) {  // one partial row per CTA: the four quarters are added in a fixed order (reproducible)
       asm volatile("bar.sync 1, %0;\n" ::"r"(EW * 32) : "memory");
-      if (half == 0) {
-        float* o = p.stats + ((size_t)blockIdx.x * 4 + q) * 2 * p.N;
-        for (int i = lane; i < 2 * p.N; i += 32) o[i] = ld_shared_f32(my_acc + i * 4);
+      float* o = p.stats + (size_t)blockIdx.x * 2 * p.N;
+      const uint32_t qs = (uint32_t)(2 * p.N) * 4u;
+      for (int i = (half * 4 + q) * 32 + lane; i < 2 * p.N; i += EW * 32) {
+        const uint32_t a = acc_u32 + i * 4;
+        o[i] = (ld_shared_f32(a) + ld_shared_f32(a + qs)) + (ld_shared_f32(a + 2 * qs) + ld_shared_f32(a + 3 * qs));
       }
     }
   }
@@ -991,7 +993,7 @@ static int persistent_bn(int M, int N, int splits) {
 // Rows of the batch-norm statistics buffer [rows][2][N] that dtf_gemm_bf16_ex fills for this problem when given a
 // `stats` pointer, or 0 when the epilogue cannot produce them (then run dtf_bn_stats on the output). The persistent
 // kernel keeps per-warp column sums / sums of squares of the stored bf16 values in shared memory across its tiles and
-// writes one partial row per (CTA, epilogue warp): 4 x grid rows for dtf_bn_finalize_rows.
+// writes one partial row per CTA (`grid` rows) for dtf_bn_finalize_rows.
 extern "C" int dtf_gemm_stats_rows(const void* A, const void* B, const void* C, int M, int N, int K, int lda, int ldb,
                                    int ldc) {
   (void)K;
@@ -1003,7 +1005,7 @@ extern "C" int dtf_gemm_stats_rows(const void* A, const void* B, const void* C, 
     case 128: persistent_plan<128, 3>(M, N, 1, true, &smem, &grid); break;
     default: persistent_plan<256, 3>(M, N, 1, true, &smem, &grid); break;
   }
-  return smem <= kMaxSmemOptin ? grid * 4 : 0;
+  return smem <= kMaxSmemOptin ? grid : 0;
 }
 // Same with `addend` (bf16 [M, N], row stride ldc, may be NULL): C = act(A*B + bias + addend); bf16 outputs only.
 // `stats`: NULL, or a buffer of dtf_gemm_stats_rows(...) x 2 x N floats that receives per-warp partial column sums and

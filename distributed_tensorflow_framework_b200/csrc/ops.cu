@@ -535,11 +535,23 @@ __device__ __forceinline__ void reduce_partials(const float* __restrict__ part, 
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
 #pragma unroll
   for (int q = 0; q < NACC; ++q) {
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    // every warp issues all of its loads up front (8 independent accumulators): these kernels are pure latency --
+    // a few hundred partial rows, a handful of blocks -- and run 106 times per ResNet-50 step
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f, a5 = 0.f, a6 = 0.f, a7 = 0.f;
     if (c < N) {
       const float* p = part + (size_t)q * N + c;
       const size_t st = (size_t)NACC * N;
       int b = w;
+      for (; b + 7 * NW < nblk; b += 8 * NW) {
+        a0 += p[(size_t)b * st];
+        a1 += p[(size_t)(b + NW) * st];
+        a2 += p[(size_t)(b + 2 * NW) * st];
+        a3 += p[(size_t)(b + 3 * NW) * st];
+        a4 += p[(size_t)(b + 4 * NW) * st];
+        a5 += p[(size_t)(b + 5 * NW) * st];
+        a6 += p[(size_t)(b + 6 * NW) * st];
+        a7 += p[(size_t)(b + 7 * NW) * st];
+      }
       for (; b + 3 * NW < nblk; b += 4 * NW) {
         a0 += p[(size_t)b * st];
         a1 += p[(size_t)(b + NW) * st];
@@ -548,7 +560,7 @@ __device__ __forceinline__ void reduce_partials(const float* __restrict__ part, 
       }
       for (; b < nblk; b += NW) a0 += p[(size_t)b * st];
     }
-    sm[q][w][lane] = (a0 + a1) + (a2 + a3);
+    sm[q][w][lane] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
   }
   __syncthreads();
 #pragma unroll

@@ -191,7 +191,7 @@ def test_gemm_epilogue_statistics(raw, M, N, K):
     b = (torch.randn(K, N, device="cuda") * 0.1).to(torch.bfloat16)
     st = {}
     y = raw.gemm(a, b, stats=st)
-    assert "part" in st and st["part"].shape[1:] == (2, N) and st["part"].shape[0] % 4 == 0
+    assert "part" in st and st["part"].shape[1:] == (2, N) and 1 <= st["part"].shape[0] <= 296
     assert torch.equal(y, raw.gemm(a, b))
     tot = st["part"].double().sum(0)
     yf = y.double()
