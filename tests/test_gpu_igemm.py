@@ -247,3 +247,46 @@ def test_tap_masks_do_not_change_the_result(raw):
         raw.USE_TAP_MASKS = True
     for g, r in zip(got, ref):
         assert torch.equal(g, r)
+
+
+BOUNDARY_CONVS = [(2, 7, 7, 64, 64, 3, 3, 1), (1, 5, 9, 64, 128, 3, 3, 1), (2, 17, 19, 64, 192, 3, 3, 1),
+                  (3, 17, 19, 32, 64, 3, 3, 2), (2, 13, 13, 128, 128, 3, 3, 2), (2, 9, 9, 64, 64, 5, 5, 1),
+                  (2, 15, 15, 256, 64, 1, 1, 2), (1, 33, 33, 8, 64, 7, 7, 2)]
+
+
+@pytest.mark.parametrize("n,H,W,Ci,Co,KH,KW,s", BOUNDARY_CONVS)
+def test_conv_family_against_cpu_fp32_oracle(raw, n, H, W, Ci, Co, KH, KW, s):
+    """Boundary-heavy shapes (small / odd maps where most outputs touch the TF-SAME padding, asymmetric for stride 2)
+    against torch's CPU fp32 convolution -- not cuDNN on the same GPU -- with a per-element mixed bound
+    |err| <= atol + rtol |ref| (bf16 inputs, fp32 accumulation, bf16 output rounding)."""
+    from distributed_tensorflow_framework_b200.ops.raw import same_pad
+    g = torch.Generator().manual_seed(H * 1000 + W * 10 + KH)
+    x = torch.randn(n, H, W, Ci, generator=g).to(torch.bfloat16)
+    w = (torch.randn(KH, KW, Ci, Co, generator=g) * 0.1).to(torch.bfloat16)
+    OH, pt = same_pad(H, KH, s)
+    OW, pl = same_pad(W, KW, s)
+    pb = max((OH - 1) * s + KH - H, 0) - pt
+    pr = max((OW - 1) * s + KW - W, 0) - pl
+    xc = F.pad(x.float().permute(0, 3, 1, 2), (pl, pr, pt, pb)).requires_grad_(True)
+    wc = w.float().permute(3, 2, 0, 1).clone().requires_grad_(True)
+    ref = F.conv2d(xc, wc, stride=s)
+    dy = torch.randn(n, OH, OW, Co, generator=g).to(torch.bfloat16)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    ref_y = ref.detach().permute(0, 2, 3, 1)
+    ref_dx = xc.grad[:, :, pt:pt + H, pl:pl + W].permute(0, 2, 3, 1)
+    ref_dw = wc.grad.permute(2, 3, 1, 0).reshape(KH * KW * Ci, Co)
+
+    def bound(got, want, atol, rtol):
+        got, want = got.float().cpu(), want.float()
+        bad = (got - want).abs() > atol + rtol * want.abs()
+        assert not bool(bad.any()), (int(bad.sum()), float((got - want).abs().max()), float(want.abs().max()))
+
+    xg, wg, dyg = x.cuda(), w.cuda(), dy.cuda()
+    w2 = wg.reshape(KH * KW * Ci, Co)
+    wt = wg.permute(0, 1, 3, 2).contiguous().reshape(KH * KW * Co, Ci)
+    scale = float(ref_y.abs().max())
+    bound(raw.conv_fprop(xg, w2, None, KH, KW, s), ref_y, 1e-2 * scale, 1e-2)
+    bound(raw.conv_dgrad(dyg, wt, (H, W), KH, KW, s), ref_dx, 1e-2 * float(ref_dx.abs().max()), 1e-2)
+    dw = torch.zeros(KH * KW * Ci, Co, device="cuda")
+    raw.conv_wgrad(xg, dyg, KH, KW, s, out=dw)
+    bound(dw, ref_dw, 2e-3 * float(ref_dw.abs().max()), 2e-3)
