@@ -58,6 +58,10 @@ def build_operator(main, model_module=None, loss_module=None, input_module=None,
     sample_number = g(main, "sample_number")
     data_dir = g(main, "data_dir")
     model_dir = g(main, "model_dir")
+    if os.environ.get("DTF_SPAWNED") and os.environ.get("DTF_SPAWN_MODEL_DIR"):
+        # a spawned tower re-executes the user's script: all towers must share the directory the parent resolved
+        # (the script may have created a fresh temporary one per process)
+        model_dir = os.environ["DTF_SPAWN_MODEL_DIR"]
     if not os.path.exists(model_dir):
         raise ValueError("Path to save or restore model doesn't exist")
     loss = annotations.get_instance_from_annotation(main, "loss", loss_module or Loss)
@@ -137,7 +141,7 @@ def build_operator(main, model_module=None, loss_module=None, input_module=None,
     return operator
 
 
-def _spawn_towers(n):
+def _spawn_towers(n, main=None):
     """`@gpu_num(N)` without a launcher: the reference drives N GPUs from one process
     (`for i in range(num_devices): with tf.device('/gpu:%d')`, distribute_train.py:116-139). Here every tower is its
     own process on its own GPU (one rank per GPU over the peer-memory collectives): re-run this script N times with
@@ -151,6 +155,8 @@ def _spawn_towers(n):
     for r in range(n):
         env = dict(os.environ, DTF_SPAWNED="1", RANK=str(r), LOCAL_RANK=str(r), WORLD_SIZE=str(n),
                    LOCAL_WORLD_SIZE=str(n), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        if main is not None and getattr(main, "model_dir", None):
+            env["DTF_SPAWN_MODEL_DIR"] = str(main.model_dir)
         procs.append(subprocess.Popen([sys.executable] + sys.argv, env=env))
     rc = 0
     for p in procs:
@@ -176,7 +182,7 @@ def _should_spawn(main):
 def run_main(main, **kwargs):
     n = _should_spawn(main)
     if n:
-        rc = _spawn_towers(n)
+        rc = _spawn_towers(n, main)
         if rc:
             raise RuntimeError("a tower process failed (exit code %d)" % rc)
         return None
