@@ -130,7 +130,11 @@ def _conv_impl(x, w, b, stride, relu, fork=False, emit_stats=False):
         assert sh == sw, "anisotropic strides are not supported on the CUDA path"
         x = _prep_cuda_input(x, w.store_shape[2])
         if fork or emit_stats:
-            y, x_fwd, part = Fn.conv2d(x, w, b, sh, relu, fork=fork, emit_stats=emit_stats and _training)
+            want_stats = emit_stats and _training  # inference uses the running statistics: nothing to emit
+            if fork or want_stats:
+                y, x_fwd, part = Fn.conv2d(x, w, b, sh, relu, fork=fork, emit_stats=want_stats)
+            else:
+                y, x_fwd, part = Fn.conv2d(x, w, b, sh, relu), None, None
             if w.store_shape[3] != w.shape[3]:
                 y, part = y[..., :w.shape[3]], None
             return y, x_fwd, part

@@ -72,6 +72,23 @@ def test_resnet_trains(name):
     losses = [float(tr.step((x, y))) for _ in range(25)]
     assert all(l == l for l in losses)
     assert min(losses[-5:]) < 0.7 * losses[0], losses
+    # inference mode (running statistics; the convolutions that feed statistics to their batch norm in training emit
+    # none here) against the CPU path with the same variables
+    from distributed_tensorflow_framework_b200.engine import layers, variables as V
+    cpu = _make(Small, "cpu")
+    cpu.build(x, y)
+    cpu.store.load_state_dict(tr.store.state_dict())
+    layers.set_training(False)
+    try:
+        with torch.no_grad():
+            with V.using_store(tr.store):
+                lg = tr.net.process(x.cuda()).float().cpu()
+            with V.using_store(cpu.store):
+                lc = cpu.net.process(x).float()
+    finally:
+        layers.set_training(True)
+    assert lg.shape == lc.shape == (8, 16) and bool(torch.isfinite(lg).all())
+    assert (lg - lc).abs().max() < 0.08 * lc.abs().max() + 0.05, ((lg - lc).abs().max(), lc.abs().max())
 
 
 def test_dehaze_fcn_trains_and_matches_cpu_forward():
