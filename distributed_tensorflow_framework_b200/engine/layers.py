@@ -123,6 +123,23 @@ def _prep_cuda_input(x, cin_store):
     return x.contiguous()
 
 
+def _chan_pad(x):
+    """CUDA activations for the memory-bound kernels: bf16, contiguous, channel count a multiple of 8 (16-byte
+    vectors). Layers whose channel count is not get zero channels appended here and cut off again after the op
+    (a slow path for unusual widths; zeros are neutral for max / average pooling windows taken per channel, LRN sums,
+    batch statistics of their own column, ReLU and add). Returns (tensor, logical channel count)."""
+    C = x.shape[-1]
+    if x.dtype != torch.bfloat16:
+        x = x.to(torch.bfloat16)
+    if C % 8:
+        x = F.pad(x, (0, _pad8(C) - C))
+    return x.contiguous(), C
+
+
+def _chan_cut(y, C):
+    return y if y.shape[-1] == C else y[..., :C]
+
+
 def _conv_impl(x, w, b, stride, relu, fork=False, emit_stats=False):
     sh, sw = _stride_hw(stride)
     KH, KW = w.shape[0], w.shape[1]
@@ -194,7 +211,8 @@ def conv_nonacti_eval(layer_name, x, in_channels, out_channels, kernel_size=[3, 
 def acti_layer(x):
     """ReLU -- distribute_tools.py:123-128."""
     if x.is_cuda:
-        return Fn.relu(x.contiguous())
+        xp, C = _chan_pad(x)
+        return _chan_cut(Fn.relu(xp), C)
     return _q(F.relu(x))
 
 
@@ -206,12 +224,15 @@ def deconv(layer_name, x, in_channels, out_channels, output_shape=[32, 224, 224,
     OUTPUT channels of the transposed conv and dim 3 must equal x's channel count."""
     sh, sw = _stride_hw(stride)
     with variable_scope(layer_name):
+        # CUDA: both channel counts are stored padded to multiples of 8 (zero filters), like the conv layers
+        store = [kernel_size[0], kernel_size[1], _pad8(in_channels), _pad8(out_channels)] if x.is_cuda else None
         w = _get("weights", [kernel_size[0], kernel_size[1], in_channels, out_channels], XavierInitializer(),
-                 kind="deconv_w")
+                 kind="deconv_w", store_shape=store)
         out_hw = (int(output_shape[1]), int(output_shape[2]))
         if x.is_cuda:
             assert sh == sw
-            return Fn.conv2d_transpose(_prep_cuda_input(x, out_channels), w, out_hw, sh)
+            y = Fn.conv2d_transpose(_prep_cuda_input(x, w.store_shape[3]), w, out_hw, sh)
+            return y if w.store_shape[2] == in_channels else y[..., :in_channels]
         # oracle: adjoint of the SAME conv (out_hw -> x spatial). conv_transpose2d without padding yields the
         # gradient w.r.t. the zero-padded input; cropping by TF's asymmetric (top/left) padding gives the result.
         from ..ops.raw import same_pad
@@ -235,7 +256,8 @@ def pool(layer_name, x, kernel=[1, 2, 2, 1], stride=[1, 2, 2, 1], is_max_pool=Tr
     k = (int(kernel[1]), int(kernel[2])) if len(kernel) == 4 else tuple(kernel)
     s = _stride_hw(stride)
     if x.is_cuda:
-        return Fn.pool2d(x.contiguous(), k, s, is_max_pool)
+        xp, C = _chan_pad(x)
+        return _chan_cut(Fn.pool2d(xp, k, s, is_max_pool), C)
     xn = x.float().permute(0, 3, 1, 2)
     pad = _same_pad_nchw(xn, k, s)
     if is_max_pool:
@@ -252,49 +274,64 @@ def batch_norm(x):
     averages -- distribute_tools.py:168-180."""
     epsilon = 1e-3
     if x.is_cuda:
-        return Fn.batch_norm_train(x.contiguous(), rows=x.shape[0], eps=epsilon)
+        xp, C = _chan_pad(x)
+        return _chan_cut(Fn.batch_norm_train(xp, rows=x.shape[0], eps=epsilon), C)
     xf = x.float()
     mean = xf.mean(0, keepdim=True)
     var = xf.var(0, unbiased=False, keepdim=True)
     return _q((xf - mean) * torch.rsqrt(var + epsilon))
 
 
-def _bn_vars(layer_name, C):
+def _bn_vars(layer_name, C, cuda=False):
+    # on CUDA a channel count that is not a multiple of 8 is stored padded (the kernels work on 8-channel vectors);
+    # checkpoints keep the logical shape
+    ss = [_pad8(C)] if cuda and C % 8 else None
     with variable_scope(layer_name):
-        beta = _get("beta", [C], ConstantInitializer(0.0), kind="bias")
-        gamma = _get("gamma", [C], ConstantInitializer(1.0), kind="bias")
-        rm = _get("moving_mean", [C], ConstantInitializer(0.0), trainable=False)
-        rv = _get("moving_variance", [C], ConstantInitializer(1.0), trainable=False)
+        beta = _get("beta", [C], ConstantInitializer(0.0), kind="bias", store_shape=ss)
+        gamma = _get("gamma", [C], ConstantInitializer(1.0), kind="bias", store_shape=ss)
+        rm = _get("moving_mean", [C], ConstantInitializer(0.0), trainable=False, store_shape=ss)
+        rv = _get("moving_variance", [C], ConstantInitializer(1.0), trainable=False, store_shape=ss)
     return gamma, beta, rm, rv
 
 
 def batch_norm_channel(layer_name, x, relu=False, residual=None, eps=1e-3, momentum=0.1, stats_part=None,
-                       residual_bn=None, residual_part=None):
+                       residual_bn=None, residual_part=None, _logical_c=None):
     """Standard per-channel batch norm with affine parameters and running statistics (needed by the ResNet
     configs of BASELINE.json; optionally fused with a residual add and ReLU). `stats_part`: per-tile statistics of x
     from the convolution that produced it (conv_nonacti(..., emit_stats=True)); saves the statistics pass.
     `residual_bn` (a layer name): the residual is the RAW output of a projection shortcut's convolution and goes
     through its own batch norm (variables under that name) inside the same pass -- y = act(bn(x) + bn_r(residual));
     `residual_part`: that convolution's epilogue statistics."""
+    C_log = _logical_c or x.shape[-1]
+    if x.is_cuda and x.shape[-1] % 8:
+        # unusual width: zero channels appended for the 8-channel vector kernels, cut off again below
+        x = _chan_pad(x)[0]
+        residual = _chan_pad(residual)[0] if residual is not None else None
+        stats_part = residual_part = None
     C = x.shape[-1]
-    gamma, beta, rm, rv = _bn_vars(layer_name, C)
+    gamma, beta, rm, rv = _bn_vars(layer_name, C_log, x.is_cuda)
     rows = x.numel() // C
     if residual_bn is not None:
         assert residual is not None
-        gamma_r, beta_r, rm_r, rv_r = _bn_vars(residual_bn, C)
-        if x.is_cuda and _training and C % 8 == 0:
-            return Fn.batch_norm_dual_train(x.contiguous(), residual.contiguous(), rows, gamma, beta, rm.master,
-                                            rv.master, gamma_r, beta_r, rm_r.master, rv_r.master, eps, momentum, relu,
-                                            stats_part, residual_part)
+        gamma_r, beta_r, rm_r, rv_r = _bn_vars(residual_bn, C_log, x.is_cuda)
+        if x.is_cuda and _training:
+            y = Fn.batch_norm_dual_train(x.contiguous(), residual.contiguous(), rows, gamma, beta, rm.master,
+                                         rv.master, gamma_r, beta_r, rm_r.master, rv_r.master, eps, momentum, relu,
+                                         stats_part, residual_part)
+            return _chan_cut(y, C_log)
         # eval / CPU: normalise the shortcut on its own, then the plain fused path
         residual = batch_norm_channel(residual_bn, residual, relu=False, eps=eps, momentum=momentum,
-                                      stats_part=residual_part)
+                                      stats_part=residual_part, _logical_c=C_log)
+        if x.is_cuda and residual.shape[-1] != C:
+            residual = _chan_pad(residual)[0]
     if x.is_cuda:
         x = x.contiguous()
         if _training:
-            return Fn.batch_norm_train(x, rows, gamma, beta, rm.master, rv.master, eps, momentum, residual, relu,
-                                       part=stats_part)
-        return Fn.batch_norm_eval(x, rows, gamma, beta, rm.master, rv.master, eps, residual, relu)
+            y = Fn.batch_norm_train(x, rows, gamma, beta, rm.master, rv.master, eps, momentum, residual, relu,
+                                    part=stats_part)
+        else:
+            y = Fn.batch_norm_eval(x, rows, gamma, beta, rm.master, rv.master, eps, residual, relu)
+        return _chan_cut(y, C_log)
     xf = x.float().reshape(rows, C)
     y = F.batch_norm(xf, rm.master.detach(), rv.master.detach(), gamma.master, beta.master, _training, momentum, eps)
     y = y.reshape(x.shape)
@@ -312,7 +349,7 @@ def batch_norm_relu_pool(bn_name, pool_name, x, kernel=[1, 3, 3, 1], stride=[1, 
     k = (int(kernel[1]), int(kernel[2])) if len(kernel) == 4 else tuple(kernel)
     s = _stride_hw(stride)
     if x.is_cuda and _training and C % 8 == 0 and k in ((3, 3), (2, 2)):
-        gamma, beta, rm, rv = _bn_vars(bn_name, C)
+        gamma, beta, rm, rv = _bn_vars(bn_name, C, True)
         return Fn.batch_norm_relu_pool_train(x, x.numel() // C, gamma, beta, rm.master, rv.master, k, s, eps, momentum,
                                              stats_part)
     y = batch_norm_channel(bn_name, x, relu=True, eps=eps, momentum=momentum, stats_part=stats_part)
@@ -326,7 +363,8 @@ def norm(name, x, lsize=4):
         return x
     alpha, beta, bias = 0.001 / 9.0, 0.75, 1.0
     if x.is_cuda:
-        return Fn.lrn(x.contiguous(), lsize, bias, alpha, beta)
+        xp, C = _chan_pad(x)
+        return _chan_cut(Fn.lrn(xp, lsize, bias, alpha, beta), C)
     n = 2 * lsize + 1
     return _q(F.local_response_norm(x.float().permute(0, 3, 1, 2), n, alpha=alpha * n, beta=beta,
                                     k=bias).permute(0, 2, 3, 1))
@@ -363,13 +401,15 @@ def global_avg_pool(x):
     """[N,H,W,C] -> [N,C] mean over the spatial dims (ResNet head)."""
     H, W = x.shape[1], x.shape[2]
     if x.is_cuda:
-        return Fn.pool2d(x.contiguous(), (H, W), (H, W), False).reshape(x.shape[0], x.shape[3])
+        xp, C = _chan_pad(x)
+        return _chan_cut(Fn.pool2d(xp, (H, W), (H, W), False).reshape(x.shape[0], xp.shape[3]), C)
     return _q(x.float().mean(dim=(1, 2)))
 
 
 def add_relu(a, b, relu=True):
     if a.is_cuda:
-        return Fn.add(a.contiguous(), b.contiguous(), relu)
+        ap, C = _chan_pad(a)
+        return _chan_cut(Fn.add(ap, _chan_pad(b)[0], relu), C)
     y = a.float() + b.float()
     return _q(F.relu(y) if relu else y)
 

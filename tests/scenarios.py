@@ -184,3 +184,121 @@ def adam_with_decaying_learning_rate(tmp_path, gpu):
     again = LearningRate(0.01, os.path.join(md, "lr.json"), decay_factor=0.1)
     assert abs(again.learning_rate - 0.001) < 1e-9
     return seen
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The whole layer library on awkward shapes: rectangular images, channel counts that are not multiples of 8, odd
+# spatial sizes, 1/3/5/7 kernels, strides 1 and 2, literal batch norm, LRN, transposed convolutions.
+
+class KitchenSinkClassifier(dtf.Model):
+    def inference(self, x, *a, **k):
+        T = dtf.tools
+        x = T.conv("c1", x, 3, 20, kernel_size=[5, 5])                                  # 24x40x20
+        x = T.pool("p1", x, kernel=[1, 3, 3, 1], stride=[1, 2, 2, 1])                   # 12x20
+        x = T.norm("n1", x)
+        x = T.conv_nonacti("c2", x, 20, 36, kernel_size=[3, 3], stride=[1, 2, 2, 1])    # 6x10x36
+        x = T.acti_layer(x)
+        x = T.batch_norm(x)
+        x = T.conv_nonacti("c3", x, 36, 28, kernel_size=[1, 1])
+        x = layers.batch_norm_channel("bn3", x, relu=True)                              # per-channel, 28 channels
+        x = T.conv("c4", x, 28, 24, kernel_size=[7, 7])
+        x = T.pool("p2", x, is_max_pool=False)                                          # 3x5x24
+        x = T.FC_layer("f1", x, 50)
+        return T.fc_nonacti("logits", x, 7)
+
+
+class KitchenSinkImage(dtf.Model):
+    def inference(self, x, *a, **k):
+        T = dtf.tools
+        n, h, w = x.shape[0], x.shape[1], x.shape[2]
+        e = T.conv("c1", x, 3, 12, kernel_size=[3, 3])                                  # 21x27x12
+        d = T.conv("c2", e, 12, 40, kernel_size=[3, 3], stride=[1, 2, 2, 1])            # 11x14x40
+        d = T.conv("c3", d, 40, 44, kernel_size=[3, 3])
+        u = T.deconv("u1", d, 12, 44, output_shape=[n, h, w, 12], stride=[1, 2, 2, 1])  # back to 21x27x12
+        u = T.acti_layer(u)
+        u = T.add_relu(u, e, relu=False)
+        return T.conv_nonacti("out", u, 12, 3, kernel_size=[1, 1])
+
+
+def _one_step_parity(model_cls, loss, x, y, cos_min=0.97, ratio_tol=0.15):
+    """One SGD step on the CPU oracle and on CUDA from identical variables: loss, forward output and the update of every
+    variable (direction and size) must agree within bf16 noise."""
+    cpu = dtf.Trainer(dtf.Net(model_cls()), loss, dtf.GradientDescentOptimizer(0.05), device="cpu")
+    gpu = dtf.Trainer(dtf.Net(model_cls()), loss, dtf.GradientDescentOptimizer(0.05), device="cuda:0")
+    cpu.build(x, y)
+    gpu.build(x, y)
+    gpu.store.load_state_dict(cpu.store.state_dict())
+    gpu.store.shadow_arena.copy_(gpu.store.master_arena)
+    gpu.store.refresh_transposed_shadows()
+    fc, fg = cpu.forward(x).float(), gpu.forward(x).float().cpu()
+    assert fc.shape == fg.shape
+    assert (fc - fg).abs().max() < 0.04 * fc.abs().max() + 0.02, (float((fc - fg).abs().max()), float(fc.abs().max()))
+    before = {k: v.clone() for k, v in cpu.store.state_dict().items()}
+    lc, lg = float(cpu.step((x, y))), float(gpu.step((x, y)))
+    assert abs(lc - lg) < 0.03 * max(1.0, abs(lc)), (lc, lg)
+    after_c, after_g = cpu.store.state_dict(), gpu.store.state_dict()
+    checked = 0
+    # a bias in front of a batch norm has a zero gradient up to rounding: updates far below the largest one are only
+    # required to be small on both devices
+    tiny = 1e-3 * max(float((after_c[k] - before[k]).norm()) for k in before)
+    for k in before:
+        dc = (after_c[k] - before[k]).flatten().double()
+        dg = (after_g[k].cpu() - before[k]).flatten().double()
+        if dc.norm() < tiny:
+            assert dg.norm() < 20 * tiny + 1e-6, (k, float(dc.norm()), float(dg.norm()))
+            continue
+        cos = float(torch.dot(dc, dg) / (dc.norm() * dg.norm() + 1e-30))
+        ratio = float(dg.norm() / dc.norm())
+        assert cos > cos_min and abs(ratio - 1.0) < ratio_tol, (k, cos, ratio)
+        checked += 1
+    return checked
+
+
+def kitchen_sink_parity():
+    torch.manual_seed(11)
+    # (the first layers sit behind two batch norms over a batch of 6, an LRN and a max pool: bf16 noise is amplified
+    # there, so this integration check is looser than the per-layer one below)
+    n = _one_step_parity(KitchenSinkClassifier, dtf.SoftmaxCrossEntropyLoss(), torch.rand(6, 24, 40, 3),
+                         torch.randint(0, 7, (6,)), cos_min=0.95, ratio_tol=0.3)
+    assert n >= 14
+    n = _one_step_parity(KitchenSinkImage, dtf.MSELoss(), torch.rand(3, 21, 27, 3), torch.rand(3, 21, 27, 3))
+    assert n >= 8
+
+
+# Every layer on its own behind a 1x1 convolution that produces C channels: forward, loss and the update of that
+# convolution (i.e. the layer's backward) against the CPU path.
+_T = dtf.tools
+LAYER_CASES = {
+    "pool_max_3x3s2": lambda x: _T.pool("p", x, kernel=[1, 3, 3, 1], stride=[1, 2, 2, 1]),
+    "pool_max_2x2": lambda x: _T.pool("p", x),
+    "pool_avg_2x2": lambda x: _T.pool("p", x, is_max_pool=False),
+    "lrn": lambda x: _T.norm("n", x),
+    "batch_norm_literal": lambda x: _T.batch_norm(x),
+    "acti": lambda x: _T.acti_layer(x - 0.5),
+    "add_relu": lambda x: _T.add_relu(x - 0.5, 0.5 * x, relu=True),
+    "gap": lambda x: _T.global_avg_pool(x),
+    "bn_channel": lambda x: layers.batch_norm_channel("bn", x, relu=True),
+    "bn_channel_res": lambda x: layers.batch_norm_channel("bn", x, relu=True, residual=0.5 - x),
+    "conv3x3": lambda x: _T.conv("c", x, x.shape[-1], 12),
+    "conv5x5s2_nonacti": lambda x: _T.conv_nonacti("c", x, x.shape[-1], 20, kernel_size=[5, 5], stride=[1, 2, 2, 1]),
+    "conv1x1": lambda x: _T.conv("c", x, x.shape[-1], 36, kernel_size=[1, 1]),
+    "deconv_s2": lambda x: _T.deconv("d", x, 12, x.shape[-1], stride=[1, 2, 2, 1],
+                                     output_shape=[x.shape[0], 2 * x.shape[1], 2 * x.shape[2], 12]),
+    "fc": lambda x: _T.FC_layer("f", x, 30),
+    "fc_nonacti": lambda x: _T.fc_nonacti("f", x, 7),
+}
+
+
+def layer_case_parity(name, n, h, w, C):
+    fn = LAYER_CASES[name]
+
+    class M(dtf.Model):
+        def inference(self, x, *a, **k):
+            return fn(_T.conv_nonacti("pre", x, 3, C, kernel_size=[1, 1]))
+
+    torch.manual_seed(0)
+    x = torch.rand(n, h, w, 3)
+    probe = dtf.Trainer(dtf.Net(M()), dtf.MSELoss(), dtf.GradientDescentOptimizer(0.05), device="cpu")
+    probe.build(x, None)
+    shape = probe.forward(x).shape
+    return _one_step_parity(M, dtf.MSELoss(), x, torch.rand(*shape)), tuple(shape)

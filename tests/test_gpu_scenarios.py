@@ -49,3 +49,18 @@ def test_estimator_example_on_cuda(tmp_path):
     out = _run(["examples/estimator.py", "--model=ResNet18", "--image_size=64", "--steps=30", "--lr=0.01",
                 "--model_dir=%s" % tmp_path])
     assert "trained 30 steps" in out and "resumed to step 60" in out and "predict: [" in out
+
+
+def test_layer_library_on_awkward_shapes_matches_the_cpu_oracle():
+    scenarios.kitchen_sink_parity()
+
+
+@pytest.mark.parametrize("geom", [(4, 9, 13, 20), (3, 8, 8, 3), (2, 7, 7, 36)])
+def test_every_layer_with_channel_counts_that_are_not_multiples_of_8(geom):
+    failures = []
+    for name in scenarios.LAYER_CASES:
+        try:
+            scenarios.layer_case_parity(name, *geom)
+        except Exception as e:  # collect all of them: one line per failing layer
+            failures.append("%s: %s: %s" % (name, type(e).__name__, str(e)[:160]))
+    assert not failures, "\n".join(failures)
