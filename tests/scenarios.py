@@ -302,3 +302,37 @@ def layer_case_parity(name, n, h, w, C):
     probe.build(x, None)
     shape = probe.forward(x).shape
     return _one_step_parity(M, dtf.MSELoss(), x, torch.rand(*shape)), tuple(shape)
+
+
+def in_process_towers_equal_one_big_batch(device, use_graph=False):
+    """`gpu_num = 2` towers inside one process (distribute_train.py:116-139 with fewer devices than towers): the mean
+    of the tower gradients is the gradient of the concatenated batch for a net without batch statistics, so two towers
+    of 8 images must move the variables like one tower of 16."""
+    torch.manual_seed(5)
+    xs = [torch.rand(8, 32, 32, 3) for _ in range(2)]
+    ys = [torch.randint(0, 10, (8,)) for _ in range(2)]
+    kw = {"use_cuda_graph": True} if use_graph else {}
+    one = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.MomentumOptimizer(0.05, 0.9),
+                      device=device, **kw)
+    two = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.MomentumOptimizer(0.05, 0.9),
+                      device=device, gpu_num=2, **kw)
+    one.build(xs[0], ys[0])
+    two.build(xs[0], ys[0])
+    two.store.load_state_dict(one.store.state_dict())
+    if str(device) != "cpu":
+        two.store.shadow_arena.copy_(two.store.master_arena)
+        two.store.refresh_transposed_shadows()
+    before = {k: v.clone().cpu() for k, v in one.store.state_dict().items()}
+    for _ in range(3):  # three steps: momentum slots take part, graph replay (if any) is exercised
+        l1 = float(one.step((torch.cat(xs), torch.cat(ys))))
+        l2 = float(two.step([(xs[0], ys[0]), (xs[1], ys[1])]))
+        assert abs(l1 - l2) < 0.02 * max(1.0, abs(l1)), (l1, l2)
+    a1, a2 = one.store.state_dict(), two.store.state_dict()
+    for k in before:
+        d1 = (a1[k].cpu() - before[k]).flatten().double()
+        d2 = (a2[k].cpu() - before[k]).flatten().double()
+        if d1.norm() < 1e-9:
+            continue
+        cos = float(torch.dot(d1, d2) / (d1.norm() * d2.norm() + 1e-30))
+        assert cos > 0.98 and abs(float(d2.norm() / d1.norm()) - 1.0) < 0.1, (k, cos, float(d2.norm() / d1.norm()))
+    assert one.store.global_step == two.store.global_step == 3

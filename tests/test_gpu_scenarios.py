@@ -64,3 +64,8 @@ def test_every_layer_with_channel_counts_that_are_not_multiples_of_8(geom):
         except Exception as e:  # collect all of them: one line per failing layer
             failures.append("%s: %s: %s" % (name, type(e).__name__, str(e)[:160]))
     assert not failures, "\n".join(failures)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_two_in_process_towers_equal_one_tower_on_the_concatenated_batch(graph):
+    scenarios.in_process_towers_equal_one_big_batch("cuda:0", use_graph=graph)

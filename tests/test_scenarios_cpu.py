@@ -12,3 +12,7 @@ def test_placeholder_and_datapath_loaders_learn(tmp_path):
 
 def test_adam_follows_a_decaying_learning_rate_handler(tmp_path):
     scenarios.adam_with_decaying_learning_rate(tmp_path, gpu=False)
+
+
+def test_two_in_process_towers_equal_one_tower_on_the_concatenated_batch():
+    scenarios.in_process_towers_equal_one_big_batch("cpu")
