@@ -336,3 +336,65 @@ def in_process_towers_equal_one_big_batch(device, use_graph=False):
         cos = float(torch.dot(d1, d2) / (d1.norm() * d2.norm() + 1e-30))
         assert cos > 0.98 and abs(float(d2.norm() / d1.norm()) - 1.0) < 0.1, (k, cos, float(d2.norm() / d1.norm()))
     assert one.store.global_step == two.store.global_step == 3
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# User code written with plain torch ops between the library's layers, a user-defined loss and advice hooks.
+
+class UserOpsModel(dtf.Model):
+    """Two branches joined with torch.cat (a skip connection), arithmetic and a sigmoid written in torch."""
+
+    def inference(self, x, *a, **k):
+        T = dtf.tools
+        s = T.conv("stem", x, 3, 16)
+        a1 = T.conv("a1", s, 16, 16)
+        b1 = T.pool("b_pool", s)
+        b1 = T.deconv("b_up", T.conv("b1", b1, 16, 24), 8, 24, output_shape=[s.shape[0], s.shape[1], s.shape[2], 8],
+                      stride=[1, 2, 2, 1])
+        j = torch.cat([a1, b1.to(a1.dtype) * 0.5], dim=-1)                       # 24 channels
+        y = T.conv_nonacti("head", j, 24, 3, kernel_size=[1, 1])
+        return torch.sigmoid(y.float())
+
+
+class L1PlusTVLoss(dtf.Loss):
+    """A user loss in torch: mean absolute error plus a small total-variation term on the prediction."""
+
+    def loss(self, predict, ground_truth):
+        p = predict.float()
+        l1 = (p - ground_truth.float()).abs().mean()
+        tv = (p[:, 1:] - p[:, :-1]).abs().mean() + (p[:, :, 1:] - p[:, :, :-1]).abs().mean()
+        return l1 + 0.1 * tv
+
+
+def _centre(raw, gt, args, kwargs):
+    return raw * 2.0 - 1.0, gt
+
+
+def user_torch_ops_loss_and_advice_parity():
+    torch.manual_seed(7)
+    x, t = torch.rand(4, 16, 20, 3), torch.rand(4, 16, 20, 3)
+    mk = lambda dev: dtf.Trainer(dtf.Net(UserOpsModel()), L1PlusTVLoss(), dtf.GradientDescentOptimizer(1.0),  # noqa
+                                 device=dev, pre_process_fn=_centre)
+    cpu, gpu = mk("cpu"), mk("cuda:0")
+    cpu.build(x, t)
+    gpu.build(x, t)
+    gpu.store.load_state_dict(cpu.store.state_dict())
+    gpu.store.shadow_arena.copy_(gpu.store.master_arena)
+    gpu.store.refresh_transposed_shadows()
+    before = {k: v.clone() for k, v in cpu.store.state_dict().items()}
+    lc, lg = float(cpu.step((x, t))), float(gpu.step((x, t)))
+    assert abs(lc - lg) < 0.02 * max(1.0, abs(lc)), (lc, lg)
+    ac, ag = cpu.store.state_dict(), gpu.store.state_dict()
+    tiny = 1e-3 * max(float((ac[k] - before[k]).norm()) for k in before)
+    n = 0
+    for k in before:
+        dc = (ac[k] - before[k]).flatten().double()
+        dg = (ag[k].cpu() - before[k]).flatten().double()
+        if dc.norm() < tiny:
+            continue
+        cos = float(torch.dot(dc, dg) / (dc.norm() * dg.norm() + 1e-30))
+        assert cos > 0.95 and abs(float(dg.norm() / dc.norm()) - 1.0) < 0.25, (k, cos, float(dg.norm() / dc.norm()))
+        n += 1
+    assert n >= 8, n
+    losses = [float(gpu.step((x, t))) for _ in range(20)]
+    assert losses[-1] < lg, (lg, losses)

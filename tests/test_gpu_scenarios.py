@@ -69,3 +69,7 @@ def test_every_layer_with_channel_counts_that_are_not_multiples_of_8(geom):
 @pytest.mark.parametrize("graph", [False, True])
 def test_two_in_process_towers_equal_one_tower_on_the_concatenated_batch(graph):
     scenarios.in_process_towers_equal_one_big_batch("cuda:0", use_graph=graph)
+
+
+def test_user_torch_ops_custom_loss_and_advice_match_the_cpu_path():
+    scenarios.user_torch_ops_loss_and_advice_parity()
