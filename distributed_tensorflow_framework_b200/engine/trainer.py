@@ -199,6 +199,12 @@ class Trainer(object):
     def _graph_step(self, batches):
         if self._graph is None:
             self._capture(batches)
+        if len(batches) != len(self._static_in) or any(
+                r.shape != sr.shape or g.shape != sg.shape or r.dtype != sr.dtype or g.dtype != sg.dtype
+                for (sr, sg), (r, g) in zip(self._static_in, batches)):
+            # a batch of another shape (the smaller last batch of an epoch, say) cannot be replayed: this one step
+            # runs eagerly; the device-side step counter / learning rate are shared, so replays simply continue after
+            return self._step_body(batches)
         for (sr, sg), (r, g) in zip(self._static_in, batches):
             if r.data_ptr() != sr.data_ptr():
                 sr.copy_(r, non_blocking=True)

@@ -398,3 +398,28 @@ def user_torch_ops_loss_and_advice_parity():
     assert n >= 8, n
     losses = [float(gpu.step((x, t))) for _ in range(20)]
     assert losses[-1] < lg, (lg, losses)
+
+
+def graph_replay_with_a_smaller_batch_in_between(opt_factory):
+    """CUDA-graph training where one batch has another size (the last batch of an epoch): that step runs eagerly,
+    replays continue afterwards, and the result equals eager training on the same sequence."""
+    torch.manual_seed(9)
+    big = [(torch.rand(16, 32, 32, 3), torch.randint(0, 10, (16,))) for _ in range(3)]
+    small = (torch.rand(6, 32, 32, 3), torch.randint(0, 10, (6,)))
+    seq = [big[0], big[1], small, big[2], big[0], small, big[1]]
+    mk = lambda g: dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), opt_factory(),  # noqa
+                               device="cuda:0", use_cuda_graph=g)
+    eager, graph = mk(False), mk(True)
+    eager.build(*big[0])
+    graph.build(*big[0])
+    graph.store.load_state_dict(eager.store.state_dict())
+    graph.store.shadow_arena.copy_(graph.store.master_arena)
+    graph.store.refresh_transposed_shadows()
+    for b in seq:
+        le, lg = float(eager.step(b)), float(graph.step(b))
+        assert abs(le - lg) < 5e-3 * max(1.0, abs(le)), (le, lg)
+    assert graph._graph is not None and eager.store.global_step == graph.store.global_step == len(seq)
+    se, sg = eager.store.state_dict(), graph.store.state_dict()
+    for k in se:
+        d = float((se[k] - sg[k]).abs().max())
+        assert d <= 2e-3 * float(se[k].abs().max()) + 1e-5, (k, d)

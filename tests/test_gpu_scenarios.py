@@ -73,3 +73,10 @@ def test_two_in_process_towers_equal_one_tower_on_the_concatenated_batch(graph):
 
 def test_user_torch_ops_custom_loss_and_advice_match_the_cpu_path():
     scenarios.user_torch_ops_loss_and_advice_parity()
+
+
+@pytest.mark.parametrize("opt", ["momentum", "adam"])
+def test_graph_replay_survives_a_batch_of_another_size(opt):
+    import distributed_tensorflow_framework_b200 as dtf
+    scenarios.graph_replay_with_a_smaller_batch_in_between(
+        (lambda: dtf.MomentumOptimizer(0.02, 0.9)) if opt == "momentum" else (lambda: dtf.AdamOptimizer(1e-3)))
