@@ -357,7 +357,12 @@ class VariableStore(object):
                 if v.name not in state:
                     missing.append(v.name)
                     continue
-                src = torch.as_tensor(state[v.name]).to(torch.float32).reshape(v.shape)
+                src = torch.as_tensor(state[v.name])
+                if [d for d in src.shape if d != 1] != [d for d in v.shape if d != 1]:
+                    # (TF: "Assign requires shapes of both tensors to match")
+                    raise ValueError("variable %r: the checkpoint holds shape %s, the model declares %s"
+                                     % (v.name, tuple(src.shape), tuple(v.shape)))
+                src = src.to(torch.float32).reshape(v.shape)
                 v.logical(v.master).copy_(src.to(v.master.device))
                 if v.shadow is not None:
                     v.shadow.data.copy_(v.master)

@@ -16,3 +16,26 @@ def test_adam_follows_a_decaying_learning_rate_handler(tmp_path):
 
 def test_two_in_process_towers_equal_one_tower_on_the_concatenated_batch():
     scenarios.in_process_towers_equal_one_big_batch("cpu")
+
+
+def test_restoring_into_a_model_of_another_shape_names_the_variable(tmp_path):
+    import pytest
+    import torch
+    import distributed_tensorflow_framework_b200 as dtf
+    from distributed_tensorflow_framework_b200 import models
+
+    class TwentyClasses(models.Cifar10CNN):
+        num_classes = 20
+
+    x, y = torch.rand(4, 32, 32, 3), torch.randint(0, 10, (4,))
+    a = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.1),
+                    device="cpu")
+    a.step((x, y))
+    prefix = dtf.Saver(a.store).save(str(tmp_path), 1)
+    b = dtf.Trainer(dtf.Net(TwentyClasses()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.1),
+                    device="cpu")
+    b.build(x, y)
+    if tuple(b.store.vars["softmax_linear/weights"].shape) == tuple(a.store.vars["softmax_linear/weights"].shape):
+        pytest.skip("the example model has a fixed head")
+    with pytest.raises(ValueError, match="softmax_linear/weights.*checkpoint holds shape"):
+        dtf.Saver(b.store).restore(prefix)
