@@ -19,6 +19,39 @@ def _ready(var):
         st.notify_grad_ready(var)
 
 
+class UseVariableFn(torch.autograd.Function):
+    """Variable.value() on CUDA: forward hands out the bf16 shadow; backward accumulates into the fp32 gradient arena
+    (the variable may be used several times in one forward pass) and announces the gradient once the last
+    outstanding use of this step has delivered its part."""
+
+    @staticmethod
+    def forward(ctx, shadow, var):
+        ctx.var = var
+        st = getattr(var, "_store", None)
+        uses = getattr(st, "_bridge_uses", None) if st is not None else None
+        if uses is not None:
+            uses[var.name] = uses.get(var.name, 0) + 1
+        return shadow.view_as(shadow)
+
+    @staticmethod
+    def backward(ctx, g):
+        var = ctx.var
+        var.grad.add_(g.reshape(var.grad.shape))
+        st = getattr(var, "_store", None)
+        uses = getattr(st, "_bridge_uses", None) if st is not None else None
+        left = 0
+        if uses is not None and var.name in uses:
+            uses[var.name] -= 1
+            left = uses[var.name]
+        if left <= 0:
+            _ready(var)
+        return None, None
+
+
+def use_variable(var):
+    return UseVariableFn.apply(var.shadow, var)
+
+
 class ConvertInputFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, c_pad, scale, shift):

@@ -131,8 +131,16 @@ class Variable(object):
         return t[idx]
 
     def value(self) -> torch.Tensor:
-        """Tensor that layers compute with: bf16 shadow on CUDA (after finalize), fp32 master otherwise."""
-        return self.shadow if self.shadow is not None else self.master
+        """The variable as a tensor for USER code written in plain torch ops (what `weight()` / `bias()` of the
+        reference hand to the user, distribute_tools.py:211-224): the fp32 master on CPU; on CUDA the bf16 shadow
+        behind a bridge whose backward adds the incoming gradient into this variable's slice of the gradient arena
+        and announces it to the bucketed collectives, like the library's own layers do. Logical shape."""
+        if self.shadow is None:
+            return self.logical(self.master)
+        if not self.trainable:
+            return self.logical(self.shadow)
+        from . import functional as Fn
+        return self.logical(Fn.use_variable(self))
 
     def __repr__(self):
         return "Variable(%s, %s)" % (self.name, self.shape)
@@ -329,6 +337,7 @@ class VariableStore(object):
                 v.shadow = v.shadow.detach().requires_grad_(True)
 
     def zero_grads(self):
+        self._bridge_uses = {}  # outstanding Variable.value() applications of this step (engine/functional.py)
         if self.grad_arena is not None:
             from ..ops import _lib
             _lib.call("dtf_fill_u32", self.grad_arena, self.grad_arena.numel(), 0, _lib.stream_ptr())

@@ -423,3 +423,46 @@ def graph_replay_with_a_smaller_batch_in_between(opt_factory):
     for k in se:
         d = float((se[k] - sg[k]).abs().max())
         assert d <= 2e-3 * float(se[k].abs().max()) + 1e-5, (k, d)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# weight() / bias() handed to user code (distribute_tools.py:211-224): the variables are used by plain torch ops.
+
+class RawVariableModel(dtf.Model):
+    def inference(self, x, *a, **k):
+        T = dtf.tools
+        h = T.global_avg_pool(T.conv("c1", x, 3, 48))                      # [N, 48]
+        with dtf.variable_scope("proj"):
+            W, b = T.weight([48, 12]), T.bias([12])
+        z = torch.tanh(h.float() @ W.value().float() + b.value().float())   # user math in torch
+        with dtf.variable_scope("gate"):
+            g = T.weight([12])
+        z = z * torch.sigmoid(g.value().float()) + z * g.value().float()    # the same variable used twice
+        return T.fc_nonacti("logits", z, 5)
+
+
+def raw_variables_in_user_code_train(device):
+    torch.manual_seed(13)
+    x, y = torch.rand(8, 12, 12, 3), torch.randint(0, 5, (8,))
+    tr = dtf.Trainer(dtf.Net(RawVariableModel()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.5),
+                     device=device)
+    tr.build(x, y)
+    return tr, x, y
+
+
+def raw_variables_parity():
+    cpu, x, y = raw_variables_in_user_code_train("cpu")
+    gpu, _, _ = raw_variables_in_user_code_train("cuda:0")
+    gpu.store.load_state_dict(cpu.store.state_dict())
+    gpu.store.shadow_arena.copy_(gpu.store.master_arena)
+    gpu.store.refresh_transposed_shadows()
+    before = {k: v.clone() for k, v in cpu.store.state_dict().items()}
+    lc, lg = float(cpu.step((x, y))), float(gpu.step((x, y)))
+    assert abs(lc - lg) < 0.02 * max(1.0, abs(lc)), (lc, lg)
+    ac, ag = cpu.store.state_dict(), gpu.store.state_dict()
+    for k in ("proj/weights", "proj/biases", "gate/weights", "c1/weights", "logits/weights"):
+        dc = (ac[k] - before[k]).flatten().double()
+        dg = (ag[k].cpu() - before[k]).flatten().double()
+        assert dc.norm() > 1e-6, k  # the user's variables do receive gradients
+        cos = float(torch.dot(dc, dg) / (dc.norm() * dg.norm() + 1e-30))
+        assert cos > 0.97 and abs(float(dg.norm() / dc.norm()) - 1.0) < 0.15, (k, cos, float(dg.norm() / dc.norm()))

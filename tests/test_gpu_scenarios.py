@@ -80,3 +80,10 @@ def test_graph_replay_survives_a_batch_of_another_size(opt):
     import distributed_tensorflow_framework_b200 as dtf
     scenarios.graph_replay_with_a_smaller_batch_in_between(
         (lambda: dtf.MomentumOptimizer(0.02, 0.9)) if opt == "momentum" else (lambda: dtf.AdamOptimizer(1e-3)))
+
+
+def test_weight_and_bias_helpers_used_by_plain_torch_code_match_the_cpu_path():
+    scenarios.raw_variables_parity()
+    tr, x, y = scenarios.raw_variables_in_user_code_train("cuda:0")
+    losses = [float(tr.step((x, y))) for _ in range(15)]
+    assert losses[-1] < losses[0], losses

@@ -39,3 +39,13 @@ def test_restoring_into_a_model_of_another_shape_names_the_variable(tmp_path):
         pytest.skip("the example model has a fixed head")
     with pytest.raises(ValueError, match="softmax_linear/weights.*checkpoint holds shape"):
         dtf.Saver(b.store).restore(prefix)
+
+
+def test_weight_and_bias_helpers_used_by_plain_torch_code_receive_gradients():
+    tr, x, y = scenarios.raw_variables_in_user_code_train("cpu")
+    before = {k: v.clone() for k, v in tr.store.state_dict().items()}
+    losses = [float(tr.step((x, y))) for _ in range(15)]
+    after = tr.store.state_dict()
+    for k in ("proj/weights", "proj/biases", "gate/weights"):
+        assert float((after[k] - before[k]).abs().max()) > 0, k
+    assert losses[-1] < losses[0], losses
