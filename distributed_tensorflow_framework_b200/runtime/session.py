@@ -142,7 +142,9 @@ class MonitoredTrainingSession(object):
         return self
 
     def _init_or_restore(self):
-        """Chief: restore from the latest checkpoint if there is one, else run init_op; then init_fn(scaffold, sess).
+        """Restore from the latest checkpoint if there is one; otherwise run init_op, then init_fn(scaffold, sess) --
+        as in tf.train.SessionManager.prepare_session, a model recovered from a checkpoint is NOT re-initialised (an
+        init_fn that warm-starts from pretrained weights must not overwrite a resumed run).
         Non-chief workers restore the same checkpoint (every replica holds the full model) and then wait for the
         chief at the barrier -- the analogue of "Waiting for session to be initialized" (distribute_train.py:164-167)."""
         restored = False
@@ -151,10 +153,11 @@ class MonitoredTrainingSession(object):
             if prefix is not None:
                 self.saver.restore(prefix)
                 restored = True
-        if not restored and self.scaffold.init_op is not None:
-            self.scaffold.init_op()
-        if self.scaffold.init_fn is not None:
-            self.scaffold.init_fn(self.scaffold, self)
+        if not restored:
+            if self.scaffold.init_op is not None:
+                self.scaffold.init_op()
+            if self.scaffold.init_fn is not None:
+                self.scaffold.init_fn(self.scaffold, self)
         if self._barrier_fn is not None:
             self._barrier_fn()
 

@@ -466,3 +466,49 @@ def raw_variables_parity():
         assert dc.norm() > 1e-6, k  # the user's variables do receive gradients
         cos = float(torch.dot(dc, dg) / (dc.norm() * dg.norm() + 1e-30))
         assert cos > 0.97 and abs(float(dg.norm() / dc.norm()) - 1.0) < 0.15, (k, cos, float(dg.norm() / dc.norm()))
+
+
+def warm_start_then_resume(tmp_path, gpu):
+    """init_fn warm-starts a new model_dir from another run's checkpoint (tf.train.Scaffold(init_fn=...),
+    distribute_train.py:169-175); a later run on the same model_dir resumes from ITS checkpoint and does not run the
+    init_fn again."""
+    pre, md = str(tmp_path / "pretrained"), str(tmp_path / "finetune")
+    os.makedirs(pre)
+    os.makedirs(md)
+    dtf.run_main(experiment(pre, gpu, model="TinyMLP", loader="BlobPlaceholderLoader", epochs=4, samples=64, batch=16,
+                            opt=dtf.AdamOptimizer(0.01)))
+    src = tb.latest_checkpoint(pre)
+    with tb.BundleReader(src) as r:
+        w_src = torch.from_numpy(r.get_tensor("fc1/weights"))
+    calls = []
+
+    def init_fn(scaffold, sess):
+        calls.append(sess.global_step)
+        dtf.Saver(sess.store).restore(src)   # parameters only: no optimizer passed, slots start fresh
+        sess.store.global_step = 0
+
+    seen = {}
+
+    class FirstStep(H.SessionRunHook):
+        def after_create_session(self, session):
+            seen["w0"] = session.store.vars["fc1/weights"].master.detach().cpu().clone()
+            seen["step0"] = session.global_step
+
+    def run(epochs):
+        main = ann.get_advice(init_fn=init_fn)(experiment(md, gpu, model="TinyMLP", loader="BlobPlaceholderLoader",
+                                                          epochs=epochs, samples=64, batch=16,
+                                                          opt=dtf.AdamOptimizer(0.001)))
+        op = dtf.build_operator(main)
+        op.extra_hooks = [FirstStep()]
+        op.run()
+        return op
+
+    op = run(1)
+    assert calls == [0] and seen["step0"] == 0
+    assert torch.allclose(seen["w0"], w_src, atol=0), "the first run starts from the pretrained weights"
+    assert op.trainer.store.global_step == 4
+    w_after = op.trainer.store.vars["fc1/weights"].master.detach().cpu().clone()
+    op2 = run(2)
+    assert calls == [0], "a resumed run must not be re-initialised"
+    assert seen["step0"] == 4 and torch.allclose(seen["w0"], w_after, atol=0)
+    assert op2.trainer.store.global_step == 8

@@ -87,3 +87,7 @@ def test_weight_and_bias_helpers_used_by_plain_torch_code_match_the_cpu_path():
     tr, x, y = scenarios.raw_variables_in_user_code_train("cuda:0")
     losses = [float(tr.step((x, y))) for _ in range(15)]
     assert losses[-1] < losses[0], losses
+
+
+def test_init_fn_warm_starts_a_fresh_run_and_is_skipped_on_resume(tmp_path):
+    scenarios.warm_start_then_resume(tmp_path, gpu=True)

@@ -49,3 +49,7 @@ def test_weight_and_bias_helpers_used_by_plain_torch_code_receive_gradients():
     for k in ("proj/weights", "proj/biases", "gate/weights"):
         assert float((after[k] - before[k]).abs().max()) > 0, k
     assert losses[-1] < losses[0], losses
+
+
+def test_init_fn_warm_starts_a_fresh_run_and_is_skipped_on_resume(tmp_path):
+    scenarios.warm_start_then_resume(tmp_path, gpu=False)
