@@ -37,6 +37,25 @@ def _sync_mode(annotated=None):
     return "sync"
 
 
+def _record_files(data_dir):
+    """TFRecord inputs named by @data_dir / parse_data_dir_fn: a file (the reference passes one path to
+    string_input_producer, distribute_train.py:119-128), a list of files, a glob pattern, or a directory whose
+    *.tfrecord / *.tfrecords / *.record files are taken in sorted order."""
+    import glob
+    if not isinstance(data_dir, str):
+        return [str(p) for p in data_dir]
+    if any(ch in data_dir for ch in "*?["):
+        files = sorted(glob.glob(data_dir))
+    elif os.path.isdir(data_dir):
+        files = sorted(os.path.join(data_dir, f) for f in os.listdir(data_dir)
+                       if f.endswith((".tfrecord", ".tfrecords", ".record")) or ".tfrecord-" in f)
+    else:
+        return [data_dir]
+    if not files:
+        raise ValueError("no TFRecord files found under %r" % data_dir)
+    return files
+
+
 @annotations.get_advice(pre_fn=None)
 class Train(object):
     """Attributes injected by the IoC container: data_loader, input_mode, batch_size, epoch_num, sample_number,
@@ -110,7 +129,7 @@ class Train(object):
         # input pipeline (one logical pipeline per tower, like distribute_train.py:119-128)
         name_queue = placeholder_queue = None
         if self.input_mode == Input.InputOptions.TF_RECORD:
-            name_queue = Input.FilenameQueue([data_dir] if isinstance(data_dir, str) else list(data_dir), shuffle=True)
+            name_queue = Input.FilenameQueue(_record_files(data_dir), shuffle=True)
         elif self.input_mode == Input.InputOptions.DATAPATHLOADER:
             name_queue = self.data_loader.create_name_queue(data_dir)
         elif self.input_mode == Input.InputOptions.PLACEHOLDER:

@@ -53,3 +53,18 @@ def test_weight_and_bias_helpers_used_by_plain_torch_code_receive_gradients():
 
 def test_init_fn_warm_starts_a_fresh_run_and_is_skipped_on_resume(tmp_path):
     scenarios.warm_start_then_resume(tmp_path, gpu=False)
+
+
+def test_tfrecord_inputs_may_be_a_file_a_list_a_glob_or_a_directory(tmp_path):
+    import pytest
+    from distributed_tensorflow_framework_b200.runtime.train import _record_files
+    for n in ("b.tfrecord", "a.tfrecord", "c.tfrecords", "part.tfrecord-00001-of-00002", "notes.txt"):
+        (tmp_path / n).write_bytes(b"")
+    d = str(tmp_path)
+    assert _record_files(d + "/a.tfrecord") == [d + "/a.tfrecord"]
+    assert _record_files([d + "/a.tfrecord", d + "/b.tfrecord"]) == [d + "/a.tfrecord", d + "/b.tfrecord"]
+    assert [f.rsplit("/", 1)[1] for f in _record_files(d + "/*.tfrecord")] == ["a.tfrecord", "b.tfrecord"]
+    assert [f.rsplit("/", 1)[1] for f in _record_files(d)] == ["a.tfrecord", "b.tfrecord", "c.tfrecords",
+                                                              "part.tfrecord-00001-of-00002"]
+    with pytest.raises(ValueError):
+        _record_files(d + "/*.nothing")
