@@ -65,7 +65,7 @@ class Trainer(object):
         if self.built:
             return
         with V.using_store(self.store), torch.no_grad():
-            raw = self._to_device(sample_raw)
+            raw = self._to_device(self._host_pairs((sample_raw, sample_gt))[0][0][0])
             self.store.losses = []
             self.net.process(raw)
         if self.device.type == "cuda":
@@ -124,7 +124,25 @@ class Trainer(object):
         return self._graph_step(batches)
 
     # ------------------------------------------------------------------ host batches: staged H2D on a copy stream
-    def _stage(self, host_batches):
+    @staticmethod
+    def _host_pairs(host_batches):
+        """Normalise what a loader hands over: one (raw, gt) pair -- tuple or list -- or a list with one pair per
+        tower; numpy arrays / nested lists become tensors (float64 -> float32, the default dtype of numpy data).
+        Returns (pairs of tensors, the original objects as the identity key of the staging cache)."""
+        import numpy as np
+        if isinstance(host_batches, (tuple, list)) and len(host_batches) == 2 and \
+                not isinstance(host_batches[0], (tuple, list)):
+            host_batches = [host_batches]
+        keys = [(r, g) for r, g in host_batches]
+
+        def conv(t):
+            if t is None or isinstance(t, torch.Tensor):
+                return t
+            t = torch.as_tensor(np.ascontiguousarray(t))
+            return t.float() if t.dtype == torch.float64 else t
+        return [(conv(r), conv(g)) for r, g in keys], keys
+
+    def _stage(self, host_batches, keys=None):
         """Enqueue the H2D copy of `host_batches` (list of (raw, gt)) into the next staging slot on the copy stream.
         Returns the slot index."""
         if self._copy_stream is None:
@@ -150,7 +168,7 @@ class Trainer(object):
             ev = torch.cuda.Event()
             ev.record(cs)
         self._staged_ready[k] = ev
-        self._staged_src[k] = host_batches
+        self._staged_src[k] = keys if keys is not None else host_batches
         return k
 
     @staticmethod
@@ -162,30 +180,26 @@ class Trainer(object):
         is still running; the next `step()` call with the same batch objects finds the data already on the device."""
         if self.device.type != "cuda":
             return
-        if isinstance(host_batches, tuple):
-            host_batches = [host_batches]
-        host_batches = list(host_batches)
+        host_batches, keys = self._host_pairs(host_batches)
         if any(r.device.type == "cuda" for r, _ in host_batches):
             return
         for k in (0, 1):
-            if self._same_batches(self._staged_src[k], host_batches):
+            if self._same_batches(self._staged_src[k], keys):
                 return
-        self._stage(host_batches)
+        self._stage(host_batches, keys)
 
     def step(self, host_batches):
         """Public per-step API: host (pinned) batches -> H2D on the copy stream -> step -> loss tensor on the device.
         `host_batches` is one (raw, gt) pair or a list with one pair per tower."""
-        if isinstance(host_batches, tuple):
-            host_batches = [host_batches]
-        host_batches = list(host_batches)
+        host_batches, keys = self._host_pairs(host_batches)
         if self.device.type != "cuda" or any(r.device.type == "cuda" for r, _ in host_batches):
             return self.step_device([(self._to_device(r), self._to_device(g)) for r, g in host_batches])
         k = None
         for j in (0, 1):
-            if self._same_batches(self._staged_src[j], host_batches):
+            if self._same_batches(self._staged_src[j], keys):
                 k = j
         if k is None:
-            k = self._stage(host_batches)
+            k = self._stage(host_batches, keys)
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(self._staged_ready[k])
         self._staged_src[k] = None  # consumed: the same host object may carry new data next time

@@ -68,3 +68,21 @@ def test_tfrecord_inputs_may_be_a_file_a_list_a_glob_or_a_directory(tmp_path):
                                                               "part.tfrecord-00001-of-00002"]
     with pytest.raises(ValueError):
         _record_files(d + "/*.nothing")
+
+
+def test_trainer_accepts_numpy_batches_and_list_pairs():
+    import numpy as np
+    import torch
+    import distributed_tensorflow_framework_b200 as dtf
+    from distributed_tensorflow_framework_b200 import models
+    rng = np.random.RandomState(0)
+    x, y = rng.rand(4, 32, 32, 3), rng.randint(0, 10, size=(4,)).astype(np.int32)   # float64 images, int32 labels
+    tr = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.05),
+                     device="cpu")
+    l0 = float(tr.step([x, y]))            # a list pair, numpy
+    l1 = float(tr.step((torch.from_numpy(x).float(), torch.from_numpy(y).long())))
+    assert l0 == l0 and l1 == l1 and tr.store.global_step == 2
+    two = dtf.Trainer(dtf.Net(models.Cifar10CNN()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.05),
+                      device="cpu", gpu_num=2)
+    losses = [float(two.step([(x, y), [x, y]])) for _ in range(2)]   # one pair per tower, tuple or list
+    assert all(l == l for l in losses) and two.store.global_step == 2
