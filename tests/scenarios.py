@@ -400,7 +400,7 @@ def user_torch_ops_loss_and_advice_parity():
     assert losses[-1] < lg, (lg, losses)
 
 
-def graph_replay_with_a_smaller_batch_in_between(opt_factory):
+def graph_replay_with_a_smaller_batch_in_between(opt_factory, abs_tol=1e-5):
     """CUDA-graph training where one batch has another size (the last batch of an epoch): that step runs eagerly,
     replays continue afterwards, and the result equals eager training on the same sequence."""
     torch.manual_seed(9)
@@ -422,7 +422,7 @@ def graph_replay_with_a_smaller_batch_in_between(opt_factory):
     se, sg = eager.store.state_dict(), graph.store.state_dict()
     for k in se:
         d = float((se[k] - sg[k]).abs().max())
-        assert d <= 2e-3 * float(se[k].abs().max()) + 1e-5, (k, d)
+        assert d <= 2e-3 * float(se[k].abs().max()) + abs_tol, (k, d)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
