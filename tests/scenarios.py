@@ -512,3 +512,66 @@ def warm_start_then_resume(tmp_path, gpu):
     assert calls == [0], "a resumed run must not be re-initialised"
     assert seen["step0"] == 4 and torch.allclose(seen["w0"], w_after, atol=0)
     assert op2.trainer.store.global_step == 8
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The first model most users write: a LeNet on 28x28x1 images, numpy batches, uint8 pixels, int32 labels.
+
+class LeNet(dtf.Model):
+    def inference(self, x, *a, **k):
+        T = dtf.tools
+        x = T.pool("p1", T.conv("c1", x, 1, 32, kernel_size=[5, 5]))      # 14x14x32
+        x = T.pool("p2", T.conv("c2", x, 32, 64, kernel_size=[5, 5]))     # 7x7x64
+        return T.fc_nonacti("logits", T.FC_layer("f1", x, 128), 10)
+
+
+def _digits(n, seed):
+    """Synthetic 'digits': class k lights up a k-dependent stripe pattern; uint8 pixels, int32 labels, numpy."""
+    rng = np.random.RandomState(seed)
+    y = rng.randint(0, 10, size=(n,)).astype(np.int32)
+    x = rng.randint(0, 40, size=(n, 28, 28, 1)).astype(np.uint8)
+    for i, c in enumerate(y):
+        x[i, 2 * c + 2:2 * c + 6, :, 0] += 150
+        x[i, :, 2 * c + 3:2 * c + 5, 0] += 60
+    return x, y
+
+
+def lenet_on_numpy_uint8_batches_learns(device, use_graph=False):
+    kw = {"use_cuda_graph": True} if use_graph else {}
+    tr = dtf.Trainer(dtf.Net(LeNet()), dtf.SoftmaxCrossEntropyLoss(), dtf.AdamOptimizer(2e-3), device=device, **kw)
+    pool = [_digits(32, s) for s in range(4)]
+    losses = []
+    for i in range(40):
+        b = pool[i % 4]
+        tr.prefetch(pool[(i + 1) % 4])
+        losses.append(float(tr.step(b)))
+    assert all(l == l for l in losses) and losses[-1] < 0.5 * losses[0], (losses[0], losses[-1])
+    x, y = _digits(64, 99)
+    layers.set_training(False)
+    try:
+        with torch.no_grad(), V.using_store(tr.store):
+            logits = tr.net.process(torch.from_numpy(x).to(tr.device)).float().cpu()
+    finally:
+        layers.set_training(True)
+    acc = float((logits.argmax(1).numpy() == y).mean())
+    assert acc > 0.8, acc
+    return acc
+
+
+def resnet_tiny_batches(device):
+    """Batch 2 at 32x32 (the last stage is 1x1: batch norm over two values per channel), then inference on batch 1
+    and on batch 3."""
+    torch.manual_seed(21)
+    tr = dtf.Trainer(dtf.Net(TinyResNet18()), dtf.SoftmaxCrossEntropyLoss(), dtf.MomentumOptimizer(0.01, 0.9),
+                     device=device)
+    x, y = torch.rand(2, 32, 32, 3), torch.randint(0, 16, (2,))
+    losses = [float(tr.step((x, y))) for _ in range(4)]
+    assert all(l == l and l < 1e4 for l in losses), losses
+    layers.set_training(False)
+    try:
+        with torch.no_grad(), V.using_store(tr.store):
+            for n in (1, 3):
+                out = tr.net.process(torch.rand(n, 32, 32, 3).to(tr.device)).float().cpu()
+                assert out.shape == (n, 16) and bool(torch.isfinite(out).all())
+    finally:
+        layers.set_training(True)

@@ -95,3 +95,12 @@ def test_weight_and_bias_helpers_used_by_plain_torch_code_match_the_cpu_path():
 
 def test_init_fn_warm_starts_a_fresh_run_and_is_skipped_on_resume(tmp_path):
     scenarios.warm_start_then_resume(tmp_path, gpu=True)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_lenet_on_numpy_uint8_batches_learns(graph):
+    scenarios.lenet_on_numpy_uint8_batches_learns("cuda:0", use_graph=graph)
+
+
+def test_resnet_on_tiny_batches():
+    scenarios.resnet_tiny_batches("cuda:0")

@@ -86,3 +86,11 @@ def test_trainer_accepts_numpy_batches_and_list_pairs():
                       device="cpu", gpu_num=2)
     losses = [float(two.step([(x, y), [x, y]])) for _ in range(2)]   # one pair per tower, tuple or list
     assert all(l == l for l in losses) and two.store.global_step == 2
+
+
+def test_lenet_on_numpy_uint8_batches_learns():
+    scenarios.lenet_on_numpy_uint8_batches_learns("cpu")
+
+
+def test_resnet_on_tiny_batches():
+    scenarios.resnet_tiny_batches("cpu")
