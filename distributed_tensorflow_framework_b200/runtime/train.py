@@ -240,6 +240,9 @@ class Train(object):
                     break
             self.final_loss = float(state["loss"]) if state["loss"] is not None else None
             sess.close()
+        # the session's end hooks have run (the chief has written the final checkpoint): no worker returns from
+        # train() before that, so a script that goes on to evaluate finds the checkpoint on every rank
+        barrier()
         kill_ps_queue.enqueue()
         logger.info("kill_ps_enqueue_op done....")
         if writer is not None:

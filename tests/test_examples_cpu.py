@@ -51,3 +51,4 @@ def test_dehaze_example_under_a_two_rank_launcher(tmp_path):
                 "examples/dehaze_tfrecord.py", "--image_size=16", "--samples=32", "--eval_samples=8", "--epochs=1",
                 "--batch=4", "--model_dir=%s" % model_dir, "--records_dir=%s" % rec_dir], timeout=380)
     assert out.count("eval @ step 8: batches = 2") == 2 and "EVAL step 8:" in out
+    assert "freshly initialised" not in out  # no rank evaluates before the chief's final checkpoint exists
