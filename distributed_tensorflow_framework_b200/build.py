@@ -69,6 +69,19 @@ def build_io(force=False):
     return IO_LIB
 
 
+def build_io_sanitized():
+    """AddressSanitizer + UndefinedBehaviorSanitizer build of the I/O library (lib/libdtf_b200_io_asan.so); run the
+    I/O tests against it with scripts/asan_io.sh (the host-side sanitizer tier)."""
+    iosrc = os.path.join(PKG, "io", "csrc")
+    srcs = sorted(os.path.join(iosrc, f) for f in os.listdir(iosrc) if f.endswith(".cc"))
+    out = os.path.join(LIBDIR, "libdtf_b200_io_asan.so")
+    os.makedirs(LIBDIR, exist_ok=True)
+    cmd = ["g++", "-O1", "-g", "-std=c++17", "-fPIC", "-shared", "-pthread", "-fno-omit-frame-pointer",
+           "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined", "-o", out] + srcs
+    subprocess.run(cmd, check=True)
+    return out
+
+
 def build_all(force=False, verbose=False):
     return build_cuda(force, verbose), build_io(force)
 

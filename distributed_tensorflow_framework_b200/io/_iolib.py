@@ -3,7 +3,8 @@ import ctypes
 import os
 
 _PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-_LIB_PATH = os.path.join(_PKG, "lib", "libdtf_b200_io.so")
+# DTF_IO_LIB: load another build of the library instead (the ASan / UBSan build of scripts/asan_io.sh)
+_LIB_PATH = os.environ.get("DTF_IO_LIB") or os.path.join(_PKG, "lib", "libdtf_b200_io.so")
 _lib = None
 
 c_void_p, c_char_p, c_int, c_ull, c_ll = ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, ctypes.c_ulonglong, ctypes.c_longlong
