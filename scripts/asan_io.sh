@@ -10,3 +10,11 @@ export LD_PRELOAD="$(gcc -print-file-name=libasan.so):$(gcc -print-file-name=lib
 export ASAN_OPTIONS="detect_leaks=0:abort_on_error=1:halt_on_error=1"
 export UBSAN_OPTIONS="print_stacktrace=1:halt_on_error=1"
 python -m pytest tests/test_io.py tests/test_io_fuzz.py -x -q -p no:cacheprovider "$@"
+# second stage: ThreadSanitizer build for the threaded pieces (shuffling prefetcher, record queue)
+TSAN_LIB=distributed_tensorflow_framework_b200/lib/libdtf_b200_io_tsan.so
+g++ -O1 -g -std=c++17 -fPIC -shared -pthread -fsanitize=thread -o "$TSAN_LIB" distributed_tensorflow_framework_b200/io/csrc/*.cc
+export DTF_IO_LIB="$PWD/$TSAN_LIB"
+export LD_PRELOAD="$(gcc -print-file-name=libtsan.so)"
+export TSAN_OPTIONS="halt_on_error=1:report_signal_unsafe=0:exitcode=66"
+unset ASAN_OPTIONS UBSAN_OPTIONS
+python -m pytest tests/test_io.py -x -q -p no:cacheprovider "$@"

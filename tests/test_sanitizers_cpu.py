@@ -1,5 +1,6 @@
 """Host-side sanitizer tier: the I/O tests, including the corrupted-input fuzz, against an
-AddressSanitizer + UBSan build of the C++ I/O library (scripts/asan_io.sh)."""
+AddressSanitizer + UBSan build of the C++ I/O library, then the I/O tests against a ThreadSanitizer build (the
+shuffling prefetcher and the record queue are threaded) -- scripts/asan_io.sh."""
 import os
 import shutil
 import subprocess
@@ -10,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.timeout(600)
-def test_io_library_is_clean_under_asan_and_ubsan():
+def test_io_library_is_clean_under_asan_ubsan_and_tsan():
     if shutil.which("g++") is None:
         pytest.skip("no g++")
     asan = subprocess.run(["gcc", "-print-file-name=libasan.so"], capture_output=True, text=True).stdout.strip()
@@ -22,5 +23,6 @@ def test_io_library_is_clean_under_asan_and_ubsan():
     p = subprocess.run(["bash", os.path.join(ROOT, "scripts", "asan_io.sh")], capture_output=True, text=True,
                        env=env, timeout=580)
     tail = (p.stdout + p.stderr)[-3000:]
-    assert p.returncode == 0 and " passed" in p.stdout, tail
+    assert p.returncode == 0 and p.stdout.count(" passed") == 2, tail  # both stages ran their tests
     assert "ERROR: AddressSanitizer" not in tail and "runtime error:" not in tail, tail
+    assert "WARNING: ThreadSanitizer" not in tail, tail
