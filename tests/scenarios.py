@@ -130,8 +130,8 @@ def resnet_train_eval_and_cross_device_restore(tmp_path, gpu, model="TinyResNet1
     loader.batch_size = 8
     x, _ = loader.next_host_batch()
     x = x.clone()
-    cpu = dtf.Trainer(dtf.Net(getattr(__import__(__name__, fromlist=["x"]), model)()), dtf.SoftmaxCrossEntropyLoss(),
-                      dtf.GradientDescentOptimizer(0.1), device="cpu")
+    cpu = dtf.Trainer(dtf.Net(globals()[model]()), dtf.SoftmaxCrossEntropyLoss(), dtf.GradientDescentOptimizer(0.1),
+                      device="cpu")
     cpu.build(x, torch.zeros(8, dtype=torch.long))
     dtf.Saver(cpu.store).restore(prefix)
     layers.set_training(False)
