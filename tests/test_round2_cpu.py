@@ -37,7 +37,7 @@ def test_estimator_trains_checkpoints_resumes_and_evaluates(tmp_path):
     prefix = tb.latest_checkpoint(model_dir)
     assert prefix is not None and prefix.endswith("model.ckpt-6")
     with tb.BundleReader(prefix) as r:
-        assert int(r.get_tensor("global_step")) == 6 and "conv1/weights" in r.keys()
+        assert int(r.get_tensor("global_step").reshape(-1)[0]) == 6 and "conv1/weights" in r.keys()
         assert "conv1/weights/Momentum" in r.keys()
     ev = est.evaluate(lambda: iter(data))
     assert ev["global_step"] == 6 and ev["loss"] == ev["loss"] and 0.0 <= ev["accuracy"] <= 1.0

@@ -138,7 +138,7 @@ def test_train_operator_end_to_end_checkpoint_resume_and_eval(tmp_path):
         keys = set(r.keys())
         assert {"conv1/weights", "conv1/biases", "local3/weights", "softmax_linear/biases", "global_step",
                 "conv1/weights/Momentum"} <= keys
-        assert int(r.get_tensor("global_step")) == 16 and r.get_tensor("conv1/weights").shape == (5, 5, 3, 64)
+        assert int(r.get_tensor("global_step").reshape(-1)[0]) == 16 and r.get_tensor("conv1/weights").shape == (5, 5, 3, 64)
         saved_w = r.get_tensor("conv2/weights")
     assert any(f.startswith("events.out.tfevents") for f in os.listdir(model_dir))
     # resume: a second run restores, continues the global step and stops at the new total
