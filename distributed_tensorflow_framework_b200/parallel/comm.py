@@ -233,6 +233,26 @@ class Communicator(object):
             self.handle = None
 
 
+def plan_buckets(variables, n_params, bucket_bytes):
+    """Gradient buckets: contiguous [start, end) ranges of the arena in arena order, each closed at the first
+    variable boundary at or past `bucket_bytes` of fp32 gradients (at least 1024 elements); the last one runs to the
+    end of the arena. Returns [[start, end, [variables]]]: a partition of [0, n_params) in which every variable
+    (with its alignment padding) lies in exactly one bucket."""
+    per_bucket = max(bucket_bytes // 4, 1024)
+    tv = sorted(variables, key=lambda v: v.offset)
+    buckets = []
+    cur_start, cur_vars = 0, []
+    for v in tv:
+        cur_vars.append(v)
+        end = v.offset + V.padded_numel(v.numel)
+        if end - cur_start >= per_bucket:
+            buckets.append([cur_start, end, cur_vars])
+            cur_start, cur_vars = end, []
+    if cur_vars:
+        buckets.append([cur_start, n_params, cur_vars])
+    return buckets
+
+
 class GradientEngine(object):
     """Connects a finalized VariableStore to the fused gradient collectives.
 
@@ -309,18 +329,7 @@ class GradientEngine(object):
         store.masters_replicated = self.algo in ("local", "oneshot", "nccl") or world == 1
         self.n = store.n_params
         # buckets: contiguous [start, end) in arena order, flushed from the tail (last layers finish first)
-        per_bucket = max(bucket_bytes // 4, 1024)
-        tv = sorted(store.trainable_variables(), key=lambda v: v.offset)
-        self.buckets = []
-        cur_start, cur_vars = 0, []
-        for v in tv:
-            cur_vars.append(v)
-            end = v.offset + V.padded_numel(v.numel)
-            if end - cur_start >= per_bucket:
-                self.buckets.append([cur_start, end, cur_vars])
-                cur_start, cur_vars = end, []
-        if cur_vars:
-            self.buckets.append([cur_start, self.n, cur_vars])
+        self.buckets = plan_buckets(store.trainable_variables(), self.n, bucket_bytes)
         self._bucket_of = {}
         for bi, (_, _, vs) in enumerate(self.buckets):
             for v in vs:

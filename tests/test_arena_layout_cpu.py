@@ -78,3 +78,25 @@ def test_arena_layout_properties(specs, world, placement):
         assert all(not small(v) or v.offset + v.numel <= hi for v in tv) and lo == 0
     # the non-trainable statistics stay outside the arenas
     assert store.vars["stats/moving_mean"].master.numel() == 7
+
+
+@settings(max_examples=60, deadline=None)
+@given(specs=st.lists(var_spec, min_size=1, max_size=24), world=st.integers(1, 8),
+       placement=st.sampled_from(["bytes", "round_robin"]), bucket_kib=st.sampled_from([1, 4, 64, 4096]))
+def test_gradient_buckets_partition_the_arena(specs, world, placement, bucket_kib):
+    from distributed_tensorflow_framework_b200.parallel.comm import plan_buckets
+    store = _make_store(specs)
+    store.device = _FakeCuda()
+    store._build_tap_table = lambda descs, tiles: setattr(store, "_tap_table", None)
+    store.finalize(allocator=lambda tag, n, dt: torch.zeros(n, dtype=dt), placement=placement, world=world)
+    tv = store.trainable_variables()
+    buckets = plan_buckets(tv, store.n_params, bucket_kib << 10)
+    assert buckets[0][0] == 0 and buckets[-1][1] == store.n_params
+    assert all(buckets[i][1] == buckets[i + 1][0] for i in range(len(buckets) - 1))
+    seen = [v.name for _, _, vs in buckets for v in vs]
+    assert sorted(seen) == sorted(v.name for v in tv) and len(seen) == len(set(seen))
+    per = max((bucket_kib << 10) // 4, 1024)
+    for i, (lo, hi, vs) in enumerate(buckets):
+        assert vs and all(lo <= v.offset and v.offset + v.numel <= hi for v in vs)
+        if i < len(buckets) - 1:  # closed at the FIRST boundary past the threshold
+            assert hi - lo >= per and (len(vs) == 1 or vs[-1].offset - lo < per)
