@@ -52,3 +52,18 @@ def test_dehaze_example_under_a_two_rank_launcher(tmp_path):
                 "--batch=4", "--model_dir=%s" % model_dir, "--records_dir=%s" % rec_dir], timeout=380)
     assert out.count("eval @ step 8: batches = 2") == 2 and "EVAL step 8:" in out
     assert "freshly initialised" not in out  # no rank evaluates before the chief's final checkpoint exists
+
+
+@pytest.mark.timeout(300)
+def test_local_cluster_script_runs_a_ps_and_two_workers(tmp_path):
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        base = s.getsockname()[1]
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "TORCHELASTIC_RUN_ID")}
+    env.update(CUDA_VISIBLE_DEVICES="", DTF_BASE_PORT=str(base), DTF_MODEL_DIR=str(tmp_path))
+    p = subprocess.run(["bash", "examples/launch_local_cluster.sh", "2", "--samples=128"], cwd=ROOT, env=env,
+                       capture_output=True, text=True, timeout=280)
+    out = p.stdout + p.stderr
+    assert p.returncode == 0 and "cluster finished (exit 0)" in out, out[-3000:]
+    assert any(f.startswith("model.ckpt-4") for f in os.listdir(tmp_path))
