@@ -31,7 +31,7 @@ def write_bundle(prefix, tensors, shard_of=None, num_shards=1):
         if isinstance(arr, tuple):
             arr, tag = arr
             dt = DT_BFLOAT16 if tag == "bfloat16" else None
-        arr = np.ascontiguousarray(arr)
+        arr = np.require(arr, requirements="C")  # (ascontiguousarray would turn a scalar into shape [1])
         if dt is None:
             dt = _NP2DT[arr.dtype]
         shape = (ctypes.c_longlong * max(arr.ndim, 1))(*arr.shape)

@@ -153,6 +153,7 @@ def test_tensorbundle_roundtrip_and_independent_parse(tmp_path):
             ref = v[0] if isinstance(v, tuple) else v
             np.testing.assert_array_equal(r.get_tensor(k), ref)
         assert r.dtype_of("bf16w") == tb.DT_BFLOAT16 and r.dtype_of("global_step") == tb.DT_INT64
+        assert r.get_tensor("global_step").shape == ()  # a scalar, as tf.train.Saver writes global_step
     # independent parse: keys sorted bytewise, header first, entries decode to the right offsets
     kv = _py_read_index(prefix + ".index")
     keys = [k for k, _ in kv]

@@ -74,3 +74,31 @@ def test_corrupted_tfrecords_and_examples_raise_instead_of_crashing(tmp_path):
         except Exception:
             pass
     assert int(np.asarray(tfr.parse_single_example(example, feats)["label"]).reshape(-1)[0]) == 3
+
+
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+_names = st.text(alphabet="abcdefghij/_0123456789ABC", min_size=1, max_size=60).filter(
+    lambda s: not s.startswith("/") and not s.endswith("/"))
+_dtypes = st.sampled_from(["float32", "int32", "int64", "float16", "uint8", "float64"])
+_shapes = st.lists(st.integers(0, 7), min_size=0, max_size=4)
+
+
+@settings(max_examples=40, deadline=None)
+@given(items=st.dictionaries(_names, st.tuples(_dtypes, _shapes, st.integers(0, 2 ** 31 - 1)), min_size=1, max_size=30),
+       num_shards=st.integers(1, 4))
+def test_checkpoint_round_trip_for_random_names_shapes_dtypes_and_shards(tmp_path_factory, items, num_shards):
+    d = tmp_path_factory.mktemp("bundle")
+    prefix = str(d / "model.ckpt-7")
+    tensors, shard_of = {}, {}
+    for i, (name, (dt, shape, seed)) in enumerate(sorted(items.items())):
+        rng = np.random.RandomState(seed)
+        tensors[name] = (rng.rand(*shape) * 100).astype(dt) if shape else np.array(rng.rand() * 100).astype(dt)
+        shard_of[name] = i % num_shards
+    tb.write_bundle(prefix, tensors, shard_of=shard_of, num_shards=num_shards)
+    with tb.BundleReader(prefix) as r:
+        assert r.num_shards == num_shards and set(r.keys()) == set(tensors)
+        for name, ref in tensors.items():
+            got = r.get_tensor(name)
+            assert got.dtype == ref.dtype and tuple(got.shape) == tuple(ref.shape), name
+            assert np.array_equal(got, ref), name
