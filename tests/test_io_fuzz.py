@@ -102,3 +102,53 @@ def test_checkpoint_round_trip_for_random_names_shapes_dtypes_and_shards(tmp_pat
             got = r.get_tensor(name)
             assert got.dtype == ref.dtype and tuple(got.shape) == tuple(ref.shape), name
             assert np.array_equal(got, ref), name
+
+
+def _py_crc32c(data):
+    crc = 0xffffffff
+    for b in data:
+        crc ^= b
+        for _ in range(8):
+            crc = (crc >> 1) ^ (0x82f63b78 if crc & 1 else 0)
+    return crc ^ 0xffffffff
+
+
+@settings(max_examples=80, deadline=None)
+@given(data=st.binary(min_size=0, max_size=700))
+def test_crc32c_matches_a_bitwise_reference_for_random_buffers(data):
+    from distributed_tensorflow_framework_b200.io import _iolib
+    assert _iolib.lib().dtf_crc32c(data, len(data)) == _py_crc32c(data)
+
+
+_feat_name = st.text(alphabet="abcdefgh_/XYZ019", min_size=1, max_size=24)
+_feat_value = st.one_of(
+    st.lists(st.binary(min_size=0, max_size=40), min_size=1, max_size=4),
+    st.lists(st.integers(-2 ** 63, 2 ** 63 - 1), min_size=1, max_size=9),
+    st.lists(st.floats(width=32, allow_nan=False, allow_infinity=False), min_size=1, max_size=9))
+
+
+@settings(max_examples=80, deadline=None)
+@given(features=st.dictionaries(_feat_name, _feat_value, min_size=1, max_size=8))
+def test_example_round_trip_for_random_features(tmp_path_factory, features):
+    """make_example -> TFRecord file -> C++ reader -> C++ Example parser gives back every value (bytes lists,
+    negative / 64-bit integers as varints, packed floats), whatever the feature names and their order."""
+    path = str(tmp_path_factory.mktemp("rec") / "x.tfrecord")
+    with tfr.TFRecordWriter(path) as w:
+        w.write(tfr.make_example(features))
+        w.write(tfr.make_example(features))
+    spec = {}
+    for name, v in features.items():
+        kind = "string" if isinstance(v[0], bytes) else ("float32" if isinstance(v[0], float) else "int64")
+        spec[name] = tfr.FixedLenFeature([len(v)], kind)
+    n = 0
+    for rec in tfr.tf_record_iterator(path):
+        got = tfr.parse_single_example(rec, spec)
+        n += 1
+        for name, v in features.items():
+            if isinstance(v[0], bytes):
+                assert list(got[name]) == v, name
+            elif isinstance(v[0], float):
+                assert np.array_equal(got[name], np.array(v, dtype=np.float32)), name
+            else:
+                assert got[name].tolist() == v, name
+    assert n == 2
