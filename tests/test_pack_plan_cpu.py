@@ -105,3 +105,44 @@ def test_plans_are_refused_where_packing_does_not_apply():
     assert raw._pack_plan(14, 14, 64, 64, 1, 1, 2) is None      # 1x1: plain pixel selection + GEMM
     assert raw._pack_plan(14, 14, 64, 64, 3, 3, 1) is None      # stride 1, C % 64 == 0: the halo kernel takes it as is
     assert raw._pack_plan(14, 14, 24, 24, 3, 3, 2) is None      # C not a multiple of 16 and too wide to tap-pack
+
+
+# ---- the same identity for random geometries (rectangular images and kernels, both modes) ----------------------------
+from hypothesis import assume, given, settings, strategies as st  # noqa: E402
+
+
+def _same_ref_rect(x, w, s):
+    H, W, KH, KW = x.shape[1], x.shape[2], w.shape[0], w.shape[1]
+    OH, pt = raw.same_pad(H, KH, s)
+    OW, pl = raw.same_pad(W, KW, s)
+    pb = max((OH - 1) * s + KH - H, 0) - pt
+    pr = max((OW - 1) * s + KW - W, 0) - pl
+    xp = F.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    return F.conv2d(xp, w.permute(3, 2, 0, 1), stride=s).permute(0, 2, 3, 1)
+
+
+@settings(max_examples=60, deadline=None)
+@given(H=st.integers(3, 15), W=st.integers(3, 15), KH=st.integers(1, 7), KW=st.integers(1, 7), s=st.sampled_from([1, 2]),
+       geom=st.sampled_from([(16, 16), (32, 32), (8, 1), (8, 3), (8, 4), (16, 5)]), seed=st.integers(0, 1000))
+def test_packed_convolution_identity_for_random_geometries(H, W, KH, KW, s, geom, seed):
+    Cx, C = geom
+    plan = raw._pack_plan(H, W, Cx, C, KH, KW, s)
+    assume(plan is not None)
+    torch.manual_seed(seed)
+    Co = 8
+    x = torch.randn(1, H, W, Cx)
+    x[..., C:] = 0
+    w = torch.randn(KH, KW, Cx, Co)
+    ref = _same_ref_rect(x, w, s)
+    P = _pack(x, plan)
+    Wp = torch.zeros(plan.KH2 * plan.KW2 * plan.Cp, Co)
+    _block_copy(w.reshape(KH * KW * Cx, Co), Wp, plan.descs("w", Co, "cpu"))
+    wp4 = Wp.reshape(plan.KH2, plan.KW2, plan.Cp, Co)
+    Pp = F.pad(P.permute(0, 3, 1, 2), (plan.pad_w2, plan.KW2 - 1 - plan.pad_w2, plan.pad_h2, plan.KH2 - 1 - plan.pad_h2))
+    got = F.conv2d(Pp, wp4.permute(3, 2, 0, 1)).permute(0, 2, 3, 1)
+    assert got.shape == ref.shape, (plan.mode, got.shape, ref.shape)
+    assert torch.allclose(got, ref, atol=1e-4, rtol=1e-4), plan.mode
+    # and the filter-gradient descriptors invert the filter descriptors
+    back = torch.zeros(KH * KW * Cx, Co)
+    _block_copy(Wp, back, plan.descs("dw", Co, "cpu"))
+    assert torch.equal(back.reshape(KH, KW, Cx, Co)[:, :, :C], w[:, :, :C])
