@@ -94,3 +94,19 @@ def test_lenet_on_numpy_uint8_batches_learns():
 
 def test_resnet_on_tiny_batches():
     scenarios.resnet_tiny_batches("cpu")
+
+
+def test_inspect_checkpoint_tool_lists_tensors_and_events(tmp_path, capsys):
+    import os
+    import distributed_tensorflow_framework_b200 as dtf
+    from distributed_tensorflow_framework_b200.cli import inspect_checkpoint
+    md = str(tmp_path / "m")
+    os.makedirs(md)
+    dtf.run_main(scenarios.experiment(md, False, model="TinyMLP", loader="BlobPlaceholderLoader", epochs=1, samples=64,
+                                      batch=16, opt=dtf.AdamOptimizer(0.01)))
+    assert inspect_checkpoint.main([md, "--events"]) == 0
+    out = capsys.readouterr().out
+    assert "model.ckpt-4" in out and "fc1/weights" in out and "fc1/weights/Adam_1" in out and "[16, 64]" in out
+    assert "global_step" in out and "int64" in out and "event file" in out
+    assert inspect_checkpoint.main([md, "--tensor_name", "global_step"]) == 0
+    assert "\n4\n" in capsys.readouterr().out
