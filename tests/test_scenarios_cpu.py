@@ -110,3 +110,42 @@ def test_inspect_checkpoint_tool_lists_tensors_and_events(tmp_path, capsys):
     assert "global_step" in out and "int64" in out and "event file" in out
     assert inspect_checkpoint.main([md, "--tensor_name", "global_step"]) == 0
     assert "\n4\n" in capsys.readouterr().out
+
+
+def test_checkpoint_converts_to_a_torch_dict_and_back(tmp_path):
+    import os
+    import numpy as np
+    import torch
+    import distributed_tensorflow_framework_b200 as dtf
+    from distributed_tensorflow_framework_b200.cli import convert_checkpoint
+    from distributed_tensorflow_framework_b200.io import tensorbundle as tb
+    md = str(tmp_path / "m")
+    os.makedirs(md)
+    op = dtf.run_main(scenarios.experiment(md, False, model="TinyMLP", loader="BlobPlaceholderLoader", epochs=1,
+                                           samples=64, batch=16, opt=dtf.MomentumOptimizer(0.05, 0.9)))
+    pt = str(tmp_path / "model.pt")
+    assert convert_checkpoint.main([md, pt]) == 0
+    state = torch.load(pt)
+    assert int(state["global_step"]) == 4 and state["global_step"].shape == ()
+    assert torch.equal(state["fc1/weights"], op.trainer.store.vars["fc1/weights"].master.detach())
+    state["extra/bf16"] = torch.arange(6, dtype=torch.float32).reshape(2, 3).to(torch.bfloat16)
+    torch.save(state, pt)
+    new_dir = tmp_path / "converted"
+    new_dir.mkdir()
+    assert convert_checkpoint.main([pt, str(new_dir / "model.ckpt-4")]) == 0
+    assert tb.latest_checkpoint(str(new_dir)).endswith("model.ckpt-4")
+    # the converted checkpoint resumes a run
+    fresh = dtf.Trainer(dtf.Net(scenarios.TinyMLP()), dtf.SoftmaxCrossEntropyLoss(), dtf.MomentumOptimizer(0.05, 0.9),
+                        device="cpu")
+    fresh.build(torch.zeros(2, 16), torch.zeros(2, dtype=torch.long))
+    assert dtf.Saver(fresh.store, fresh.optimizer).restore(tb.latest_checkpoint(str(new_dir))) == 4
+    assert torch.equal(fresh.store.vars["logits/weights"].master.detach(), state["logits/weights"])
+    with tb.BundleReader(tb.latest_checkpoint(str(new_dir))) as r:
+        assert r.dtype_of("extra/bf16") == tb.DT_BFLOAT16
+        bits = r.get_tensor("extra/bf16")
+        assert np.array_equal((bits.astype(np.uint32) << 16).view(np.float32), np.arange(6, dtype=np.float32).reshape(2, 3))
+    back = str(tmp_path / "back.pt")
+    assert convert_checkpoint.main([str(new_dir), back]) == 0
+    again = torch.load(back)
+    assert again["extra/bf16"].dtype == torch.bfloat16 and torch.equal(again["extra/bf16"], state["extra/bf16"])
+    assert sorted(again) == sorted(state)
